@@ -1,0 +1,750 @@
+// tcgen05 / TMEM / TMA tensor-core kernels for sm_100a.
+//
+// One persistent, warp-specialised kernel template covers the three contraction shapes of the
+// training hot path:
+//   KIND_GEMM  : D[M,N] = A . B^T with A and B each either K-major or MN-major in memory
+//                (Linear forward / dgrad / wgrad -- the nn.Linear call sites of the reference,
+//                nn/attention.py:25,85 and arch/transformer.py:24-26).
+//   KIND_CONV  : implicit-GEMM convolution, A gathered by TMA in im2col mode from an NHWC tensor,
+//                B = filter matrix (K-major for fprop, MN-major for dgrad).
+//   KIND_WGRAD : filter gradient; the reduction runs over output pixels, so both operands are
+//                MN-major: A = dY tiles, B = im2col tiles of X.
+//
+// Roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+// warps 2..5 = epilogue (TMEM -> registers -> global).  Three mbarrier rings: smem full/empty
+// between producer and MMA, TMEM full/empty between MMA and epilogue (two accumulator buffers so
+// the epilogue of tile i overlaps the main loop of tile i+1).
+#include <string.h>
+
+#include "tc_ptx.cuh"
+
+namespace {
+
+constexpr int BM = 128;       // UMMA M (cta_group::1)
+constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
+constexpr int A_BYTES = BM * BK * 2;
+constexpr int NUM_THREADS = 192;
+constexpr int MAX_TAPS = 64;
+
+enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
+
+struct TapDesc {
+  int16_t ow, oh;  // filter-tap offsets handed to the im2col TMA
+  int32_t bcol;    // column (or row-block) of this tap inside the filter matrix
+};
+
+struct TcParams {
+  int M, N;             // extents of D (WGRAD: N = channels per tap)
+  int k_iters;          // 64-deep iterations of the full reduction
+  int splits;           // split-K factor (partials go to ws)
+  int n_mblk, n_nblk;   // tile grid
+  // im2col base-pixel mapping: linear index -> (img, i, j) -> (w, h) = (j*ts_w+lo_w, i*ts_h+lo_h)
+  int Wo, HoWo, ts_w, ts_h, lo_w, lo_h;
+  int cchunks;          // CONV: 64-channel chunks per tap
+  int ntaps;
+  int ncblk, tapC;      // WGRAD: column blocks per tap, channels per tap
+  // output mapping
+  long long ldd;        // row stride of D (elements)
+  int pix_map;          // CONV: rows of D are scattered pixels (strided dgrad)
+  int OW, OHOW, os_h, os_w, oa, ob;
+  void* D;              // bf16 output (when ws == nullptr)
+  float* ws;            // fp32 output / split-K partials [splits][M][ldw]
+  long long ldw;
+  const float* scale;   // per-column scale (nullable)
+  const float* shift;   // per-column shift / bias (nullable)
+  const bf16* residual; // added before ReLU (nullable), same indexing as D
+  int relu;
+  TapDesc taps[MAX_TAPS];
+};
+
+template <int BN>
+struct Cfg {
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+  static constexpr int TMEM_COLS = 2 * BN;  // 128 / 256 / 512: powers of two
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+};
+
+template <int BN, int KIND, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(NUM_THREADS, 1)
+tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+          const __grid_constant__ TcParams p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t raw_addr = tc::smem_u32(smem_raw);
+  uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
+
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + C::STAGES;
+  uint64_t* tfull_bar = empty_bar + C::STAGES;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int num_tiles = p.n_mblk * p.n_nblk * p.splits;
+
+  if (warp == 0 && lane == 0) {
+    tc::prefetch_tmap(&tmA);
+    tc::prefetch_tmap(&tmB);
+    for (int s = 0; s < C::STAGES; ++s) {
+      tc::mbar_init(&full_bar[s], 1);
+      tc::mbar_init(&empty_bar[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(&tfull_bar[a], 1);
+      tc::mbar_init(&tempty_bar[a], 4);  // one arrive per epilogue warp
+    }
+    tc::fence_barrier_init();
+  }
+  if (warp == 1) {
+    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tc::tmem_relinquish();
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        int t = tile;
+        const int nblk = t % p.n_nblk; t /= p.n_nblk;
+        const int mblk = t % p.n_mblk;
+        const int split = t / p.n_mblk;
+        const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
+        const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
+        const int m0 = mblk * BM;
+        int n0 = nblk * BN;
+        // CONV: base pixel of this M tile
+        int img0 = 0, w0 = 0, h0 = 0;
+        if (KIND == KIND_CONV) {
+          img0 = m0 / p.HoWo;
+          const int rem = m0 - img0 * p.HoWo;
+          const int i = rem / p.Wo, j = rem - i * p.Wo;
+          w0 = j * p.ts_w + p.lo_w;
+          h0 = i * p.ts_h + p.lo_h;
+        }
+        int wtap = 0;
+        if (KIND == KIND_WGRAD) {
+          wtap = nblk / p.ncblk;
+          n0 = (nblk - wtap * p.ncblk) * BN;  // channel offset inside the tap
+        }
+        for (int it = k_lo; it < k_hi; ++it) {
+          tc::mbar_wait(&empty_bar[stage], phase ^ 1u);
+          uint8_t* sA = smem + stage * C::STAGE_BYTES;
+          uint8_t* sB = sA + A_BYTES;
+          tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          if (KIND == KIND_GEMM) {
+            const int kc = it * BK;
+            if (!A_MN) {
+              tc::tma_load_2d(sA, &tmA, &full_bar[stage], kc, m0);
+            } else {
+              tc::tma_load_2d(sA, &tmA, &full_bar[stage], m0, kc);
+              tc::tma_load_2d(sA + 8192, &tmA, &full_bar[stage], m0 + 64, kc);
+            }
+            if (!B_MN) {
+              tc::tma_load_2d(sB, &tmB, &full_bar[stage], kc, n0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tc::tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], n0 + j * 64, kc);
+            }
+          } else if (KIND == KIND_CONV) {
+            const int tap = it / p.cchunks;
+            const int cc = it - tap * p.cchunks;
+            const TapDesc td = p.taps[tap];
+            tc::tma_load_im2col_4d(sA, &tmA, &full_bar[stage], cc * BK, w0, h0, img0, (uint16_t)td.ow,
+                                   (uint16_t)td.oh);
+            if (!B_MN) {
+              tc::tma_load_2d(sB, &tmB, &full_bar[stage], td.bcol + cc * BK, n0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BN / 64; ++j)
+                tc::tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], td.bcol + n0 + j * 64, cc * BK);
+            }
+          } else {  // KIND_WGRAD: reduction over pixels
+            const int pix0 = it * BK;
+            const int img = pix0 / p.HoWo;
+            const int rem = pix0 - img * p.HoWo;
+            const int i = rem / p.Wo, j2 = rem - i * p.Wo;
+            const TapDesc td = p.taps[wtap];
+            tc::tma_load_2d(sA, &tmA, &full_bar[stage], m0, pix0);
+            tc::tma_load_2d(sA + 8192, &tmA, &full_bar[stage], m0 + 64, pix0);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tc::tma_load_im2col_4d(sB + j * 8192, &tmB, &full_bar[stage], n0 + j * 64, j2 * p.ts_w + p.lo_w,
+                                     i * p.ts_h + p.lo_h, img, (uint16_t)td.ow, (uint16_t)td.oh);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, A_MN, B_MN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int split = tile / (p.n_nblk * p.n_mblk);
+        const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
+        const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
+        tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+        tc::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        for (int it = k_lo; it < k_hi; ++it) {
+          tc::mbar_wait(&full_bar[stage], phase);
+          tc::tc_fence_after();
+          const uint32_t sA = tc::smem_u32(smem + stage * C::STAGE_BYTES);
+          const uint32_t sB = sA + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t adesc = A_MN ? tc::make_smem_desc(sA + k * 2048, 8192, 1024)
+                                        : tc::make_smem_desc(sA + k * 32, 16, 1024);
+            const uint64_t bdesc = B_MN ? tc::make_smem_desc(sB + k * 2048, 8192, 1024)
+                                        : tc::make_smem_desc(sB + k * 32, 16, 1024);
+            tc::umma_bf16(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
+          }
+          tc::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+        }
+        tc::umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+      }
+    }
+  } else {
+    // ===================================================================== epilogue (warps 2..5)
+    const int q = warp & 3;  // TMEM lane quarter this warp may read
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      int t = tile;
+      const int nblk = t % p.n_nblk; t /= p.n_nblk;
+      const int mblk = t % p.n_mblk;
+      const int split = t / p.n_mblk;
+      const int row = mblk * BM + q * 32 + lane;
+      const bool row_ok = row < p.M;
+      int col_base, col_lim_local;  // first D column of this tile; valid columns inside the tile
+      if (KIND == KIND_WGRAD) {
+        const int wtap = nblk / p.ncblk;
+        const int c0 = (nblk - wtap * p.ncblk) * BN;
+        col_base = wtap * p.tapC + c0;
+        col_lim_local = p.N - c0;
+      } else {
+        col_base = nblk * BN;
+        col_lim_local = p.N - col_base;
+      }
+      long long out_row = row;
+      if (KIND == KIND_CONV && p.pix_map && row_ok) {
+        const int img = row / p.HoWo;
+        const int rem = row - img * p.HoWo;
+        const int i = rem / p.Wo, j = rem - i * p.Wo;
+        out_row = (long long)img * p.OHOW + (long long)(i * p.os_h + p.oa) * p.OW + (j * p.os_w + p.ob);
+      }
+      tc::mbar_wait(&tfull_bar[acc], acc_phase);
+      tc::tc_fence_after();
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        uint32_t r[32];
+        __syncwarp();
+        tc::tmem_ld32(tmem_base + (uint32_t)(acc * BN + chunk * 32) + ((uint32_t)(q * 32) << 16), r);
+        tc::tmem_ld_wait();
+        if (!row_ok) {
+          // rows past M hold no data; the aligned TMEM load above still had to run warp-wide
+        } else if (p.ws != nullptr) {
+          float* dst = p.ws + ((long long)split * p.M + row) * p.ldw + col_base + chunk * 32;
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            if (chunk * 32 + g * 4 < col_lim_local) {
+              float4 v = make_float4(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1]),
+                                     __uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3]));
+              *reinterpret_cast<float4*>(dst + g * 4) = v;
+            }
+          }
+        } else {
+          bf16* dst = reinterpret_cast<bf16*>(p.D) + out_row * p.ldd + col_base + chunk * 32;
+          const bf16* res = p.residual ? p.residual + out_row * p.ldd + col_base + chunk * 32 : nullptr;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            if (chunk * 32 + g * 8 < col_lim_local) {
+              float v[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * g + e]);
+              const int c = col_base + chunk * 32 + g * 8;
+              if (p.scale) {
+                const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
+                const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
+                v[0] *= s0.x; v[1] *= s0.y; v[2] *= s0.z; v[3] *= s0.w;
+                v[4] *= s1.x; v[5] *= s1.y; v[6] *= s1.z; v[7] *= s1.w;
+              }
+              if (p.shift) {
+                const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.shift + c));
+                const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.shift + c + 4));
+                v[0] += s0.x; v[1] += s0.y; v[2] += s0.z; v[3] += s0.w;
+                v[4] += s1.x; v[5] += s1.y; v[6] += s1.z; v[7] += s1.w;
+              }
+              if (res) {
+                float rr[8];
+                unpack8(*reinterpret_cast<const uint4*>(res + g * 8), rr);
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] += rr[e];
+              }
+              if (p.relu) {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+              }
+              *reinterpret_cast<uint4*>(dst + g * 8) = pack8(v);
+            }
+          }
+        }
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&tempty_bar[acc]);
+      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// Sum split-K partials (fp32) and finish the epilogue: out = [out +] sum_s ws[s] (+shift) (relu).
+__global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long slab, int ncols,
+                                     const float* __restrict__ shift, int relu, int accumulate, void* out,
+                                     int out_f32) {
+  const long long i4 = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i4 >= slab) return;
+  float4 a = *reinterpret_cast<const float4*>(ws + i4);
+  for (int s = 1; s < splits; ++s) {
+    const float4 b = *reinterpret_cast<const float4*>(ws + (long long)s * slab + i4);
+    a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+  }
+  if (shift) {
+    const int c = (int)(i4 % ncols);
+    a.x += shift[c]; a.y += shift[c + 1]; a.z += shift[c + 2]; a.w += shift[c + 3];
+  }
+  if (out_f32) {
+    float* o = reinterpret_cast<float*>(out) + i4;
+    if (accumulate) {
+      const float4 b = *reinterpret_cast<const float4*>(o);
+      a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w;
+    }
+    if (relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+    *reinterpret_cast<float4*>(o) = a;
+  } else {
+    bf16* o = reinterpret_cast<bf16*>(out) + i4;
+    if (accumulate) {
+      const uint2 b = *reinterpret_cast<const uint2*>(o);
+      const float2 b0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&b.x));
+      const float2 b1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&b.y));
+      a.x += b0.x; a.y += b0.y; a.z += b1.x; a.w += b1.y;
+    }
+    if (relu) { a.x = fmaxf(a.x, 0.f); a.y = fmaxf(a.y, 0.f); a.z = fmaxf(a.z, 0.f); a.w = fmaxf(a.w, 0.f); }
+    uint2 u;
+    u.x = pack2(a.x, a.y);
+    u.y = pack2(a.z, a.w);
+    *reinterpret_cast<uint2*>(o) = u;
+  }
+}
+
+// ------------------------------------------------------------------------------------- host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const int*, const int*, cuuint32_t, cuuint32_t,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn g_encode_tiled = nullptr;
+EncodeIm2colFn g_encode_im2col = nullptr;
+
+int load_driver_entry_points() {
+  if (g_encode_tiled && g_encode_im2col) return RNN_OK;
+  void* f = nullptr;
+  cudaDriverEntryPointQueryResult qr;
+  RNN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &qr));
+  RNN_REQUIRE(f != nullptr && qr == cudaDriverEntryPointSuccess, RNN_ERR_CUDA);
+  g_encode_tiled = reinterpret_cast<EncodeTiledFn>(f);
+  f = nullptr;
+  RNN_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &f, cudaEnableDefault, &qr));
+  RNN_REQUIRE(f != nullptr && qr == cudaDriverEntryPointSuccess, RNN_ERR_CUDA);
+  g_encode_im2col = reinterpret_cast<EncodeIm2colFn>(f);
+  return RNN_OK;
+}
+
+// Row-major bf16 matrix [rows, cols] (leading dimension ld elements); box = {64 cols, box_rows}.
+int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols, long long ld, int box_rows) {
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstr[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {64u, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1u, 1u};
+  RNN_REQUIRE((ld * 2) % 16 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15u) == 0, RNN_ERR_ALIGN);
+  CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box,
+                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RNN_REQUIRE(r == CUDA_SUCCESS, RNN_ERR_TENSORMAP);
+  return RNN_OK;
+}
+
+// NHWC bf16 activation tensor seen as (C, W, H, N) for im2col-mode TMA.  Strides are explicit so
+// that callers may describe virtual (overlapping) views.
+int make_tmap_im2col(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, long long str_w,
+                     long long str_h, long long str_n, int lo_w, int lo_h, int up_w, int up_h, int ts_w, int ts_h,
+                     int pixels) {
+  cuuint64_t gdim[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t gstr[3] = {(cuuint64_t)str_w * 2, (cuuint64_t)str_h * 2, (cuuint64_t)str_n * 2};
+  int lower[2] = {lo_w, lo_h};
+  int upper[2] = {up_w, up_h};
+  cuuint32_t estr[4] = {1u, (cuuint32_t)ts_w, (cuuint32_t)ts_h, 1u};
+  RNN_REQUIRE((str_w * 2) % 16 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15u) == 0, RNN_ERR_ALIGN);
+  RNN_REQUIRE(lo_w >= -128 && lo_w <= 127 && lo_h >= -128 && lo_h <= 127, RNN_ERR_SHAPE);
+  RNN_REQUIRE(up_w >= -128 && up_w <= 127 && up_h >= -128 && up_h <= 127, RNN_ERR_SHAPE);
+  CUresult r = g_encode_im2col(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(ptr), gdim, gstr, lower,
+                               upper, 64u, (cuuint32_t)pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                               CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RNN_REQUIRE(r == CUDA_SUCCESS, RNN_ERR_TENSORMAP);
+  return RNN_OK;
+}
+
+template <int BN, int KIND, bool A_MN, bool B_MN>
+int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+  static bool attr_set = false;
+  auto kern = tc_kernel<BN, KIND, A_MN, B_MN>;
+  if (!attr_set) {
+    RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    attr_set = true;
+  }
+  const int tiles = p.n_mblk * p.n_nblk * p.splits;
+  const int grid = tiles < rnn_num_sms() ? tiles : rnn_num_sms();
+  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, p);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+template <int KIND, bool A_MN, bool B_MN>
+int launch_bn(int BN, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t s) {
+  switch (BN) {
+    case 64: return launch_inst<64, KIND, A_MN, B_MN>(ta, tb, p, s);
+    case 128: return launch_inst<128, KIND, A_MN, B_MN>(ta, tb, p, s);
+    case 256: return launch_inst<256, KIND, A_MN, B_MN>(ta, tb, p, s);
+  }
+  return RNN_ERR_SHAPE;
+}
+
+int launch_reduce(const float* ws, int splits, long long slab, int ncols, const float* shift, int relu,
+                  int accumulate, void* out, int out_f32, cudaStream_t stream) {
+  RNN_REQUIRE(slab % 4 == 0 && ncols % 4 == 0, RNN_ERR_SHAPE);
+  const long long n4 = slab / 4;
+  const int threads = 256;
+  const int blocks = ceil_div_i(n4, threads);
+  splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(ws, splits, slab, ncols, shift, relu, accumulate, out,
+                                                       out_f32);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+int pick_bn(int n) {
+  if (n % 256 == 0) return 256;
+  if (n % 128 == 0) return 128;
+  if (n > 128 && n % 64 != 0) return 128;  // ragged: fewer, wider tiles
+  return 64;
+}
+
+// Split-K policy for plain GEMMs: split only when the tile grid leaves most SMs idle.
+int gemm_splits(int M, int N, int K, int BN) {
+  const int tiles = ceil_div_i(M, BM) * ceil_div_i(N, BN);
+  const int k_iters = ceil_div_i(K, BK);
+  const int sms = rnn_num_sms();
+  if (tiles * 2 > sms || k_iters < 8) return 1;
+  int s = sms / tiles;
+  if (s > k_iters / 4) s = k_iters / 4;
+  if (s > 32) s = 32;
+  return s < 1 ? 1 : s;
+}
+
+struct WgradPlan {
+  int BN, n_mblk, ncblk, k_iters, splits;
+  size_t ws_bytes;
+};
+
+WgradPlan plan_wgrad(const rnn_conv_desc* d) {
+  WgradPlan w;
+  w.BN = (d->C % 256 == 0) ? 256 : (d->C % 128 == 0 ? 128 : 64);
+  w.n_mblk = ceil_div_i(d->K, BM);
+  w.ncblk = ceil_div_i(d->C, w.BN);
+  const long long mpix = (long long)d->N * d->P * d->Q;
+  w.k_iters = ceil_div_i(mpix, BK);
+  const int base = w.n_mblk * w.ncblk * d->R * d->S;
+  const int sms = rnn_num_sms();
+  int s = ceil_div_i(sms, base);
+  if (s > w.k_iters / 4) s = w.k_iters / 4;
+  if (s < 1) s = 1;
+  w.splits = s;
+  w.ws_bytes = (size_t)s * d->K * d->R * d->S * d->C * sizeof(float);
+  return w;
+}
+
+}  // namespace
+
+// =============================================================================================
+// C ABI
+// =============================================================================================
+extern "C" {
+
+size_t rnn_gemm_bf16_workspace(int M, int N, int K, int out_f32, int has_epilogue) {
+  const int BN = pick_bn(N);
+  const int s = gemm_splits(M, N, K, BN);
+  if (s == 1 && !(out_f32 && has_epilogue)) return 0;
+  return (size_t)s * M * N * sizeof(float);
+}
+
+int rnn_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_mn, int b_mn,
+                  const float* bias, int relu, int out_f32, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && N > 0 && K > 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(N % 8 == 0 && K % 8 == 0 && (!a_mn || M % 8 == 0), RNN_ERR_SHAPE);
+  RNN_REQUIRE(!(a_mn && !b_mn), RNN_ERR_SHAPE);  // (MN,K) combination is not instantiated
+  int rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+
+  const int BN = pick_bn(N);
+  CUtensorMap ta, tb;
+  if (!a_mn) rc = make_tmap_2d(&ta, A, M, K, K, BM);   // A[M,K], box {64 k, 128 m}
+  else       rc = make_tmap_2d(&ta, A, K, M, M, 64);   // A stored [K,M], box {64 m, 64 k}
+  if (rc != RNN_OK) return rc;
+  if (!b_mn) rc = make_tmap_2d(&tb, B, N, K, K, BN);   // B[N,K], box {64 k, BN n}
+  else       rc = make_tmap_2d(&tb, B, K, N, N, 64);   // B stored [K,N], box {64 n, 64 k}
+  if (rc != RNN_OK) return rc;
+
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = M; p.N = N;
+  p.k_iters = ceil_div_i(K, BK);
+  p.splits = gemm_splits(M, N, K, BN);
+  p.n_mblk = ceil_div_i(M, BM);
+  p.n_nblk = ceil_div_i(N, BN);
+  p.ldd = N;
+  p.ldw = N;
+  const bool has_epi = (bias != nullptr) || relu;
+  const bool via_ws = p.splits > 1 || (out_f32 && has_epi);
+  if (via_ws) {
+    const size_t need = (size_t)p.splits * M * N * sizeof(float);
+    RNN_REQUIRE(ws != nullptr && ws_bytes >= need, RNN_ERR_WORKSPACE);
+    p.ws = reinterpret_cast<float*>(ws);
+  } else if (out_f32) {
+    p.ws = reinterpret_cast<float*>(D);
+  } else {
+    p.D = D;
+    p.shift = bias;
+    p.relu = relu;
+  }
+  if (!a_mn && !b_mn) rc = launch_bn<KIND_GEMM, false, false>(BN, ta, tb, p, stream);
+  else if (!a_mn && b_mn) rc = launch_bn<KIND_GEMM, false, true>(BN, ta, tb, p, stream);
+  else rc = launch_bn<KIND_GEMM, true, true>(BN, ta, tb, p, stream);
+  if (rc != RNN_OK) return rc;
+  if (via_ws) {
+    rc = launch_reduce(p.ws, p.splits, (long long)M * N, N, bias, relu, 0, D, out_f32, stream);
+  }
+  return rc;
+}
+
+static int check_conv_desc(const rnn_conv_desc* d) {
+  RNN_REQUIRE(d != nullptr, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->C > 0 && d->K > 0 && d->R > 0 && d->S > 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->stride_h > 0 && d->stride_w > 0 && d->pad_h >= 0 && d->pad_w >= 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->P == (d->H + 2 * d->pad_h - d->R) / d->stride_h + 1, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->Q == (d->W + 2 * d->pad_w - d->S) / d->stride_w + 1, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->C % 64 == 0, RNN_ERR_SHAPE);  // one 128-byte swizzle row of channels per K step
+  RNN_REQUIRE(d->K % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->R * d->S <= MAX_TAPS, RNN_ERR_SHAPE);
+  return RNN_OK;
+}
+
+// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); optional per-channel scale/shift, residual add, ReLU.
+int rnn_conv2d_fprop_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
+                          const float* shift, const void* residual, int relu, cudaStream_t stream) {
+  int rc = check_conv_desc(d);
+  if (rc != RNN_OK) return rc;
+  rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const int BN = pick_bn(d->K);
+  CUtensorMap ta, tb;
+  rc = make_tmap_im2col(&ta, x, d->C, d->W, d->H, d->N, d->C, (long long)d->W * d->C,
+                        (long long)d->H * d->W * d->C, -d->pad_w, -d->pad_h, d->pad_w - (d->S - 1),
+                        d->pad_h - (d->R - 1), d->stride_w, d->stride_h, BM);
+  if (rc != RNN_OK) return rc;
+  const long long rsc = (long long)d->R * d->S * d->C;
+  rc = make_tmap_2d(&tb, w, d->K, rsc, rsc, BN);
+  if (rc != RNN_OK) return rc;
+
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  const long long M = (long long)d->N * d->P * d->Q;
+  RNN_REQUIRE(M < (1ll << 31), RNN_ERR_SHAPE);
+  p.M = (int)M; p.N = d->K;
+  p.cchunks = d->C / 64;
+  p.ntaps = d->R * d->S;
+  p.k_iters = p.ntaps * p.cchunks;
+  p.splits = 1;
+  p.n_mblk = ceil_div_i(M, BM);
+  p.n_nblk = ceil_div_i(d->K, BN);
+  p.Wo = d->Q; p.HoWo = d->P * d->Q;
+  p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
+  p.ldd = d->K;
+  p.D = y; p.scale = scale; p.shift = shift; p.residual = reinterpret_cast<const bf16*>(residual); p.relu = relu;
+  for (int r = 0; r < d->R; ++r)
+    for (int s = 0; s < d->S; ++s) {
+      TapDesc& t = p.taps[r * d->S + s];
+      t.ow = (int16_t)s; t.oh = (int16_t)r; t.bcol = (r * d->S + s) * d->C;
+    }
+  return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);
+}
+
+// dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w[K,R,S,C]).  Strided convolutions are decomposed
+// into stride_h*stride_w parity classes, each a unit-stride gather over dy with a subset of taps.
+// `accumulate` != 0 adds into the existing dx (gradient of a tensor consumed by two branches).
+int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
+                          cudaStream_t stream) {
+  int rc = check_conv_desc(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(d->K % 64 == 0 && d->C % 8 == 0, RNN_ERR_SHAPE);
+  rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const int BN = pick_bn(d->C);
+  const long long rsc = (long long)d->R * d->S * d->C;
+  CUtensorMap tb;
+  rc = make_tmap_2d(&tb, w, d->K, rsc, rsc, 64);  // MN-major B: box {64 c, 64 k}
+  if (rc != RNN_OK) return rc;
+
+  // Classes with no contributing tap leave their dx pixels untouched: zero them first.
+  const bool has_empty = (d->R < d->stride_h) || (d->S < d->stride_w);
+  if (has_empty && !accumulate) {
+    RNN_CUDA(cudaMemsetAsync(dx, 0, (size_t)d->N * d->H * d->W * d->C * 2, stream));
+  }
+
+  for (int a = 0; a < d->stride_h; ++a) {
+    for (int b = 0; b < d->stride_w; ++b) {
+      const int Hc = (d->H - a + d->stride_h - 1) / d->stride_h;
+      const int Wc = (d->W - b + d->stride_w - 1) / d->stride_w;
+      if (Hc <= 0 || Wc <= 0) continue;
+      // taps: r with (a + pad - r) % stride == 0; dy row = i + (a + pad - r) / stride
+      int offh[MAX_TAPS], rr[MAX_TAPS], nh = 0, offw[MAX_TAPS], ss[MAX_TAPS], nw = 0;
+      for (int r = 0; r < d->R; ++r) {
+        const int t = a + d->pad_h - r;
+        if (((t % d->stride_h) + d->stride_h) % d->stride_h != 0) continue;
+        offh[nh] = (t >= 0) ? t / d->stride_h : -((-t) / d->stride_h);
+        rr[nh++] = r;
+      }
+      for (int s = 0; s < d->S; ++s) {
+        const int t = b + d->pad_w - s;
+        if (((t % d->stride_w) + d->stride_w) % d->stride_w != 0) continue;
+        offw[nw] = (t >= 0) ? t / d->stride_w : -((-t) / d->stride_w);
+        ss[nw++] = s;
+      }
+      if (nh == 0 || nw == 0) continue;
+      int lo_h = offh[0], lo_w = offw[0];
+      for (int i = 1; i < nh; ++i) lo_h = offh[i] < lo_h ? offh[i] : lo_h;
+      for (int i = 1; i < nw; ++i) lo_w = offw[i] < lo_w ? offw[i] : lo_w;
+      const int up_h = Hc - d->P + lo_h, up_w = Wc - d->Q + lo_w;
+
+      CUtensorMap ta;
+      rc = make_tmap_im2col(&ta, dy, d->K, d->Q, d->P, d->N, d->K, (long long)d->Q * d->K,
+                            (long long)d->P * d->Q * d->K, lo_w, lo_h, up_w, up_h, 1, 1, BM);
+      if (rc != RNN_OK) return rc;
+
+      TcParams p;
+      memset(&p, 0, sizeof(p));
+      const long long M = (long long)d->N * Hc * Wc;
+      p.M = (int)M; p.N = d->C;
+      p.cchunks = d->K / 64;
+      p.ntaps = nh * nw;
+      p.k_iters = p.ntaps * p.cchunks;
+      p.splits = 1;
+      p.n_mblk = ceil_div_i(M, BM);
+      p.n_nblk = ceil_div_i(d->C, BN);
+      p.Wo = Wc; p.HoWo = Hc * Wc;
+      p.ts_w = 1; p.ts_h = 1; p.lo_w = lo_w; p.lo_h = lo_h;
+      p.ldd = d->C;
+      p.pix_map = (d->stride_h != 1 || d->stride_w != 1) ? 1 : 0;
+      p.OW = d->W; p.OHOW = d->H * d->W; p.os_h = d->stride_h; p.os_w = d->stride_w; p.oa = a; p.ob = b;
+      p.D = dx;
+      p.residual = accumulate ? reinterpret_cast<const bf16*>(dx) : nullptr;
+      for (int i = 0; i < nh; ++i)
+        for (int j = 0; j < nw; ++j) {
+          TapDesc& t = p.taps[i * nw + j];
+          t.oh = (int16_t)(offh[i] - lo_h); t.ow = (int16_t)(offw[j] - lo_w);
+          t.bcol = (rr[i] * d->S + ss[j]) * d->C;
+        }
+      rc = launch_bn<KIND_CONV, false, true>(BN, ta, tb, p, stream);
+      if (rc != RNN_OK) return rc;
+    }
+  }
+  return RNN_OK;
+}
+
+size_t rnn_conv2d_wgrad_workspace(const rnn_conv_desc* d) {
+  if (check_conv_desc(d) != RNN_OK) return 0;
+  return plan_wgrad(d).ws_bytes;
+}
+
+// dw[K,R,S,C] = sum over pixels of dy[.,k] * x_im2col[., (r,s,c)].  Split over the pixel range;
+// fp32 partials live in `ws` and are summed in a fixed order (bitwise run-to-run reproducible).
+int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy, void* dw, int dw_f32,
+                          int accumulate, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  int rc = check_conv_desc(d);
+  if (rc != RNN_OK) return rc;
+  rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const WgradPlan w = plan_wgrad(d);
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= w.ws_bytes, RNN_ERR_WORKSPACE);
+  const long long mpix = (long long)d->N * d->P * d->Q;
+  RNN_REQUIRE(mpix < (1ll << 31), RNN_ERR_SHAPE);
+  CUtensorMap ta, tb;
+  rc = make_tmap_2d(&ta, dy, mpix, d->K, d->K, 64);  // MN-major A: box {64 k_out, 64 pixels}
+  if (rc != RNN_OK) return rc;
+  rc = make_tmap_im2col(&tb, x, d->C, d->W, d->H, d->N, d->C, (long long)d->W * d->C,
+                        (long long)d->H * d->W * d->C, -d->pad_w, -d->pad_h, d->pad_w - (d->S - 1),
+                        d->pad_h - (d->R - 1), d->stride_w, d->stride_h, 64);
+  if (rc != RNN_OK) return rc;
+
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = d->K; p.N = d->C;
+  p.k_iters = w.k_iters;
+  p.splits = w.splits;
+  p.ntaps = d->R * d->S;
+  p.ncblk = w.ncblk; p.tapC = d->C;
+  p.n_mblk = w.n_mblk;
+  p.n_nblk = p.ntaps * w.ncblk;
+  p.Wo = d->Q; p.HoWo = d->P * d->Q;
+  p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
+  p.ws = reinterpret_cast<float*>(ws);
+  p.ldw = (long long)d->R * d->S * d->C;
+  for (int r = 0; r < d->R; ++r)
+    for (int s = 0; s < d->S; ++s) {
+      TapDesc& t = p.taps[r * d->S + s];
+      t.ow = (int16_t)s; t.oh = (int16_t)r; t.bcol = (r * d->S + s) * d->C;
+    }
+  rc = launch_bn<KIND_WGRAD, true, true>(w.BN, ta, tb, p, stream);
+  if (rc != RNN_OK) return rc;
+  return launch_reduce(p.ws, p.splits, (long long)d->K * p.ldw, (int)p.ldw, nullptr, 0, accumulate, dw, dw_f32,
+                       stream);
+}
+
+}  // extern "C"
