@@ -75,6 +75,107 @@ size_t rnn_conv2d_wgrad_workspace(const rnn_conv_desc* d);
 int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy, void* dw, int dw_f32,
                           int accumulate, void* ws, size_t ws_bytes, cudaStream_t stream);
 
+/* ---- fp32 CUDA-core path (LeNet-5 class networks; BASELINE.json configs[0]) -------------------- */
+/* torch.nn.Conv2d (fp32, NHWC / KRSC) forward incl. bias, and autograd dgrad / wgrad. */
+int rnn_conv2d_fprop_f32(const rnn_conv_desc* d, const float* x, const float* w, const float* bias, float* y,
+                         cudaStream_t stream);
+int rnn_conv2d_dgrad_f32(const rnn_conv_desc* d, const float* dy, const float* w, float* dx, cudaStream_t stream);
+int rnn_conv2d_wgrad_f32(const rnn_conv_desc* d, const float* x, const float* dy, float* dw, int accumulate,
+                         cudaStream_t stream);
+/* fp32 counterpart of rnn_gemm_bf16 (same a_mn / b_mn meaning); nn.Linear in fp32 models. */
+int rnn_gemm_f32(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
+                 const float* bias, int relu, int accumulate, cudaStream_t stream);
+/* out[c] (+)= sum_r x[r,c] -- bias gradient of nn.Linear / nn.Conv2d (autograd of attention.py:85,
+ * transformer.py:24-25). */
+size_t rnn_colsum_workspace(long long M, int C);
+int rnn_colsum(const void* x, long long M, int C, void* out, int accumulate, int is_f32, void* ws, size_t ws_bytes,
+               cudaStream_t stream);
+
+/* ---- elementwise (HBM-bound) -------------------------------------------------------------------- */
+/* Input pipeline: NCHW fp32 -> NHWC bf16 with the channel dimension zero-padded to Cpad. */
+int rnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, cudaStream_t stream);
+int rnn_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int H, int W, int Cpad, cudaStream_t stream);
+/* F.relu (arch/transformer.py:30) and its autograd: dx = dy * (y > 0). */
+int rnn_relu_fwd(const void* x, void* y, long long n, int is_f32, cudaStream_t stream);
+int rnn_relu_bwd(const void* dy, const void* y, void* dx, long long n, int is_f32, cudaStream_t stream);
+/* tanh activation of the classic LeNet-5 (fp32 only). */
+int rnn_tanh_fwd_f32(const float* x, float* y, long long n, cudaStream_t stream);
+int rnn_tanh_bwd_f32(const float* dy, const float* y, float* dx, long long n, cudaStream_t stream);
+/* residual add x + sublayer(x) (arch/transformer.py:111-112) when it is not fused into a norm kernel. */
+int rnn_add_bf16(const void* a, const void* b, void* y, long long n, cudaStream_t stream);
+int rnn_cast_f32_to_bf16(const float* x, void* y, long long n, cudaStream_t stream);
+int rnn_cast_bf16_to_f32(const void* x, float* y, long long n, cudaStream_t stream);
+/* nn.Dropout (nn/attention.py:26,46,86 ; arch/transformer.py:26,32): Philox counter RNG keyed by
+ * (seed, offset); mask holds one keep-byte per element for the backward pass. */
+int rnn_dropout_fwd(const void* x, void* y, uint8_t* mask, long long n, float p, unsigned long long seed,
+                    unsigned long long offset, int is_f32, cudaStream_t stream);
+int rnn_dropout_bwd(const void* dy, const uint8_t* mask, void* dx, long long n, float p, int is_f32,
+                    cudaStream_t stream);
+
+/* ---- normalisation ------------------------------------------------------------------------------- */
+/* torch.nn.BatchNorm2d, training mode, over x[M = N*H*W, C] bf16: batch statistics (biased variance for
+ * normalisation, unbiased for running_var), scale = gamma*invstd, shift = beta - mean*scale. */
+size_t rnn_bn_workspace(long long M, int C);
+int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, const float* beta, float eps,
+                      float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                      float* scale, float* shift, void* ws, size_t ws_bytes, cudaStream_t stream);
+int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                        float eps, int C, float* scale, float* shift, cudaStream_t stream);
+/* y = relu(x*scale + shift + residual): fused BatchNorm-apply (+ residual add) (+ ReLU). */
+int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, const void* residual, int relu, void* y,
+                      long long M, int C, cudaStream_t stream);
+/* Backward of the fused op above.  y_out (nullable) is the forward output, used as the ReLU mask; dres
+ * (nullable) receives the gradient of the residual branch.  dgamma/dbeta are fp32 or bf16. */
+int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out, const float* mean, const float* invstd,
+                    const float* gamma, long long M, int C, void* dx, void* dres, void* dgamma, void* dbeta,
+                    int grads_f32, int accumulate_grads, float* sum_dy, float* sum_dy_xhat, void* ws, size_t ws_bytes,
+                    cudaStream_t stream);
+/* nn.LayerNorm(E) over y = LN(x + residual) (arch/transformer.py:65,72,111-112,188); xsum (nullable)
+ * receives x + residual for the backward pass; mean / rstd are per-row fp32. */
+int rnn_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, float eps, void* y,
+                      void* xsum, float* mean, float* rstd, long long M, int E, int is_f32, cudaStream_t stream);
+size_t rnn_layernorm_bwd_workspace(long long M, int E);
+int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const float* mean, const float* rstd,
+                      void* dx, void* dgamma, void* dbeta, int accumulate_grads, long long M, int E, int is_f32,
+                      void* ws, size_t ws_bytes, cudaStream_t stream);
+
+/* ---- pooling (NHWC) ------------------------------------------------------------------------------ */
+/* torch.nn.MaxPool2d(return_indices=True): indices are h*W+w inside the input plane (int32), first
+ * maximum in window order, NaN propagates -- bit-exact with ATen. */
+int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, int N, int H, int W, int C, int R, int S, int sh, int sw,
+                      int ph, int pw, int is_f32, cudaStream_t stream);
+int rnn_maxpool2d_bwd(const void* dy, const int* indices, void* dx, int N, int H, int W, int C, int R, int S, int sh,
+                      int sw, int ph, int pw, int is_f32, cudaStream_t stream);
+/* torch.nn.AvgPool2d (count_include_pad=True, ceil_mode=False). */
+int rnn_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
+                      int is_f32, cudaStream_t stream);
+int rnn_avgpool2d_bwd(const void* dy, void* dx, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
+                      int is_f32, cudaStream_t stream);
+/* torch.nn.AdaptiveAvgPool2d((1,1)). */
+int rnn_global_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int is_f32, cudaStream_t stream);
+int rnn_global_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, int is_f32, cudaStream_t stream);
+
+/* ---- softmax / loss ------------------------------------------------------------------------------ */
+/* F.softmax(w, dim=-1) (nn/attention.py:45) and its autograd. */
+int rnn_softmax_fwd(const void* x, void* y, long long rows, int cols, int is_f32, cudaStream_t stream);
+int rnn_softmax_bwd(const void* dy, const void* y, void* dx, long long rows, int cols, int is_f32,
+                    cudaStream_t stream);
+/* F.cross_entropy(logits, target) (mean) + dlogits = (softmax - onehot)*grad_scale in one pass. */
+int rnn_softmax_ce(const void* logits, const long long* target, long long rows, int cols, float grad_scale,
+                   float* row_loss, float* loss, void* dlogits, int is_f32, cudaStream_t stream);
+/* torch.argmax(x, dim=-1): first maximum wins. */
+int rnn_argmax(const void* x, long long* out, long long rows, int cols, int is_f32, cudaStream_t stream);
+
+/* ---- fused optimizers over flat buckets ---------------------------------------------------------- */
+/* torch.optim.SGD (momentum, dampening, nesterov, weight_decay) on an fp32 master copy. */
+int rnn_sgd_step(float* w, float* buf, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16, long long n,
+                 float lr, float momentum, float dampening, float weight_decay, int nesterov, int first_step,
+                 float grad_scale, cudaStream_t stream);
+/* torch.optim.AdamW (amsgrad=False). */
+int rnn_adamw_step(float* w, float* m, float* v, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16,
+                   long long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
+                   float grad_scale, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -32,21 +32,47 @@ def conv_desc(N, H, W, Cin, K, R, S, stride, pad) -> ConvDesc:
     return ConvDesc(N, H, W, Cin, K, R, S, sh, sw, ph, pw, P, Q)
 
 
-_vp, _i, _f, _sz, _ll = C.c_void_p, C.c_int, C.c_float, C.c_size_t, C.c_longlong
-_cdp = C.POINTER(ConvDesc)
+HEADER_PATH = _PKG.parent / "include" / "rnn_b200.h"
+_HEADER_FALLBACK = _PKG / "_lib" / "rnn_b200.h"  # copy placed next to the .so by the build
 
-# name -> (restype, argtypes).  Kept in one table so tests can check it against include/rnn_b200.h.
-SIGNATURES = {
-    "rnn_last_error": (C.c_char_p, []),
-    "rnn_version": (_i, []),
-    "rnn_sm_count": (_i, []),
-    "rnn_gemm_bf16_workspace": (_sz, [_i, _i, _i, _i, _i]),
-    "rnn_gemm_bf16": (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _vp, _i, _i, _vp, _sz, _vp]),
-    "rnn_conv2d_fprop_bf16": (_i, [_cdp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _vp]),
-    "rnn_conv2d_dgrad_bf16": (_i, [_cdp, _vp, _vp, _vp, _i, _vp]),
-    "rnn_conv2d_wgrad_workspace": (_sz, [_cdp]),
-    "rnn_conv2d_wgrad_bf16": (_i, [_cdp, _vp, _vp, _vp, _i, _i, _vp, _sz, _vp]),
-}
+
+def _ctype(decl: str):
+    d = " ".join(decl.replace("*", " * ").split())
+    if "*" in d:
+        if "rnn_conv_desc" in d:
+            return C.POINTER(ConvDesc)
+        if d.startswith("const char"):
+            return C.c_char_p
+        return C.c_void_p
+    base = d.rsplit(" ", 1)[0] if " " in d else d  # drop the parameter name
+    base = base.replace("const ", "").strip()
+    table = {
+        "cudaStream_t": C.c_void_p, "int": C.c_int, "float": C.c_float, "size_t": C.c_size_t,
+        "long long": C.c_longlong, "unsigned long long": C.c_ulonglong, "void": None,
+    }
+    if base not in table:
+        raise RnnError(f"rnn_b200.h: unknown parameter type in '{decl}'")
+    return table[base]
+
+
+def parse_header(path: os.PathLike | None = None) -> dict:
+    """Parse include/rnn_b200.h into {name: (restype, [argtypes])}: the header is the single source of
+    truth for the binding, so the ctypes signatures cannot drift from the C ABI."""
+    import re
+    hp = Path(path) if path else (HEADER_PATH if HEADER_PATH.exists() else _HEADER_FALLBACK)
+    text = hp.read_text()
+    text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
+    text = re.sub(r"//[^\n]*", " ", text)
+    sigs = {}
+    for m in re.finditer(r"(const char\s*\*|size_t|int)\s+(rnn_\w+)\s*\(([^;{}]*?)\)\s*;", text, flags=re.S):
+        ret, name, args = m.group(1), m.group(2), m.group(3).strip()
+        restype = C.c_char_p if "char" in ret else (C.c_size_t if ret == "size_t" else C.c_int)
+        argtypes = [] if args in ("", "void") else [_ctype(a.strip()) for a in args.split(",")]
+        sigs[name] = (restype, argtypes)
+    return sigs
+
+
+SIGNATURES = parse_header()
 
 
 def load(path: os.PathLike | None = None):

@@ -1,0 +1,481 @@
+// Normalisation kernels (HBM-bound; 128-bit accesses, warp-shuffle / shared-memory reductions).
+//
+// BatchNorm2d over NHWC bf16 (torch.nn.BatchNorm2d semantics, training mode):
+//   stats   : per-channel sum / sum of squares  -> partials in workspace -> finalize (mean, invstd,
+//             scale = gamma*invstd, shift = beta - mean*scale, running stats with unbiased variance)
+//   apply   : y = relu(x*scale + shift + residual)            (fused BN-apply + add + ReLU)
+//   backward: reduce  (sum dy', sum dy'*xhat with dy' = dy * [y > 0])  -> partials -> finalize
+//             apply   dx = scale * (dy' - sum_dy/M - xhat * sum_dy_xhat/M) ; dres = dy'
+//
+// LayerNorm over the last dimension (reference: nn.LayerNorm at arch/transformer.py:65,72,188 with
+// the residual add of :111-112,115-116,149-150,198-200 fused in): one warp per row.
+#include "common.cuh"
+
+namespace {
+
+// --------------------------------------------------------------------------------- BatchNorm
+// Thread layout for an [M, C] bf16 matrix: each thread owns one 8-channel vector column (cg) and
+// walks rows r0, r0 + rows_per_pass, ...   blockDim.x = 256; cgs = C/8 column groups.
+struct ColMap {
+  int cgs, rows_per_blk_pass;
+};
+
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
+                 const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
+                 float* __restrict__ partials /* [gridDim.y][2][C] */) {
+  // grid.x tiles the column groups (when C/8 > 256), grid.y tiles rows.
+  const int cgs = C >> 3;
+  const int tpr = cgs < 256 ? cgs : 256;          // threads per row
+  const int rpp = 256 / tpr;                      // rows per pass
+  const int cg = blockIdx.x * tpr + (threadIdx.x % tpr);
+  const int rlocal = threadIdx.x / tpr;
+  float s0[8], s1[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) s0[e] = s1[e] = 0.f;
+  float mu[8], is[8];
+  if (BWD && cg < cgs) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { mu[e] = mean[cg * 8 + e]; is[e] = invstd[cg * 8 + e]; }
+  }
+  if (cg < cgs && rlocal < rpp) {
+    for (long long r = (long long)blockIdx.y * rpp + rlocal; r < M; r += (long long)gridDim.y * rpp) {
+      const long long off = r * C + cg * 8;
+      float v[8];
+      unpack8(ld_stream(x + off), v);
+      if (!BWD) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { s0[e] += v[e]; s1[e] += v[e] * v[e]; }
+      } else {
+        float g[8];
+        unpack8(ld_stream(dy + off), g);
+        if (yout) {
+          float o[8];
+          unpack8(ld_stream(yout + off), o);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { s0[e] += g[e]; s1[e] += g[e] * (v[e] - mu[e]) * is[e]; }
+      }
+    }
+  }
+  // combine the rpp row-lanes of each column group through shared memory
+  __shared__ float sm[256 * 16];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { sm[threadIdx.x * 16 + e] = s0[e]; sm[threadIdx.x * 16 + 8 + e] = s1[e]; }
+  __syncthreads();
+  if (rlocal == 0 && cg < cgs) {
+    for (int rr = 1; rr < rpp; ++rr) {
+      const int t = rr * tpr + (threadIdx.x % tpr);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { s0[e] += sm[t * 16 + e]; s1[e] += sm[t * 16 + 8 + e]; }
+    }
+    float* p = partials + (long long)blockIdx.y * 2 * C;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) { p[cg * 8 + e] = s0[e]; p[C + cg * 8 + e] = s1[e]; }
+  }
+}
+
+__global__ void bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, float count,
+                                         const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                                         float momentum, float* running_mean, float* running_var,
+                                         float* __restrict__ mean, float* __restrict__ invstd,
+                                         float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f, ss = 0.f;
+  for (int p = 0; p < nparts; ++p) { s += partials[(long long)p * 2 * C + c]; ss += partials[(long long)p * 2 * C + C + c]; }
+  const float m = s / count;
+  float var = ss / count - m * m;
+  var = var < 0.f ? 0.f : var;
+  const float is = rsqrtf(var + eps);
+  mean[c] = m;
+  invstd[c] = is;
+  const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+  scale[c] = g * is;
+  shift[c] = b - m * g * is;
+  if (running_mean) {
+    const float unb = count > 1.f ? var * count / (count - 1.f) : var;
+    running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * m;
+    running_var[c] = (1.f - momentum) * running_var[c] + momentum * unb;
+  }
+}
+
+// eval mode: scale/shift from running statistics
+__global__ void bn_eval_prepare_kernel(const float* __restrict__ gamma, const float* __restrict__ beta,
+                                       const float* __restrict__ rm, const float* __restrict__ rv, float eps, int C,
+                                       float* __restrict__ scale, float* __restrict__ shift) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  const float is = rsqrtf(rv[c] + eps);
+  const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
+  scale[c] = g * is;
+  shift[c] = b - rm[c] * g * is;
+}
+
+__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
+                                       float* __restrict__ sum_dy, float* __restrict__ sum_dy_xhat,
+                                       void* dgamma, void* dbeta, int grads_f32, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float s = 0.f, ss = 0.f;
+  for (int p = 0; p < nparts; ++p) { s += partials[(long long)p * 2 * C + c]; ss += partials[(long long)p * 2 * C + C + c]; }
+  sum_dy[c] = s;
+  sum_dy_xhat[c] = ss;
+  if (dgamma) {
+    if (grads_f32) {
+      float* dg = (float*)dgamma; float* db = (float*)dbeta;
+      dg[c] = (accumulate ? dg[c] : 0.f) + ss;
+      db[c] = (accumulate ? db[c] : 0.f) + s;
+    } else {
+      bf16* dg = (bf16*)dgamma; bf16* db = (bf16*)dbeta;
+      dg[c] = __float2bfloat16((accumulate ? __bfloat162float(dg[c]) : 0.f) + ss);
+      db[c] = __float2bfloat16((accumulate ? __bfloat162float(db[c]) : 0.f) + s);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
+                const bf16* __restrict__ residual, int relu, bf16* __restrict__ y, long long nvec, int cgs) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    const int cg = (int)(i % cgs);
+    float v[8];
+    unpack8(ld_stream(x + i * 8), v);
+    const float4 a0 = __ldg(reinterpret_cast<const float4*>(scale + cg * 8));
+    const float4 a1 = __ldg(reinterpret_cast<const float4*>(scale + cg * 8 + 4));
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(shift + cg * 8));
+    const float4 b1 = __ldg(reinterpret_cast<const float4*>(shift + cg * 8 + 4));
+    v[0] = v[0] * a0.x + b0.x; v[1] = v[1] * a0.y + b0.y; v[2] = v[2] * a0.z + b0.z; v[3] = v[3] * a0.w + b0.w;
+    v[4] = v[4] * a1.x + b1.x; v[5] = v[5] * a1.y + b1.y; v[6] = v[6] * a1.z + b1.z; v[7] = v[7] * a1.w + b1.w;
+    if (residual) {
+      float r[8];
+      unpack8(ld_stream(residual + i * 8), r);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] += r[e];
+    }
+    if (relu) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+    }
+    st_stream(y + i * 8, pack8(v));
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
+                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
+                    const float* __restrict__ sum_dy, const float* __restrict__ sum_dy_xhat, float inv_count,
+                    bf16* __restrict__ dx, bf16* __restrict__ dres, long long nvec, int cgs) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % cgs) * 8;
+    float g[8], v[8];
+    unpack8(ld_stream(dy + i * 8), g);
+    unpack8(ld_stream(x + i * 8), v);
+    if (yout) {
+      float o[8];
+      unpack8(ld_stream(yout + i * 8), o);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
+    }
+    if (dres) st_stream(dres + i * 8, pack8(g));
+    float r[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int c = c0 + e;
+      const float is = __ldg(invstd + c);
+      const float xhat = (v[e] - __ldg(mean + c)) * is;
+      const float gm = gamma ? __ldg(gamma + c) : 1.f;
+      r[e] = gm * is * (g[e] - __ldg(sum_dy + c) * inv_count - xhat * __ldg(sum_dy_xhat + c) * inv_count);
+    }
+    st_stream(dx + i * 8, pack8(r));
+  }
+}
+
+int bn_row_blocks(long long M, int C) {
+  const int cgs = C >> 3;
+  const int tpr = cgs < 256 ? cgs : 256;
+  const int rpp = 256 / tpr;
+  const int gx = (cgs + tpr - 1) / tpr;
+  long long gy = (M + rpp - 1) / rpp;
+  // enough rows per block to amortise the tail reduction; cap the grid at ~8 blocks per SM
+  long long cap = (long long)rnn_num_sms() * 8 / gx;
+  if (cap < 1) cap = 1;
+  if (gy > cap) gy = cap;
+  return (int)gy;
+}
+
+// --------------------------------------------------------------------------------- LayerNorm
+// One warp per row; E % 8 == 0 (bf16) / E % 4 == 0 (fp32).  y = LN(x + res) * gamma + beta.
+template <typename T>
+struct Vec;
+template <>
+struct Vec<bf16> {
+  static constexpr int W = 8;
+  __device__ static void load(const bf16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
+  __device__ static void store(bf16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
+};
+template <>
+struct Vec<float> {
+  static constexpr int W = 4;
+  __device__ static void load(const float* p, float* f) {
+    const float4 v = *reinterpret_cast<const float4*>(p);
+    f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+  }
+  __device__ static void store(float* p, const float* f) {
+    *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+  }
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, const T* __restrict__ gamma,
+                     const T* __restrict__ beta, float eps, T* __restrict__ y, T* __restrict__ xsum,
+                     float* __restrict__ mean, float* __restrict__ rstd, long long M, int E) {
+  constexpr int W = Vec<T>::W;
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= M) return;
+  const T* xr = x + row * E;
+  const T* rr = res ? res + row * E : nullptr;
+  // pass 1: sum (and keep x+res if requested so the backward pass can reread it)
+  float s = 0.f;
+  for (int c = lane * W; c < E; c += 32 * W) {
+    float v[W];
+    Vec<T>::load(xr + c, v);
+    if (rr) {
+      float r[W];
+      Vec<T>::load(rr + c, r);
+#pragma unroll
+      for (int e = 0; e < W; ++e) v[e] += r[e];
+      if (xsum) {
+        Vec<T>::store(xsum + row * E + c, v);
+      }
+    }
+#pragma unroll
+    for (int e = 0; e < W; ++e) s += v[e];
+  }
+  s = warp_sum(s);
+  const float mu = s / E;
+  // pass 2: variance about the mean (two-pass, as torch does)
+  const T* src = (rr && xsum) ? xsum + row * E : xr;
+  const bool readd = rr && !xsum;
+  float q = 0.f;
+  for (int c = lane * W; c < E; c += 32 * W) {
+    float v[W];
+    Vec<T>::load(src + c, v);
+    if (readd) {
+      float r[W];
+      Vec<T>::load(rr + c, r);
+#pragma unroll
+      for (int e = 0; e < W; ++e) v[e] += r[e];
+    }
+#pragma unroll
+    for (int e = 0; e < W; ++e) { const float d = v[e] - mu; q += d * d; }
+  }
+  q = warp_sum(q);
+  const float rs = rsqrtf(q / E + eps);
+  if (lane == 0) { mean[row] = mu; rstd[row] = rs; }
+  for (int c = lane * W; c < E; c += 32 * W) {
+    float v[W], g[W], b[W];
+    Vec<T>::load(src + c, v);
+    if (readd) {
+      float r[W];
+      Vec<T>::load(rr + c, r);
+#pragma unroll
+      for (int e = 0; e < W; ++e) v[e] += r[e];
+    }
+    Vec<T>::load(gamma + c, g);
+    Vec<T>::load(beta + c, b);
+#pragma unroll
+    for (int e = 0; e < W; ++e) v[e] = (v[e] - mu) * rs * g[e] + b[e];
+    Vec<T>::store(y + row * E + c, v);
+  }
+}
+
+// dx = rstd * (g - mean(g) - xhat*mean(g*xhat)), g = dy*gamma.  Per-block partial dgamma/dbeta rows are
+// written to `partials` [gridDim.x][2][E] and summed by layernorm_bwd_finalize_kernel.
+template <typename T>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ xin, const T* __restrict__ gamma,
+                     const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
+                     float* __restrict__ partials, long long M, int E) {
+  constexpr int W = Vec<T>::W;
+  extern __shared__ float acc[];  // [2][E] block accumulators
+  for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) acc[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  for (long long row = (long long)blockIdx.x * nw + wid; row < M; row += (long long)gridDim.x * nw) {
+    const float mu = mean[row], rs = rstd[row];
+    float sg = 0.f, sgx = 0.f;
+    for (int c = lane * W; c < E; c += 32 * W) {
+      float d[W], v[W], g[W];
+      Vec<T>::load(dy + row * E + c, d);
+      Vec<T>::load(xin + row * E + c, v);
+      Vec<T>::load(gamma + c, g);
+#pragma unroll
+      for (int e = 0; e < W; ++e) {
+        const float xh = (v[e] - mu) * rs;
+        const float gg = d[e] * g[e];
+        sg += gg;
+        sgx += gg * xh;
+        atomicAdd(&acc[c + e], d[e] * xh);
+        atomicAdd(&acc[E + c + e], d[e]);
+      }
+    }
+    sg = warp_sum(sg) / E;
+    sgx = warp_sum(sgx) / E;
+    for (int c = lane * W; c < E; c += 32 * W) {
+      float d[W], v[W], g[W], o[W];
+      Vec<T>::load(dy + row * E + c, d);
+      Vec<T>::load(xin + row * E + c, v);
+      Vec<T>::load(gamma + c, g);
+#pragma unroll
+      for (int e = 0; e < W; ++e) {
+        const float xh = (v[e] - mu) * rs;
+        o[e] = rs * (d[e] * g[e] - sg - xh * sgx);
+      }
+      Vec<T>::store(dx + row * E + c, o);
+    }
+  }
+  __syncthreads();
+  float* p = partials + (long long)blockIdx.x * 2 * E;
+  for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) p[i] = acc[i];
+}
+
+template <typename T>
+__global__ void layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int E, T* dgamma,
+                                              T* dbeta, int accumulate) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= E) return;
+  float a = 0.f, b = 0.f;
+  for (int p = 0; p < nparts; ++p) { a += partials[(long long)p * 2 * E + c]; b += partials[(long long)p * 2 * E + E + c]; }
+  if (accumulate) { a += (float)dgamma[c]; b += (float)dbeta[c]; }
+  dgamma[c] = (T)a;
+  dbeta[c] = (T)b;
+}
+
+int ln_bwd_blocks(long long M) {
+  long long b = (M + 7) / 8;
+  const long long cap = (long long)rnn_num_sms() * 2;
+  return (int)(b > cap ? cap : (b < 1 ? 1 : b));
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t rnn_bn_workspace(long long M, int C) { return (size_t)bn_row_blocks(M, C) * 2 * C * sizeof(float); }
+
+int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, const float* beta, float eps,
+                      float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                      float* scale, float* shift, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
+  const int gy = bn_row_blocks(M, C);
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)gy * 2 * C * sizeof(float), RNN_ERR_WORKSPACE);
+  const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
+  bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
+                                                           (float*)ws);
+  RNN_CHECK_LAUNCH();
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
+                                                                   momentum, running_mean, running_var, mean, invstd,
+                                                                   scale, shift);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
+                        float eps, int C, float* scale, float* shift, cudaStream_t stream) {
+  RNN_REQUIRE(C > 0, RNN_ERR_SHAPE);
+  bn_eval_prepare_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>(gamma, beta, running_mean, running_var, eps, C, scale,
+                                                                 shift);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, const void* residual, int relu, void* y,
+                      long long M, int C, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
+  const long long nvec = M * (C / 8);
+  long long blocks = (nvec + 255) / 256;
+  const long long cap = (long long)rnn_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  bn_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)x, scale, shift, (const bf16*)residual, relu, (bf16*)y,
+                                                   nvec, C / 8);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable: ReLU output */, const float* mean,
+                    const float* invstd, const float* gamma, long long M, int C, void* dx,
+                    void* dres /* nullable */, void* dgamma, void* dbeta, int grads_f32, int accumulate_grads,
+                    float* sum_dy, float* sum_dy_xhat, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
+  const int gy = bn_row_blocks(M, C);
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)gy * 2 * C * sizeof(float), RNN_ERR_WORKSPACE);
+  const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
+  bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
+                                                          invstd, M, C, (float*)ws);
+  RNN_CHECK_LAUNCH();
+  bn_bwd_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
+                                                                 dbeta, grads_f32, accumulate_grads);
+  RNN_CHECK_LAUNCH();
+  const long long nvec = M * (C / 8);
+  long long blocks = (nvec + 255) / 256;
+  const long long cap = (long long)rnn_num_sms() * 16;
+  if (blocks > cap) blocks = cap;
+  bn_bwd_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y_out, mean, invstd,
+                                                       gamma, sum_dy, sum_dy_xhat, 1.f / (float)M, (bf16*)dx,
+                                                       (bf16*)dres, nvec, C / 8);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+int rnn_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, float eps, void* y,
+                      void* xsum, float* mean, float* rstd, long long M, int E, int is_f32, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && E > 0 && E % (is_f32 ? 4 : 8) == 0, RNN_ERR_SHAPE);
+  const int blocks = ceil_div_i(M, 8);
+  if (is_f32)
+    layernorm_fwd_kernel<float><<<blocks, 256, 0, stream>>>((const float*)x, (const float*)residual, (const float*)gamma,
+                                                            (const float*)beta, eps, (float*)y, (float*)xsum, mean, rstd,
+                                                            M, E);
+  else
+    layernorm_fwd_kernel<bf16><<<blocks, 256, 0, stream>>>((const bf16*)x, (const bf16*)residual, (const bf16*)gamma,
+                                                           (const bf16*)beta, eps, (bf16*)y, (bf16*)xsum, mean, rstd, M,
+                                                           E);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+size_t rnn_layernorm_bwd_workspace(long long M, int E) { return (size_t)ln_bwd_blocks(M) * 2 * E * sizeof(float); }
+
+int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const float* mean, const float* rstd,
+                      void* dx, void* dgamma, void* dbeta, int accumulate_grads, long long M, int E, int is_f32,
+                      void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && E > 0 && E % (is_f32 ? 4 : 8) == 0, RNN_ERR_SHAPE);
+  const int blocks = ln_bwd_blocks(M);
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)blocks * 2 * E * sizeof(float), RNN_ERR_WORKSPACE);
+  const size_t smem = (size_t)2 * E * sizeof(float);
+  RNN_REQUIRE(smem <= 48 * 1024, RNN_ERR_SHAPE);
+  if (is_f32) {
+    layernorm_bwd_kernel<float><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
+                                                               mean, rstd, (float*)dx, (float*)ws, M, E);
+    RNN_CHECK_LAUNCH();
+    layernorm_bwd_finalize_kernel<float><<<ceil_div_i(E, 128), 128, 0, stream>>>((const float*)ws, blocks, E,
+                                                                                (float*)dgamma, (float*)dbeta,
+                                                                                accumulate_grads);
+  } else {
+    layernorm_bwd_kernel<bf16><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
+                                                              mean, rstd, (bf16*)dx, (float*)ws, M, E);
+    RNN_CHECK_LAUNCH();
+    layernorm_bwd_finalize_kernel<bf16><<<ceil_div_i(E, 128), 128, 0, stream>>>((const float*)ws, blocks, E,
+                                                                               (bf16*)dgamma, (bf16*)dbeta,
+                                                                               accumulate_grads);
+  }
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+}  // extern "C"

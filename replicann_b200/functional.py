@@ -36,7 +36,8 @@ def _req(t: torch.Tensor, dtype, name: str):
 
 # ------------------------------------------------------------------------------------------- GEMM
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
-         bias: torch.Tensor | None = None, relu: bool = False, out_dtype=torch.bfloat16) -> torch.Tensor:
+         bias: torch.Tensor | None = None, relu: bool = False, out_dtype=torch.bfloat16,
+         out: torch.Tensor | None = None) -> torch.Tensor:
     """D[M,N] = op(A) . op(B)^T.  a_mn: A stored [K,M]; b_mn: B stored [K,N]."""
     lib = _lib.load()
     _req(a, torch.bfloat16, "a")
@@ -45,8 +46,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     Kb, N = (b.shape if b_mn else b.shape[::-1])
     if K != Kb:
         raise ValueError(f"reduction mismatch {K} vs {Kb}")
+    if out is not None:
+        if tuple(out.shape) != (M, N) or not out.is_contiguous():
+            raise ValueError(f"out must be a contiguous [{M},{N}] tensor")
+        out_dtype = out.dtype
     out_f32 = out_dtype == torch.float32
-    d = torch.empty((M, N), dtype=out_dtype, device=a.device)
+    d = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
     if bias is not None:
         _req(bias, torch.float32, "bias")
     nbytes = lib.rnn_gemm_bf16_workspace(M, N, K, int(out_f32), int(bias is not None or relu))
@@ -103,3 +108,361 @@ def conv2d_wgrad(x, dy, w_shape, *, stride=1, pad=0, out=None, accumulate=False,
     check(lib.rnn_conv2d_wgrad_bf16(d, ptr(x), ptr(dy), ptr(dw), int(dw.dtype == torch.float32), int(accumulate),
                                     ptr(ws), nbytes, cur_stream()), "rnn_conv2d_wgrad_bf16")
     return dw
+
+
+# =========================================================================================== helpers
+def _is_f32(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return 1
+    if t.dtype == torch.bfloat16:
+        return 0
+    raise TypeError(f"unsupported dtype {t.dtype}: kernels exist for float32 and bfloat16")
+
+
+def _cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.RnnError("replicann_b200 kernels need CUDA tensors; there is no CPU path")
+
+
+def _contig(t, name):
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+
+
+# =========================================================================================== fp32 path
+def gemm_f32(a, b, *, a_mn=False, b_mn=False, bias=None, relu=False, out=None, accumulate=False):
+    lib = _lib.load()
+    _req(a, torch.float32, "a"); _req(b, torch.float32, "b")
+    K, M = (a.shape if a_mn else a.shape[::-1])
+    Kb, N = (b.shape if b_mn else b.shape[::-1])
+    if K != Kb:
+        raise ValueError(f"reduction mismatch {K} vs {Kb}")
+    d = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=a.device)
+    check(lib.rnn_gemm_f32(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
+                           int(accumulate), cur_stream()), "rnn_gemm_f32")
+    return d
+
+
+def conv2d_fprop_f32(x, w, bias=None, *, stride=1, pad=0):
+    lib = _lib.load()
+    _req(x, torch.float32, "x"); _req(w, torch.float32, "w")
+    d = _cdesc(x.shape, w.shape, stride, pad)
+    y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.float32, device=x.device)
+    check(lib.rnn_conv2d_fprop_f32(d, ptr(x), ptr(w), ptr(bias), ptr(y), cur_stream()), "rnn_conv2d_fprop_f32")
+    return y
+
+
+def conv2d_dgrad_f32(dy, w, x_shape, *, stride=1, pad=0):
+    lib = _lib.load()
+    _req(dy, torch.float32, "dy"); _req(w, torch.float32, "w")
+    d = _cdesc(x_shape, w.shape, stride, pad)
+    dx = torch.empty(tuple(x_shape), dtype=torch.float32, device=dy.device)
+    check(lib.rnn_conv2d_dgrad_f32(d, ptr(dy), ptr(w), ptr(dx), cur_stream()), "rnn_conv2d_dgrad_f32")
+    return dx
+
+
+def conv2d_wgrad_f32(x, dy, w_shape, *, stride=1, pad=0, out=None, accumulate=False):
+    lib = _lib.load()
+    _req(x, torch.float32, "x"); _req(dy, torch.float32, "dy")
+    d = _cdesc(x.shape, w_shape, stride, pad)
+    dw = out if out is not None else torch.empty(tuple(w_shape), dtype=torch.float32, device=x.device)
+    check(lib.rnn_conv2d_wgrad_f32(d, ptr(x), ptr(dy), ptr(dw), int(accumulate), cur_stream()), "rnn_conv2d_wgrad_f32")
+    return dw
+
+
+def colsum(x2d, *, out=None, accumulate=False):
+    """out[c] (+)= sum_r x2d[r, c]; output dtype = input dtype."""
+    lib = _lib.load()
+    _cuda(x2d); _contig(x2d, "x")
+    M, Cn = x2d.shape
+    o = out if out is not None else torch.empty((Cn,), dtype=x2d.dtype, device=x2d.device)
+    nbytes = lib.rnn_colsum_workspace(M, Cn)
+    ws = workspace(nbytes, x2d.device)
+    check(lib.rnn_colsum(ptr(x2d), M, Cn, ptr(o), int(accumulate), _is_f32(x2d), ptr(ws), nbytes, cur_stream()),
+          "rnn_colsum")
+    return o
+
+
+# =========================================================================================== elementwise
+def nchw_to_nhwc_bf16(x, cpad=None):
+    lib = _lib.load()
+    _req(x, torch.float32, "x")
+    N, Cn, H, W = x.shape
+    cp = cpad or Cn
+    y = torch.empty((N, H, W, cp), dtype=torch.bfloat16, device=x.device)
+    check(lib.rnn_nchw_f32_to_nhwc_bf16(ptr(x), ptr(y), N, Cn, H, W, cp, cur_stream()), "rnn_nchw_f32_to_nhwc_bf16")
+    return y
+
+
+def nhwc_bf16_to_nchw_f32(x, channels=None):
+    lib = _lib.load()
+    _req(x, torch.bfloat16, "x")
+    N, H, W, cp = x.shape
+    Cn = channels or cp
+    y = torch.empty((N, Cn, H, W), dtype=torch.float32, device=x.device)
+    check(lib.rnn_nhwc_bf16_to_nchw_f32(ptr(x), ptr(y), N, Cn, H, W, cp, cur_stream()), "rnn_nhwc_bf16_to_nchw_f32")
+    return y
+
+
+def relu_fwd(x):
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    y = torch.empty_like(x)
+    check(lib.rnn_relu_fwd(ptr(x), ptr(y), x.numel(), _is_f32(x), cur_stream()), "rnn_relu_fwd")
+    return y
+
+
+def relu_bwd(dy, y):
+    lib = _lib.load(); _cuda(dy, y)
+    dx = torch.empty_like(y)
+    check(lib.rnn_relu_bwd(ptr(dy), ptr(y), ptr(dx), y.numel(), _is_f32(y), cur_stream()), "rnn_relu_bwd")
+    return dx
+
+
+def tanh_fwd(x):
+    lib = _lib.load(); _req(x, torch.float32, "x")
+    y = torch.empty_like(x)
+    check(lib.rnn_tanh_fwd_f32(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_tanh_fwd_f32")
+    return y
+
+
+def tanh_bwd(dy, y):
+    lib = _lib.load(); _req(dy, torch.float32, "dy")
+    dx = torch.empty_like(y)
+    check(lib.rnn_tanh_bwd_f32(ptr(dy), ptr(y), ptr(dx), y.numel(), cur_stream()), "rnn_tanh_bwd_f32")
+    return dx
+
+
+def add(a, b):
+    lib = _lib.load(); _req(a, torch.bfloat16, "a"); _req(b, torch.bfloat16, "b")
+    y = torch.empty_like(a)
+    check(lib.rnn_add_bf16(ptr(a), ptr(b), ptr(y), a.numel(), cur_stream()), "rnn_add_bf16")
+    return y
+
+
+def cast_f32_to_bf16(x, out=None):
+    lib = _lib.load(); _req(x, torch.float32, "x")
+    y = out if out is not None else torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
+    check(lib.rnn_cast_f32_to_bf16(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_f32_to_bf16")
+    return y
+
+
+def cast_bf16_to_f32(x, out=None):
+    lib = _lib.load(); _req(x, torch.bfloat16, "x")
+    y = out if out is not None else torch.empty(x.shape, dtype=torch.float32, device=x.device)
+    check(lib.rnn_cast_bf16_to_f32(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_bf16_to_f32")
+    return y
+
+
+def dropout_fwd(x, p, seed, offset):
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    y = torch.empty_like(x)
+    mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+    check(lib.rnn_dropout_fwd(ptr(x), ptr(y), ptr(mask), x.numel(), float(p), int(seed), int(offset), _is_f32(x),
+                              cur_stream()), "rnn_dropout_fwd")
+    return y, mask
+
+
+def dropout_bwd(dy, mask, p):
+    lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
+    dx = torch.empty_like(dy)
+    check(lib.rnn_dropout_bwd(ptr(dy), ptr(mask), ptr(dx), dy.numel(), float(p), _is_f32(dy), cur_stream()),
+          "rnn_dropout_bwd")
+    return dx
+
+
+# =========================================================================================== normalisation
+def bn_stats(x2d, gamma, beta, eps, momentum, running_mean, running_var):
+    """x2d [M, C] bf16 -> (mean, invstd, scale, shift) fp32; updates running stats in place."""
+    lib = _lib.load(); _req(x2d, torch.bfloat16, "x")
+    M, Cn = x2d.shape
+    st = torch.empty((4, Cn), dtype=torch.float32, device=x2d.device)
+    nbytes = lib.rnn_bn_workspace(M, Cn)
+    ws = workspace(nbytes, x2d.device)
+    check(lib.rnn_bn_stats_bf16(ptr(x2d), M, Cn, ptr(gamma), ptr(beta), float(eps), float(momentum),
+                                ptr(running_mean), ptr(running_var), ptr(st[0]), ptr(st[1]), ptr(st[2]), ptr(st[3]),
+                                ptr(ws), nbytes, cur_stream()), "rnn_bn_stats_bf16")
+    return st[0], st[1], st[2], st[3]
+
+
+def bn_eval_prepare(gamma, beta, running_mean, running_var, eps):
+    lib = _lib.load()
+    Cn = running_mean.numel()
+    st = torch.empty((2, Cn), dtype=torch.float32, device=running_mean.device)
+    check(lib.rnn_bn_eval_prepare(ptr(gamma), ptr(beta), ptr(running_mean), ptr(running_var), float(eps), Cn,
+                                  ptr(st[0]), ptr(st[1]), cur_stream()), "rnn_bn_eval_prepare")
+    return st[0], st[1]
+
+
+def bn_apply(x2d, scale, shift, residual=None, relu=False):
+    lib = _lib.load(); _req(x2d, torch.bfloat16, "x")
+    M, Cn = x2d.shape
+    y = torch.empty_like(x2d)
+    check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), M, Cn,
+                                cur_stream()), "rnn_bn_apply_bf16")
+    return y
+
+
+def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, accumulate):
+    lib = _lib.load(); _req(dy2d, torch.bfloat16, "dy")
+    M, Cn = x2d.shape
+    dx = torch.empty_like(x2d)
+    dres = torch.empty_like(x2d) if want_dres else None
+    sums = torch.empty((2, Cn), dtype=torch.float32, device=x2d.device)
+    nbytes = lib.rnn_bn_workspace(M, Cn)
+    ws = workspace(nbytes, x2d.device)
+    check(lib.rnn_bn_bwd_bf16(ptr(dy2d), ptr(x2d), ptr(y_out), ptr(mean), ptr(invstd), ptr(gamma), M, Cn, ptr(dx),
+                              ptr(dres), ptr(dgamma), ptr(dbeta), _is_f32(dgamma) if dgamma is not None else 1,
+                              int(accumulate), ptr(sums[0]), ptr(sums[1]), ptr(ws), nbytes, cur_stream()),
+          "rnn_bn_bwd_bf16")
+    return dx, dres
+
+
+def layernorm_fwd(x2d, residual, gamma, beta, eps, keep_sum=True):
+    lib = _lib.load(); _cuda(x2d); _contig(x2d, "x")
+    M, E = x2d.shape
+    y = torch.empty_like(x2d)
+    xsum = torch.empty_like(x2d) if (residual is not None and keep_sum) else None
+    st = torch.empty((2, M), dtype=torch.float32, device=x2d.device)
+    check(lib.rnn_layernorm_fwd(ptr(x2d), ptr(residual), ptr(gamma), ptr(beta), float(eps), ptr(y), ptr(xsum),
+                                ptr(st[0]), ptr(st[1]), M, E, _is_f32(x2d), cur_stream()), "rnn_layernorm_fwd")
+    return y, (xsum if xsum is not None else x2d), st[0], st[1]
+
+
+def layernorm_bwd(dy2d, xin2d, gamma, mean, rstd, dgamma, dbeta, accumulate):
+    lib = _lib.load(); _cuda(dy2d); _contig(dy2d, "dy")
+    M, E = xin2d.shape
+    dx = torch.empty_like(xin2d)
+    nbytes = lib.rnn_layernorm_bwd_workspace(M, E)
+    ws = workspace(nbytes, xin2d.device)
+    check(lib.rnn_layernorm_bwd(ptr(dy2d), ptr(xin2d), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx), ptr(dgamma),
+                                ptr(dbeta), int(accumulate), M, E, _is_f32(xin2d), ptr(ws), nbytes, cur_stream()),
+          "rnn_layernorm_bwd")
+    return dx
+
+
+# =========================================================================================== pooling
+def _pool_args(x, k, s, p):
+    N, H, W, Cn = x.shape
+    kh, kw = (k, k) if isinstance(k, int) else k
+    sh, sw = (s, s) if isinstance(s, int) else s
+    ph, pw = (p, p) if isinstance(p, int) else p
+    P = (H + 2 * ph - kh) // sh + 1
+    Q = (W + 2 * pw - kw) // sw + 1
+    return N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q
+
+
+def maxpool2d_fwd(x, k, s, p, return_indices=True):
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q = _pool_args(x, k, s, p)
+    y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
+    idx = torch.empty((N, P, Q, Cn), dtype=torch.int32, device=x.device) if return_indices else None
+    check(lib.rnn_maxpool2d_fwd(ptr(x), ptr(y), ptr(idx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x),
+                                cur_stream()), "rnn_maxpool2d_fwd")
+    return y, idx
+
+
+def maxpool2d_bwd(dy, idx, x_shape, k, s, p):
+    lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
+    N, H, W, Cn = x_shape
+    kh, kw = (k, k) if isinstance(k, int) else k
+    sh, sw = (s, s) if isinstance(s, int) else s
+    ph, pw = (p, p) if isinstance(p, int) else p
+    dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
+    check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy),
+                                cur_stream()), "rnn_maxpool2d_bwd")
+    return dx
+
+
+def avgpool2d_fwd(x, k, s, p):
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q = _pool_args(x, k, s, p)
+    y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
+    check(lib.rnn_avgpool2d_fwd(ptr(x), ptr(y), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x), cur_stream()),
+          "rnn_avgpool2d_fwd")
+    return y
+
+
+def avgpool2d_bwd(dy, x_shape, k, s, p):
+    lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
+    N, H, W, Cn = x_shape
+    kh, kw = (k, k) if isinstance(k, int) else k
+    sh, sw = (s, s) if isinstance(s, int) else s
+    ph, pw = (p, p) if isinstance(p, int) else p
+    dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
+    check(lib.rnn_avgpool2d_bwd(ptr(dy), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()),
+          "rnn_avgpool2d_bwd")
+    return dx
+
+
+def global_avgpool_fwd(x):
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    N, H, W, Cn = x.shape
+    y = torch.empty((N, 1, 1, Cn), dtype=x.dtype, device=x.device)
+    check(lib.rnn_global_avgpool_fwd(ptr(x), ptr(y), N, H * W, Cn, _is_f32(x), cur_stream()), "rnn_global_avgpool_fwd")
+    return y
+
+
+def global_avgpool_bwd(dy, x_shape):
+    lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
+    N, H, W, Cn = x_shape
+    dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
+    check(lib.rnn_global_avgpool_bwd(ptr(dy), ptr(dx), N, H * W, Cn, _is_f32(dy), cur_stream()),
+          "rnn_global_avgpool_bwd")
+    return dx
+
+
+# =========================================================================================== softmax / loss
+def softmax_fwd(x2d):
+    lib = _lib.load(); _cuda(x2d); _contig(x2d, "x")
+    y = torch.empty_like(x2d)
+    check(lib.rnn_softmax_fwd(ptr(x2d), ptr(y), x2d.shape[0], x2d.shape[1], _is_f32(x2d), cur_stream()),
+          "rnn_softmax_fwd")
+    return y
+
+
+def softmax_bwd(dy2d, y2d):
+    lib = _lib.load(); _cuda(dy2d); _contig(dy2d, "dy")
+    dx = torch.empty_like(y2d)
+    check(lib.rnn_softmax_bwd(ptr(dy2d), ptr(y2d), ptr(dx), y2d.shape[0], y2d.shape[1], _is_f32(y2d), cur_stream()),
+          "rnn_softmax_bwd")
+    return dx
+
+
+def softmax_ce(logits, target, grad_scale=None, want_grad=True):
+    """Returns (loss scalar fp32 tensor, dlogits or None).  grad_scale defaults to 1/rows (mean reduction)."""
+    lib = _lib.load(); _cuda(logits, target); _contig(logits, "logits")
+    if target.dtype != torch.int64:
+        raise TypeError("target must be int64 class indices")
+    rows, cols = logits.shape
+    row_loss = torch.empty((rows + 1,), dtype=torch.float32, device=logits.device)
+    dl = torch.empty_like(logits) if want_grad else None
+    gs = (1.0 / rows) if grad_scale is None else grad_scale
+    check(lib.rnn_softmax_ce(ptr(logits), ptr(target), rows, cols, float(gs), ptr(row_loss), ptr(row_loss[rows:]),
+                             ptr(dl), _is_f32(logits), cur_stream()), "rnn_softmax_ce")
+    return row_loss[rows], dl
+
+
+def argmax(x2d):
+    lib = _lib.load(); _cuda(x2d); _contig(x2d, "x")
+    out = torch.empty((x2d.shape[0],), dtype=torch.int64, device=x2d.device)
+    check(lib.rnn_argmax(ptr(x2d), ptr(out), x2d.shape[0], x2d.shape[1], _is_f32(x2d), cur_stream()), "rnn_argmax")
+    return out
+
+
+# =========================================================================================== optimizers
+def sgd_step(w, buf, grad, wcopy, *, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
+             first_step=False, grad_scale=1.0):
+    lib = _lib.load(); _req(w, torch.float32, "w")
+    check(lib.rnn_sgd_step(ptr(w), ptr(buf), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
+                           int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
+                           float(momentum), float(dampening), float(weight_decay), int(nesterov), int(first_step),
+                           float(grad_scale), cur_stream()), "rnn_sgd_step")
+
+
+def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, step=1, grad_scale=1.0):
+    lib = _lib.load(); _req(w, torch.float32, "w")
+    check(lib.rnn_adamw_step(ptr(w), ptr(m), ptr(v), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
+                             int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
+                             float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
+                             float(grad_scale), cur_stream()), "rnn_adamw_step")

@@ -1,0 +1,378 @@
+"""torch.autograd.Function wrappers: one per operator, forward and backward both running the library's
+CUDA kernels.  The reference has no custom Functions ("backward of all of the above
+-- implicit autograd"); these replace ATen's forward AND derivative kernels for the same operators.
+
+Layout convention: 4-D activations are logical NCHW tensors with channels_last strides, so
+`x.permute(0, 2, 3, 1)` is the contiguous NHWC buffer the kernels read.  Parameter gradients are written
+straight into `param.grad` (which may be a view into a flat optimizer bucket) and reported to
+`grad_ready_hooks` so that data-parallel buckets can start their all-reduce during backward.
+"""
+from __future__ import annotations
+
+import torch
+from torch.autograd import Function
+
+from .. import functional as RF
+
+# callables invoked as hook(param) right after a parameter's gradient kernel has been enqueued
+grad_ready_hooks: list = []
+
+
+def _notify(p):
+    for h in grad_ready_hooks:
+        h(p)
+
+
+def grad_target(p: torch.Tensor):
+    """Tensor to write p's gradient into and whether the write must accumulate."""
+    if p.grad is None:
+        p.grad = torch.empty_like(p)
+        return p.grad, False
+    if getattr(p, "_rnn_fresh", False):
+        p._rnn_fresh = False
+        return p.grad, False
+    return p.grad, True
+
+
+def nhwc(x: torch.Tensor) -> torch.Tensor:
+    """Contiguous NHWC buffer behind a logical NCHW tensor (a view when x is channels_last)."""
+    if x.dim() != 4:
+        raise ValueError(f"expected a 4-D NCHW tensor, got shape {tuple(x.shape)}")
+    xp = x.permute(0, 2, 3, 1)
+    return xp if xp.is_contiguous() else xp.contiguous()
+
+
+def nchw(y_nhwc: torch.Tensor) -> torch.Tensor:
+    return y_nhwc.permute(0, 3, 1, 2)
+
+
+def _bias_f32(b):
+    if b is None:
+        return None
+    if b.dtype == torch.float32:
+        return b.detach()
+    n = b.numel()
+    if n % 4 == 0:
+        return RF.cast_bf16_to_f32(b.detach().contiguous())
+    return b.detach().float()
+
+
+def _write_param_grad(p, compute):
+    """compute(out, accumulate) enqueues the kernel(s) that produce p's gradient."""
+    tgt, acc = grad_target(p)
+    compute(tgt, acc)
+    _notify(p)
+
+
+# ------------------------------------------------------------------------------------------ Conv2d
+class Conv2dFn(Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, pad):
+        xh = nhwc(x)
+        wk = nhwc(weight)  # [K,C,R,S] channels_last -> KRSC
+        ctx.stride, ctx.pad = stride, pad
+        ctx.has_bias = bias is not None
+        if weight.dtype == torch.float32:
+            y = RF.conv2d_fprop_f32(xh, wk, bias.detach() if bias is not None else None, stride=stride, pad=pad)
+        else:
+            y = RF.conv2d_fprop(xh, wk, stride=stride, pad=pad, shift=_bias_f32(bias))
+        ctx.save_for_backward(xh, weight, bias)
+        return nchw(y)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xh, weight, bias = ctx.saved_tensors
+        wk = nhwc(weight)
+        dyh = nhwc(dy)
+        stride, pad = ctx.stride, ctx.pad
+        f32 = weight.dtype == torch.float32
+        if weight.requires_grad:
+            def wg(out, acc):
+                o = nhwc_param_view(out)
+                if f32:
+                    RF.conv2d_wgrad_f32(xh, dyh, tuple(wk.shape), stride=stride, pad=pad, out=o, accumulate=acc)
+                else:
+                    RF.conv2d_wgrad(xh, dyh, tuple(wk.shape), stride=stride, pad=pad, out=o, accumulate=acc)
+            _write_param_grad(weight, wg)
+        if bias is not None and bias.requires_grad:
+            K = dyh.shape[-1]
+            _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if f32:
+                dx = nchw(RF.conv2d_dgrad_f32(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
+            else:
+                dx = nchw(RF.conv2d_dgrad(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
+        return dx, None, None, None, None
+
+
+def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
+    """KRSC buffer behind a [K,C,R,S] gradient tensor; it must already be channels_last (no copy allowed,
+    the kernel writes through it)."""
+    v = g.permute(0, 2, 3, 1)
+    if not v.is_contiguous():
+        raise RuntimeError("conv weight gradients must be channels_last (use replicann_b200.nn.Conv2d parameters)")
+    return v
+
+
+# ------------------------------------------------------------------------------------------ Linear
+class LinearFn(Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, relu):
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        if weight.dtype == torch.float32:
+            y = RF.gemm_f32(x2, weight.detach(), bias=bias.detach() if bias is not None else None, relu=relu)
+        else:
+            y = RF.gemm(x2, weight.detach(), bias=_bias_f32(bias), relu=relu)
+        ctx.relu = relu
+        ctx.xshape = x.shape
+        ctx.save_for_backward(x2, weight, bias, y if relu else None)
+        return y.reshape(*x.shape[:-1], weight.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, weight, bias, y = ctx.saved_tensors
+        dy2 = dy.reshape(-1, weight.shape[0])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if ctx.relu:
+            dy2 = RF.relu_bwd(dy2, y)
+        f32 = weight.dtype == torch.float32
+        if weight.requires_grad:
+            def wg(out, acc):
+                if f32:
+                    RF.gemm_f32(dy2, x2, a_mn=True, b_mn=True, out=out, accumulate=acc)
+                else:
+                    g = RF.gemm(dy2, x2, a_mn=True, b_mn=True, out=None if acc else out)
+                    if acc:
+                        out.copy_(RF.add(out, g))
+            _write_param_grad(weight, wg)
+        if bias is not None and bias.requires_grad:
+            _write_param_grad(bias, lambda out, acc: RF.colsum(dy2, out=out, accumulate=acc))
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if f32:
+                dx = RF.gemm_f32(dy2, weight.detach(), b_mn=True)
+            else:
+                dx = RF.gemm(dy2, weight.detach(), b_mn=True)
+            dx = dx.reshape(ctx.xshape)
+        return dx, None, None, None
+
+
+# ------------------------------------------------------------------------------------------ BatchNorm2d
+class BatchNormFn(Function):
+    """y = relu(BN(x) + residual) with batch statistics (training) or running statistics (eval)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, running_mean, running_var, training, momentum, eps, relu):
+        xh = nhwc(x)
+        Cn = xh.shape[-1]
+        x2 = xh.reshape(-1, Cn)
+        r2 = nhwc(residual).reshape(-1, Cn) if residual is not None else None
+        g = gamma.detach() if gamma is not None else None
+        b = beta.detach() if beta is not None else None
+        if training:
+            mean, invstd, scale, shift = RF.bn_stats(x2, g, b, eps, momentum, running_mean, running_var)
+        else:
+            scale, shift = RF.bn_eval_prepare(g, b, running_mean, running_var, eps)
+            mean, invstd = running_mean, torch.rsqrt(running_var + eps)
+        y2 = RF.bn_apply(x2, scale, shift, r2, relu)
+        ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
+        ctx.save_for_backward(x2, y2 if relu else None, mean, invstd, gamma, beta)
+        ctx.shape = xh.shape
+        return nchw(y2.reshape(xh.shape))
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, y2, mean, invstd, gamma, beta = ctx.saved_tensors
+        if not ctx.training:
+            raise RuntimeError("BatchNorm2d backward in eval mode is not supported by replicann_b200")
+        Cn = x2.shape[1]
+        dy2 = nhwc(dy).reshape(-1, Cn)
+        need_g = gamma is not None and gamma.requires_grad
+        if need_g:
+            dg, acc = grad_target(gamma)
+            db, acc_b = grad_target(beta)
+            acc = acc or acc_b
+        else:
+            dg = db = None
+            acc = False
+        dx2, dres2 = RF.bn_bwd(dy2, x2, y2, mean, invstd, gamma.detach() if gamma is not None else None,
+                               want_dres=ctx.has_res, dgamma=dg, dbeta=db, accumulate=acc)
+        if need_g:
+            _notify(gamma)
+            _notify(beta)
+        dx = nchw(dx2.reshape(ctx.shape)) if ctx.needs_input_grad[0] else None
+        dres = nchw(dres2.reshape(ctx.shape)) if ctx.has_res else None
+        return dx, None, None, dres, None, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------ LayerNorm
+class LayerNormFn(Function):
+    """y = LayerNorm(x + residual) * gamma + beta  (post-LN block, arch/transformer.py:111-112)."""
+
+    @staticmethod
+    def forward(ctx, x, residual, gamma, beta, eps):
+        E = x.shape[-1]
+        x2 = x.reshape(-1, E)
+        x2 = x2 if x2.is_contiguous() else x2.contiguous()
+        r2 = None
+        if residual is not None:
+            r2 = residual.reshape(-1, E)
+            r2 = r2 if r2.is_contiguous() else r2.contiguous()
+        y2, xin, mean, rstd = RF.layernorm_fwd(x2, r2, gamma.detach(), beta.detach(), eps)
+        ctx.has_res = residual is not None
+        ctx.shape = x.shape
+        ctx.save_for_backward(xin, mean, rstd, gamma, beta)
+        return y2.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xin, mean, rstd, gamma, beta = ctx.saved_tensors
+        E = xin.shape[1]
+        dy2 = dy.reshape(-1, E)
+        dy2 = dy2 if dy2.is_contiguous() else dy2.contiguous()
+        dg, acc = grad_target(gamma)
+        db, acc_b = grad_target(beta)
+        if acc != acc_b:
+            raise RuntimeError("LayerNorm weight/bias gradient state out of sync")
+        dx2 = RF.layernorm_bwd(dy2, xin, gamma.detach(), mean, rstd, dg, db, acc)
+        _notify(gamma)
+        _notify(beta)
+        dx = dx2.reshape(ctx.shape)
+        return dx, (dx if ctx.has_res else None), None, None, None
+
+
+# ------------------------------------------------------------------------------------------ activations
+class ReLUFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        if x.dim() == 4:
+            xh = nhwc(x)
+            y = RF.relu_fwd(xh)
+            ctx.save_for_backward(y)
+            ctx.four = True
+            return nchw(y)
+        xc = x if x.is_contiguous() else x.contiguous()
+        y = RF.relu_fwd(xc)
+        ctx.save_for_backward(y)
+        ctx.four = False
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if ctx.four:
+            return nchw(RF.relu_bwd(nhwc(dy), y))
+        return RF.relu_bwd(dy if dy.is_contiguous() else dy.contiguous(), y)
+
+
+class TanhFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        four = x.dim() == 4
+        xc = nhwc(x) if four else (x if x.is_contiguous() else x.contiguous())
+        y = RF.tanh_fwd(xc)
+        ctx.save_for_backward(y)
+        ctx.four = four
+        return nchw(y) if four else y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if ctx.four:
+            return nchw(RF.tanh_bwd(nhwc(dy), y))
+        return RF.tanh_bwd(dy if dy.is_contiguous() else dy.contiguous(), y)
+
+
+class DropoutFn(Function):
+    @staticmethod
+    def forward(ctx, x, p, seed, offset):
+        xc = x if x.is_contiguous() else x.contiguous()
+        y, mask = RF.dropout_fwd(xc, p, seed, offset)
+        ctx.p = p
+        ctx.save_for_backward(mask)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (mask,) = ctx.saved_tensors
+        return RF.dropout_bwd(dy if dy.is_contiguous() else dy.contiguous(), mask, ctx.p), None, None, None
+
+
+# ------------------------------------------------------------------------------------------ pooling
+class MaxPool2dFn(Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        xh = nhwc(x)
+        y, idx = RF.maxpool2d_fwd(xh, k, s, p)
+        ctx.cfg = (tuple(xh.shape), k, s, p)
+        ctx.save_for_backward(idx)
+        ctx.mark_non_differentiable(idx)
+        return nchw(y), nchw(idx)
+
+    @staticmethod
+    def backward(ctx, dy, _didx):
+        (idx,) = ctx.saved_tensors
+        shape, k, s, p = ctx.cfg
+        return nchw(RF.maxpool2d_bwd(nhwc(dy), idx, shape, k, s, p)), None, None, None
+
+
+class AvgPool2dFn(Function):
+    @staticmethod
+    def forward(ctx, x, k, s, p):
+        xh = nhwc(x)
+        ctx.cfg = (tuple(xh.shape), k, s, p)
+        return nchw(RF.avgpool2d_fwd(xh, k, s, p))
+
+    @staticmethod
+    def backward(ctx, dy):
+        shape, k, s, p = ctx.cfg
+        return nchw(RF.avgpool2d_bwd(nhwc(dy), shape, k, s, p)), None, None, None
+
+
+class GlobalAvgPoolFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        xh = nhwc(x)
+        ctx.shape = tuple(xh.shape)
+        return nchw(RF.global_avgpool_fwd(xh))
+
+    @staticmethod
+    def backward(ctx, dy):
+        return nchw(RF.global_avgpool_bwd(nhwc(dy), ctx.shape))
+
+
+# ------------------------------------------------------------------------------------------ loss
+class SoftmaxCrossEntropyFn(Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        lg = logits if logits.is_contiguous() else logits.contiguous()
+        loss, dl = RF.softmax_ce(lg, target, want_grad=logits.requires_grad)
+        ctx.save_for_backward(dl)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dl,) = ctx.saved_tensors
+        ctx_one = getattr(SoftmaxCrossEntropyFn, "assume_unit_grad", False)
+        return (dl if ctx_one else dl * dloss.to(dl.dtype)), None
+
+
+class SoftmaxFn(Function):
+    @staticmethod
+    def forward(ctx, x):
+        cols = x.shape[-1]
+        x2 = x.reshape(-1, cols)
+        y = RF.softmax_fwd(x2 if x2.is_contiguous() else x2.contiguous())
+        ctx.save_for_backward(y)
+        ctx.shape = x.shape
+        return y.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        d2 = dy.reshape(y.shape)
+        return RF.softmax_bwd(d2 if d2.is_contiguous() else d2.contiguous(), y).reshape(ctx.shape)

@@ -1,0 +1,324 @@
+"""GPU parity of the HBM-bound kernels and the fp32 path against torch CPU (the dependency the reference
+calls into), through the C ABI.  Tolerances: fp32 1e-4 relative, bf16 1e-2 relative (north_star);
+indices bit-exact."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def RF():
+    from replicann_b200 import functional
+    return functional
+
+
+def rel_err(got, ref):
+    got = got.detach().float().cpu()
+    ref = ref.detach().float().cpu()
+    return ((got - ref).abs().max() / (ref.abs().max() + 1e-12)).item()
+
+
+def rnd(shape, seed, dtype=torch.float32, scale=1.0):
+    g = torch.Generator().manual_seed(seed)
+    return (torch.randn(shape, generator=g) * scale).to(dtype)
+
+
+# ------------------------------------------------------------------------------------------ BatchNorm
+@pytest.mark.parametrize("M,C", [(2 * 14 * 14, 64), (3 * 7 * 7, 256), (1000, 2048), (513, 192), (4096, 8)])
+@pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
+def test_batchnorm_fwd_bwd(M, C, relu, res):
+    f = RF()
+    x = rnd((M, C), 1, torch.bfloat16) * 2 + 0.5
+    gamma = torch.rand(C, generator=torch.Generator().manual_seed(2)) + 0.5
+    beta = rnd((C,), 3)
+    resid = rnd((M, C), 4, torch.bfloat16) if res else None
+    dy = rnd((M, C), 5, torch.bfloat16)
+    rm, rv = torch.zeros(C), torch.ones(C)
+    xd = x.cuda()
+    rmd, rvd = rm.cuda(), rv.cuda()
+    gd, bd = gamma.cuda(), beta.cuda()
+    mean, invstd, scale, shift = f.bn_stats(xd, gd, bd, 1e-5, 0.1, rmd, rvd)
+    y = f.bn_apply(xd, scale, shift, resid.cuda() if res else None, relu)
+
+    # reference: torch BatchNorm on [M, C, 1, 1]
+    xr = x.float().reshape(M, C, 1, 1).requires_grad_(True)
+    gr = gamma.clone().requires_grad_(True)
+    br = beta.clone().requires_grad_(True)
+    rr = resid.float().reshape(M, C, 1, 1).requires_grad_(True) if res else None
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    out = F.batch_norm(xr, rm_ref, rv_ref, gr, br, training=True, momentum=0.1, eps=1e-5)
+    if res:
+        out = out + rr
+    if relu:
+        # A pre-activation within fp32 rounding of zero may land on either side of the ReLU; such ties
+        # must be rare, and the backward comparison uses the GPU's own mask so it is tie-free.
+        mask = (y.float().cpu() > 0).reshape(M, C, 1, 1)
+        assert ((out > 0) != mask).float().mean().item() < 1e-5
+        out = out * mask
+    out.backward(dy.float().reshape(M, C, 1, 1))
+    assert rel_err(y, out.reshape(M, C)) < 1e-2
+    assert rel_err(rmd, rm_ref) < 1e-4 and rel_err(rvd, rv_ref) < 1e-3
+    dgamma = torch.empty(C, device="cuda")
+    dbeta = torch.empty(C, device="cuda")
+    dx, dres = f.bn_bwd(dy.cuda(), xd, y if relu else None, mean, invstd, gd, want_dres=res, dgamma=dgamma,
+                        dbeta=dbeta, accumulate=False)
+    assert rel_err(dx, xr.grad.reshape(M, C)) < 1e-2
+    assert rel_err(dgamma, gr.grad) < 1e-2 and rel_err(dbeta, br.grad) < 1e-2
+    if res:
+        assert rel_err(dres, rr.grad.reshape(M, C)) < 1e-2
+
+
+def test_batchnorm_eval_prepare():
+    f = RF()
+    C = 64
+    g, b, rm = rnd((C,), 1), rnd((C,), 2), rnd((C,), 3)
+    rv = torch.rand(C) + 0.1
+    scale, shift = f.bn_eval_prepare(g.cuda(), b.cuda(), rm.cuda(), rv.cuda(), 1e-5)
+    x = rnd((10, C), 4)
+    ref = F.batch_norm(x.reshape(10, C, 1, 1), rm, rv, g, b, training=False, eps=1e-5).reshape(10, C)
+    assert rel_err(x * scale.cpu() + shift.cpu(), ref) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ LayerNorm
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-4), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("M,E,res", [(64, 512, True), (37, 768, False), (8, 16, True)])
+def test_layernorm(dtype, tol, M, E, res):
+    f = RF()
+    x = rnd((M, E), 1, dtype)
+    r = rnd((M, E), 2, dtype) if res else None
+    g = (torch.rand(E) + 0.5).to(dtype)
+    b = rnd((E,), 3, dtype)
+    dy = rnd((M, E), 4, dtype)
+    xr = x.float().requires_grad_(True)
+    rr = r.float().requires_grad_(True) if res else None
+    gr, br = g.float().requires_grad_(True), b.float().requires_grad_(True)
+    s = xr + rr if res else xr
+    ref = F.layer_norm(s, (E,), gr, br, 1e-5)
+    ref.backward(dy.float())
+    y, xin, mean, rstd = f.layernorm_fwd(x.cuda(), r.cuda() if res else None, g.cuda(), b.cuda(), 1e-5)
+    assert rel_err(y, ref) < tol
+    dg = torch.empty(E, dtype=dtype, device="cuda")
+    db = torch.empty(E, dtype=dtype, device="cuda")
+    dx = f.layernorm_bwd(dy.cuda(), xin, g.cuda(), mean, rstd, dg, db, False)
+    assert rel_err(dx, xr.grad) < tol
+    assert rel_err(dg, gr.grad) < max(tol, 2e-4) and rel_err(db, br.grad) < max(tol, 2e-4)
+
+
+# ------------------------------------------------------------------------------------------ pooling
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,C,k,s,p", [(2, 112, 112, 64, 3, 2, 1), (2, 13, 13, 16, 3, 2, 0), (3, 28, 28, 8, 2, 2, 0),
+                                            (1, 7, 9, 24, 3, 1, 1)])
+def test_maxpool_indices_bit_exact(dtype, N, H, W, C, k, s, p):
+    f = RF()
+    x = rnd((N, H, W, C), 1, dtype)
+    # ties on purpose: quantise so that equal maxima occur inside windows
+    x = (x * 2).round() / 2
+    xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    ref, ridx = F.max_pool2d(xr, k, s, p, return_indices=True)
+    y, idx = f.maxpool2d_fwd(x.cuda(), k, s, p)
+    assert torch.equal(y.float().cpu(), ref.permute(0, 2, 3, 1))
+    assert torch.equal(idx.cpu().long(), ridx.permute(0, 2, 3, 1))  # bit-exact argmax
+    dy = rnd(tuple(y.shape), 2, dtype)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = f.maxpool2d_bwd(dy.cuda(), idx, tuple(x.shape), k, s, p)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < (1e-5 if dtype == torch.float32 else 1e-2)
+
+
+def test_maxpool_nan_propagates():
+    f = RF()
+    x = rnd((1, 4, 4, 8), 1)
+    x[0, 1, 1, 3] = float("nan")
+    ref, ridx = F.max_pool2d(x.permute(0, 3, 1, 2), 2, 2, 0, return_indices=True)
+    y, idx = f.maxpool2d_fwd(x.cuda(), 2, 2, 0)
+    assert torch.equal(idx.cpu().long(), ridx.permute(0, 2, 3, 1))
+    assert torch.isnan(y.cpu()[0, 0, 0, 3])
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("N,H,W,C,k,s,p", [(2, 28, 28, 8, 2, 2, 0), (2, 10, 10, 16, 2, 2, 0), (1, 9, 9, 8, 3, 2, 1)])
+def test_avgpool(dtype, tol, N, H, W, C, k, s, p):
+    f = RF()
+    x = rnd((N, H, W, C), 1, dtype)
+    xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    ref = F.avg_pool2d(xr, k, s, p)
+    y = f.avgpool2d_fwd(x.cuda(), k, s, p)
+    assert rel_err(y, ref.permute(0, 2, 3, 1)) < tol
+    dy = rnd(tuple(y.shape), 2, dtype)
+    ref.backward(dy.float().permute(0, 3, 1, 2))
+    dx = f.avgpool2d_bwd(dy.cuda(), tuple(x.shape), k, s, p)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("N,HW,C", [(4, 49, 2048), (3, 36, 256), (2, 5, 16)])
+def test_global_avgpool(dtype, tol, N, HW, C):
+    f = RF()
+    x = rnd((N, HW, 1, C), 1, dtype)
+    ref = x.float().mean(dim=(1, 2))
+    y = f.global_avgpool_fwd(x.cuda())
+    assert rel_err(y.reshape(N, C), ref) < tol
+    dy = rnd((N, 1, 1, C), 2, dtype)
+    dx = f.global_avgpool_bwd(dy.cuda(), tuple(x.shape))
+    assert rel_err(dx, (dy.float() / HW).expand(N, HW, 1, C)) < tol
+
+
+# ------------------------------------------------------------------------------------------ softmax / CE
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("rows,cols", [(64, 128), (7, 1000), (5, 10)])
+def test_softmax(dtype, tol, rows, cols):
+    f = RF()
+    x = rnd((rows, cols), 1, dtype, 3.0)
+    xr = x.float().requires_grad_(True)
+    ref = F.softmax(xr, dim=-1)
+    y = f.softmax_fwd(x.cuda())
+    assert rel_err(y, ref) < tol
+    dy = rnd((rows, cols), 2, dtype)
+    ref.backward(dy.float())
+    yq = y if dtype == torch.float32 else ref.detach().to(dtype).cuda()
+    dx = f.softmax_bwd(dy.cuda(), yq)
+    assert rel_err(dx, xr.grad) < max(tol, 1e-4)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+@pytest.mark.parametrize("rows,cols", [(256, 1000), (64, 10), (3, 7)])
+def test_softmax_cross_entropy(dtype, tol, rows, cols):
+    f = RF()
+    x = rnd((rows, cols), 1, dtype, 2.0)
+    t = torch.randint(0, cols, (rows,), generator=torch.Generator().manual_seed(2))
+    xr = x.float().requires_grad_(True)
+    ref = F.cross_entropy(xr, t)
+    ref.backward()
+    loss, dl = f.softmax_ce(x.cuda(), t.cuda())
+    assert abs(loss.item() - ref.item()) < 1e-4 * max(1.0, abs(ref.item()))
+    assert rel_err(dl, xr.grad) < tol
+    am = f.argmax(x.cuda())
+    assert torch.equal(am.cpu(), x.float().argmax(dim=-1))  # bit-exact
+
+
+# ------------------------------------------------------------------------------------------ optimizers
+@pytest.mark.parametrize("gdt", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("nesterov", [False, True])
+def test_sgd_matches_torch(gdt, nesterov):
+    f = RF()
+    n = 4096 + 64
+    w0 = rnd((n,), 1)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.SGD([p], lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=nesterov)
+    w = w0.clone().cuda()
+    buf = torch.zeros(n, device="cuda")
+    wc = torch.empty(n, dtype=torch.bfloat16, device="cuda")
+    for step in range(3):
+        g = rnd((n,), 10 + step).to(gdt)
+        p.grad = g.float().clone()
+        opt.step()
+        f.sgd_step(w, buf, g.cuda(), wc, lr=0.1, momentum=0.9, weight_decay=1e-4, nesterov=nesterov,
+                   first_step=(step == 0))
+    assert rel_err(w, p.data) < 1e-5
+    assert rel_err(wc, p.data) < 1e-2
+
+
+def test_adamw_matches_torch():
+    f = RF()
+    n = 2048
+    w0 = rnd((n,), 1)
+    p = torch.nn.Parameter(w0.clone())
+    opt = torch.optim.AdamW([p], lr=1e-2, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2)
+    w = w0.clone().cuda()
+    m = torch.zeros(n, device="cuda")
+    v = torch.zeros(n, device="cuda")
+    for step in range(1, 4):
+        g = rnd((n,), 10 + step)
+        p.grad = g.clone()
+        opt.step()
+        f.adamw_step(w, m, v, g.cuda(), None, lr=1e-2, weight_decay=1e-2, step=step)
+    assert rel_err(w, p.data) < 1e-5
+
+
+# ------------------------------------------------------------------------------------------ elementwise
+def test_layout_roundtrip_and_padding():
+    f = RF()
+    x = rnd((2, 3, 17, 20), 1)
+    y = f.nchw_to_nhwc_bf16(x.cuda(), cpad=8)
+    assert tuple(y.shape) == (2, 17, 20, 8)
+    assert torch.equal(y[..., :3].float().cpu(), x.to(torch.bfloat16).float().permute(0, 2, 3, 1))
+    assert (y[..., 3:] == 0).all()
+    back = f.nhwc_bf16_to_nchw_f32(y, channels=3)
+    assert torch.equal(back.cpu(), x.to(torch.bfloat16).float())
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_relu_add_cast(dtype):
+    f = RF()
+    x = rnd((33, 64), 1, dtype)
+    y = f.relu_fwd(x.cuda())
+    assert torch.equal(y.cpu(), x.relu())
+    dy = rnd((33, 64), 2, dtype)
+    dx = f.relu_bwd(dy.cuda(), y)
+    assert torch.equal(dx.cpu(), dy * (x > 0))
+    if dtype == torch.bfloat16:
+        s = f.add(x.cuda(), dy.cuda())
+        assert torch.equal(s.cpu(), (x.float() + dy.float()).to(torch.bfloat16))
+    else:
+        assert torch.equal(f.cast_f32_to_bf16(x.cuda()).cpu(), x.to(torch.bfloat16))
+        assert torch.equal(f.cast_bf16_to_f32(x.to(torch.bfloat16).cuda()).cpu(), x.to(torch.bfloat16).float())
+        t = f.tanh_fwd(x.cuda())
+        assert rel_err(t, x.tanh()) < 1e-5
+        assert rel_err(f.tanh_bwd(dy.cuda(), t), dy * (1 - x.tanh() ** 2)) < 1e-4
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_dropout_properties(dtype):
+    f = RF()
+    n, p = 1 << 20, 0.1
+    x = torch.ones(n, dtype=dtype, device="cuda")
+    y, mask = f.dropout_fwd(x, p, seed=1234, offset=0)
+    keep = mask.float().mean().item()
+    assert abs(keep - (1 - p)) < 5e-3                         # Bernoulli(1-p)
+    kept = y[mask.bool()].float()
+    assert torch.allclose(kept, torch.full_like(kept, 1 / (1 - p)), rtol=1e-2)
+    assert (y[~mask.bool()] == 0).all()
+    y2, mask2 = f.dropout_fwd(x, p, seed=1234, offset=0)
+    assert torch.equal(mask, mask2)                           # counter-based: reproducible
+    y3, mask3 = f.dropout_fwd(x, p, seed=1234, offset=1)
+    assert not torch.equal(mask, mask3)
+    dx = f.dropout_bwd(x, mask, p)
+    assert torch.equal(dx, y)
+    y0, m0 = f.dropout_fwd(x, 0.0, seed=1, offset=0)
+    assert torch.equal(y0, x) and bool(m0.all())
+
+
+# ------------------------------------------------------------------------------------------ fp32 path
+@pytest.mark.parametrize("N,H,W,C,K,R,S,stride,pad", [(4, 28, 28, 1, 6, 5, 5, 1, 2), (4, 14, 14, 6, 16, 5, 5, 1, 0),
+                                                       (2, 9, 9, 3, 8, 3, 3, 2, 1)])
+def test_conv_f32(N, H, W, C, K, R, S, stride, pad):
+    f = RF()
+    x, w, b = rnd((N, H, W, C), 1), rnd((K, R, S, C), 2, scale=0.2), rnd((K,), 3)
+    xr = x.permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    wr = w.permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    ref = F.conv2d(xr, wr, b, stride=stride, padding=pad)
+    y = f.conv2d_fprop_f32(x.cuda(), w.cuda(), b.cuda(), stride=stride, pad=pad)
+    assert rel_err(y, ref.permute(0, 2, 3, 1)) < 1e-4
+    dy = rnd(tuple(y.shape), 4)
+    ref.backward(dy.permute(0, 3, 1, 2))
+    dx = f.conv2d_dgrad_f32(dy.cuda(), w.cuda(), tuple(x.shape), stride=stride, pad=pad)
+    dw = f.conv2d_wgrad_f32(x.cuda(), dy.cuda(), tuple(w.shape), stride=stride, pad=pad)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < 1e-4
+    assert rel_err(dw, wr.grad.permute(0, 2, 3, 1)) < 1e-4
+
+
+@pytest.mark.parametrize("M,N,K", [(64, 120, 400), (64, 10, 84), (130, 70, 33)])
+def test_gemm_f32_all_layouts(M, N, K):
+    f = RF()
+    a, b, bias = rnd((M, K), 1), rnd((N, K), 2), rnd((N,), 3)
+    ref = a @ b.t()
+    assert rel_err(f.gemm_f32(a.cuda(), b.cuda(), bias=bias.cuda()), ref + bias) < 1e-4
+    assert rel_err(f.gemm_f32(a.cuda(), b.t().contiguous().cuda(), b_mn=True), ref) < 1e-4
+    assert rel_err(f.gemm_f32(a.t().contiguous().cuda(), b.t().contiguous().cuda(), a_mn=True, b_mn=True), ref) < 1e-4
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, 1e-2)])
+def test_colsum(dtype, tol):
+    f = RF()
+    x = rnd((1000, 96), 1, dtype)
+    assert rel_err(f.colsum(x.cuda()), x.float().sum(0)) < tol
