@@ -1,0 +1,55 @@
+"""Input stage shared by the ImageNet-shaped CNNs: fp32 NCHW images -> bf16 NHWC with the channel
+dimension zero-padded to one 64-wide tensor-core K step, and the matching zero-padded first filter."""
+from __future__ import annotations
+
+import torch
+from torch import Tensor
+from torch.autograd import Function
+
+from .. import functional as RF
+from ..nn import _functions as Fn
+
+STEM_CPAD = 64
+
+
+def prepare_input(x: Tensor, weight_dtype, cpad: int = STEM_CPAD) -> Tensor:
+    """Bring a user batch to the layout the first convolution reads.
+
+    fp32 NCHW-contiguous images for a bf16 model go through the layout/cast kernel (the input pipeline
+    step of SURVEY.md section 8f.2); tensors that already match pass through untouched."""
+    if weight_dtype == torch.bfloat16:
+        if x.dtype == torch.float32:
+            if not x.is_contiguous():
+                x = x.contiguous()
+            return Fn.nchw(RF.nchw_to_nhwc_bf16(x, cpad=cpad))
+        if x.dtype == torch.bfloat16 and x.shape[1] == cpad:
+            return x
+        raise TypeError("bf16 models take fp32 NCHW images (or an already padded bf16 channels_last tensor)")
+    if x.dtype != torch.float32:
+        raise TypeError(f"fp32 model got input of dtype {x.dtype}")
+    return x
+
+
+class PadFilterFn(Function):
+    """[K, C, R, S] filter -> [K, Cpad, R, S] (channels_last) with zeros in the added channels."""
+
+    @staticmethod
+    def forward(ctx, w, cpad):
+        K, Cn, R, S = w.shape
+        out = torch.zeros((K, cpad, R, S), dtype=w.dtype, device=w.device).contiguous(memory_format=torch.channels_last)
+        out[:, :Cn].copy_(w)
+        ctx.c = Cn
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g[:, :ctx.c].contiguous(memory_format=torch.channels_last), None
+
+
+def stem_conv(x: Tensor, conv, relu: bool = False) -> Tensor:
+    """First convolution of a bf16 CNN on a channel-padded input; fp32 models call the layer directly."""
+    w = conv.weight
+    if w.dtype == torch.bfloat16 and x.shape[1] != w.shape[1]:
+        wp = PadFilterFn.apply(w, x.shape[1])
+        return Fn.Conv2dFn.apply(x, wp, conv.bias, conv.stride, conv.padding, relu)
+    return Fn.Conv2dFn.apply(x, w, conv.bias, conv.stride, conv.padding, relu)

@@ -103,6 +103,15 @@ __global__ void relu_bwd_f32_kernel(const float4* __restrict__ dy, const float4*
     dx[i] = g;
   }
 }
+__global__ void relu_fwd_f32_scalar_kernel(const float* __restrict__ x, float* __restrict__ y, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    y[i] = fmaxf(x[i], 0.f);
+}
+__global__ void relu_bwd_f32_scalar_kernel(const float* __restrict__ dy, const float* __restrict__ y,
+                                           float* __restrict__ dx, long long n) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
 __global__ void tanh_fwd_f32_kernel(const float* __restrict__ x, float* __restrict__ y, long long n) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     y[i] = tanhf(x[i]);
@@ -199,8 +208,13 @@ int rnn_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int H, int 
 }
 
 int rnn_relu_fwd(const void* x, void* y, long long n, int is_f32, cudaStream_t stream) {
-  RNN_REQUIRE(n >= 0 && n % (is_f32 ? 4 : 8) == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(n >= 0 && (is_f32 || n % 8 == 0), RNN_ERR_SHAPE);
   if (n == 0) return RNN_OK;
+  if (is_f32 && n % 4 != 0) {
+    relu_fwd_f32_scalar_kernel<<<ew_grid(n), EW_THREADS, 0, stream>>>((const float*)x, (float*)y, n);
+    RNN_CHECK_LAUNCH();
+    return RNN_OK;
+  }
   const long long nvec = n / (is_f32 ? 4 : 8);
   if (is_f32) relu_fwd_f32_kernel<<<ew_grid(nvec), EW_THREADS, 0, stream>>>((const float4*)x, (float4*)y, nvec);
   else relu_fwd_bf16_kernel<<<ew_grid(nvec), EW_THREADS, 0, stream>>>((const uint4*)x, (uint4*)y, nvec);
@@ -208,8 +222,13 @@ int rnn_relu_fwd(const void* x, void* y, long long n, int is_f32, cudaStream_t s
   return RNN_OK;
 }
 int rnn_relu_bwd(const void* dy, const void* y, void* dx, long long n, int is_f32, cudaStream_t stream) {
-  RNN_REQUIRE(n >= 0 && n % (is_f32 ? 4 : 8) == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(n >= 0 && (is_f32 || n % 8 == 0), RNN_ERR_SHAPE);
   if (n == 0) return RNN_OK;
+  if (is_f32 && n % 4 != 0) {
+    relu_bwd_f32_scalar_kernel<<<ew_grid(n), EW_THREADS, 0, stream>>>((const float*)dy, (const float*)y, (float*)dx, n);
+    RNN_CHECK_LAUNCH();
+    return RNN_OK;
+  }
   const long long nvec = n / (is_f32 ? 4 : 8);
   if (is_f32)
     relu_bwd_f32_kernel<<<ew_grid(nvec), EW_THREADS, 0, stream>>>((const float4*)dy, (const float4*)y, (float4*)dx, nvec);

@@ -5,13 +5,23 @@
 
 namespace {
 
-template <typename T> struct PV;
-template <> struct PV<bf16> {
+template <typename T, bool VEC> struct PV;
+template <> struct PV<bf16, false> {
+  static constexpr int W = 1;
+  __device__ static void load(const bf16* p, float* f) { f[0] = __bfloat162float(*p); }
+  __device__ static void store(bf16* p, const float* f) { *p = __float2bfloat16(f[0]); }
+};
+template <> struct PV<float, false> {
+  static constexpr int W = 1;
+  __device__ static void load(const float* p, float* f) { f[0] = *p; }
+  __device__ static void store(float* p, const float* f) { *p = f[0]; }
+};
+template <> struct PV<bf16, true> {
   static constexpr int W = 8;
   __device__ static void load(const bf16* p, float* f) { unpack8(*reinterpret_cast<const uint4*>(p), f); }
   __device__ static void store(bf16* p, const float* f) { *reinterpret_cast<uint4*>(p) = pack8(f); }
 };
-template <> struct PV<float> {
+template <> struct PV<float, true> {
   static constexpr int W = 4;
   __device__ static void load(const float* p, float* f) {
     const float4 v = *reinterpret_cast<const float4*>(p);
@@ -26,10 +36,10 @@ struct PoolGeom {
   int N, H, W, C, R, S, sh, sw, ph, pw, P, Q;
 };
 
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx, PoolGeom g) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.P * g.Q * cgs;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -48,25 +58,25 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
     for (int h = hs; h < he; ++h)
       for (int w = ws; w < we; ++w) {
         float v[VW];
-        PV<T>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
+        PV<T, VEC>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
 #pragma unroll
         for (int e = 0; e < VW; ++e)
           if (v[e] > best[e] || v[e] != v[e]) { best[e] = v[e]; bi[e] = h * g.W + w; }
       }
     const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
-    PV<T>::store(y + o, best);
+    PV<T, VEC>::store(y + o, best);
     if (idx) {
 #pragma unroll
-      for (int e = 0; e < VW; e += 4) *reinterpret_cast<int4*>(idx + o + e) = make_int4(bi[e], bi[e + 1], bi[e + 2], bi[e + 3]);
+      for (int e = 0; e < VW; ++e) idx[o + e] = bi[e];
     }
   }
 }
 
 // Gather form of the backward pass: every input element sums the dy of the windows whose argmax it is.
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, T* __restrict__ dx, PoolGeom g) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.H * g.W * cgs;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -88,20 +98,20 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, T* __r
       for (int q = q_lo; q <= q_hi; ++q) {
         const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
         float d[VW];
-        PV<T>::load(dy + o, d);
+        PV<T, VEC>::load(dy + o, d);
 #pragma unroll
         for (int e = 0; e < VW; ++e)
           if (idx[o + e] == me) acc[e] += d[e];
       }
-    PV<T>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
+    PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
   }
 }
 
 // count_include_pad = True, ceil_mode = False (torch defaults): divisor is always R*S.
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, PoolGeom g) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.P * g.Q * cgs;
   const float inv = 1.f / (float)(g.R * g.S);
@@ -118,20 +128,20 @@ avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, PoolGeom g) {
     for (int h = max(h0, 0); h < min(h0 + g.R, g.H); ++h)
       for (int w = max(w0, 0); w < min(w0 + g.S, g.W); ++w) {
         float v[VW];
-        PV<T>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
+        PV<T, VEC>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
 #pragma unroll
         for (int e = 0; e < VW; ++e) acc[e] += v[e];
       }
 #pragma unroll
     for (int e = 0; e < VW; ++e) acc[e] *= inv;
-    PV<T>::store(y + (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW, acc);
+    PV<T, VEC>::store(y + (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW, acc);
   }
 }
 
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, PoolGeom g) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.H * g.W * cgs;
   const float inv = 1.f / (float)(g.R * g.S);
@@ -151,21 +161,21 @@ avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, PoolGeom g) {
     for (int p = p_lo; p <= p_hi; ++p)
       for (int q = q_lo; q <= q_hi; ++q) {
         float d[VW];
-        PV<T>::load(dy + (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW, d);
+        PV<T, VEC>::load(dy + (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW, d);
 #pragma unroll
         for (int e = 0; e < VW; ++e) acc[e] += d[e];
       }
 #pragma unroll
     for (int e = 0; e < VW; ++e) acc[e] *= inv;
-    PV<T>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
+    PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
   }
 }
 
 // Global average pool: x[N, HW, C] -> y[N, C].  Block = (image, 256-thread slab of column groups x rows).
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 global_avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int HW, int C) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = C / VW;
   const int tpr = cgs < 256 ? cgs : 256;
   const int rpp = 256 / tpr;
@@ -178,7 +188,7 @@ global_avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int HW, in
   if (cg < cgs && rl < rpp)
     for (int r = rl; r < HW; r += rpp) {
       float v[VW];
-      PV<T>::load(x + ((long long)n * HW + r) * C + cg * VW, v);
+      PV<T, VEC>::load(x + ((long long)n * HW + r) * C + cg * VW, v);
 #pragma unroll
       for (int e = 0; e < VW; ++e) acc[e] += v[e];
     }
@@ -195,24 +205,24 @@ global_avgpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int HW, in
     const float inv = 1.f / (float)HW;
 #pragma unroll
     for (int e = 0; e < VW; ++e) acc[e] *= inv;
-    PV<T>::store(y + (long long)n * C + cg * VW, acc);
+    PV<T, VEC>::store(y + (long long)n * C + cg * VW, acc);
   }
 }
 
-template <typename T>
+template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 global_avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int HW, int C, long long total_vec) {
-  constexpr int VW = PV<T>::W;
+  constexpr int VW = PV<T, VEC>::W;
   const int cgs = C / VW;
   const float inv = 1.f / (float)HW;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec; i += (long long)gridDim.x * blockDim.x) {
     const int cg = (int)(i % cgs);
     const long long n = i / ((long long)cgs * HW);
     float d[VW];
-    PV<T>::load(dy + n * C + cg * VW, d);
+    PV<T, VEC>::load(dy + n * C + cg * VW, d);
 #pragma unroll
     for (int e = 0; e < VW; ++e) d[e] *= inv;
-    PV<T>::store(dx + i * VW, d);
+    PV<T, VEC>::store(dx + i * VW, d);
   }
 }
 
@@ -223,7 +233,8 @@ int pgrid(long long total) {
 }
 
 int make_geom(PoolGeom* g, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw, int vw) {
-  RNN_REQUIRE(N > 0 && H > 0 && W > 0 && C > 0 && C % vw == 0, RNN_ERR_SHAPE);
+  (void)vw;
+  RNN_REQUIRE(N > 0 && H > 0 && W > 0 && C > 0, RNN_ERR_SHAPE);
   RNN_REQUIRE(R > 0 && S > 0 && sh > 0 && sw > 0 && ph >= 0 && pw >= 0 && ph * 2 <= R && pw * 2 <= S, RNN_ERR_SHAPE);
   g->N = N; g->H = H; g->W = W; g->C = C; g->R = R; g->S = S; g->sh = sh; g->sw = sw; g->ph = ph; g->pw = pw;
   g->P = (H + 2 * ph - R) / sh + 1;
@@ -239,62 +250,103 @@ extern "C" {
 int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, int N, int H, int W, int C, int R, int S, int sh, int sw,
                       int ph, int pw, int is_f32, cudaStream_t stream) {
   PoolGeom g;
-  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, is_f32 ? 4 : 8);
+  const int vw = is_f32 ? 4 : 8;
+  const bool vec = C % vw == 0;
+  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * g.P * g.Q * (C / (is_f32 ? 4 : 8));
-  if (is_f32) maxpool_fwd_kernel<float><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, g);
-  else maxpool_fwd_kernel<bf16><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, g);
+  const long long total = (long long)N * g.P * g.Q * (vec ? C / vw : C);
+  if (is_f32) {
+    if (vec) maxpool_fwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, g);
+    else maxpool_fwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, g);
+  } else {
+    if (vec) maxpool_fwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, g);
+    else maxpool_fwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, g);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 int rnn_maxpool2d_bwd(const void* dy, const int* indices, void* dx, int N, int H, int W, int C, int R, int S, int sh,
                       int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
   PoolGeom g;
-  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, is_f32 ? 4 : 8);
+  const int vw = is_f32 ? 4 : 8;
+  const bool vec = C % vw == 0;
+  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * H * W * (C / (is_f32 ? 4 : 8));
-  if (is_f32) maxpool_bwd_kernel<float><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, (float*)dx, g);
-  else maxpool_bwd_kernel<bf16><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, (bf16*)dx, g);
+  const long long total = (long long)N * H * W * (vec ? C / vw : C);
+  if (is_f32) {
+    if (vec) maxpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, (float*)dx, g);
+    else maxpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, (float*)dx, g);
+  } else {
+    if (vec) maxpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, (bf16*)dx, g);
+    else maxpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, (bf16*)dx, g);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 int rnn_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
                       int is_f32, cudaStream_t stream) {
   PoolGeom g;
-  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, is_f32 ? 4 : 8);
+  const int vw = is_f32 ? 4 : 8;
+  const bool vec = C % vw == 0;
+  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * g.P * g.Q * (C / (is_f32 ? 4 : 8));
-  if (is_f32) avgpool_fwd_kernel<float><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, g);
-  else avgpool_fwd_kernel<bf16><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, g);
+  const long long total = (long long)N * g.P * g.Q * (vec ? C / vw : C);
+  if (is_f32) {
+    if (vec) avgpool_fwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, g);
+    else avgpool_fwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, g);
+  } else {
+    if (vec) avgpool_fwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, g);
+    else avgpool_fwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, g);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 int rnn_avgpool2d_bwd(const void* dy, void* dx, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
                       int is_f32, cudaStream_t stream) {
   PoolGeom g;
-  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, is_f32 ? 4 : 8);
+  const int vw = is_f32 ? 4 : 8;
+  const bool vec = C % vw == 0;
+  int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * H * W * (C / (is_f32 ? 4 : 8));
-  if (is_f32) avgpool_bwd_kernel<float><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, g);
-  else avgpool_bwd_kernel<bf16><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, g);
+  const long long total = (long long)N * H * W * (vec ? C / vw : C);
+  if (is_f32) {
+    if (vec) avgpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, g);
+    else avgpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, g);
+  } else {
+    if (vec) avgpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, g);
+    else avgpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, g);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 int rnn_global_avgpool_fwd(const void* x, void* y, int N, int HW, int C, int is_f32, cudaStream_t stream) {
   const int vw = is_f32 ? 4 : 8;
-  RNN_REQUIRE(N > 0 && HW > 0 && C > 0 && C % vw == 0, RNN_ERR_SHAPE);
-  const int cgs = C / vw, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
-  if (is_f32) global_avgpool_fwd_kernel<float><<<dim3(gx, N), 256, 0, stream>>>((const float*)x, (float*)y, HW, C);
-  else global_avgpool_fwd_kernel<bf16><<<dim3(gx, N), 256, 0, stream>>>((const bf16*)x, (bf16*)y, HW, C);
+  RNN_REQUIRE(N > 0 && HW > 0 && C > 0, RNN_ERR_SHAPE);
+  const bool vec = C % vw == 0;
+  const int cgs = vec ? C / vw : C, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
+  const dim3 grid(gx, N);
+  if (is_f32) {
+    if (vec) global_avgpool_fwd_kernel<float, true><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, HW, C);
+    else global_avgpool_fwd_kernel<float, false><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, HW, C);
+  } else {
+    if (vec) global_avgpool_fwd_kernel<bf16, true><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, HW, C);
+    else global_avgpool_fwd_kernel<bf16, false><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, HW, C);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 int rnn_global_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, int is_f32, cudaStream_t stream) {
   const int vw = is_f32 ? 4 : 8;
-  RNN_REQUIRE(N > 0 && HW > 0 && C > 0 && C % vw == 0, RNN_ERR_SHAPE);
-  const long long total = (long long)N * HW * (C / vw);
-  if (is_f32) global_avgpool_bwd_kernel<float><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, HW, C, total);
-  else global_avgpool_bwd_kernel<bf16><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, HW, C, total);
+  RNN_REQUIRE(N > 0 && HW > 0 && C > 0, RNN_ERR_SHAPE);
+  const bool vec = C % vw == 0;
+  const long long total = (long long)N * HW * (vec ? C / vw : C);
+  if (is_f32) {
+    if (vec) global_avgpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, HW, C, total);
+    else global_avgpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, (float*)dx, HW, C, total);
+  } else {
+    if (vec) global_avgpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, HW, C, total);
+    else global_avgpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, (bf16*)dx, HW, C, total);
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

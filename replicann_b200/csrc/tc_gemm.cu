@@ -24,7 +24,7 @@ constexpr int BM = 128;       // UMMA M (cta_group::1)
 constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
 constexpr int A_BYTES = BM * BK * 2;
 constexpr int NUM_THREADS = 192;
-constexpr int MAX_TAPS = 64;
+constexpr int MAX_TAPS = 128;
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
 
@@ -518,7 +518,9 @@ size_t rnn_gemm_bf16_workspace(int M, int N, int K, int out_f32, int has_epilogu
 int rnn_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, int a_mn, int b_mn,
                   const float* bias, int relu, int out_f32, void* ws, size_t ws_bytes, cudaStream_t stream) {
   RNN_REQUIRE(M > 0 && N > 0 && K > 0, RNN_ERR_SHAPE);
-  RNN_REQUIRE(N % 8 == 0 && K % 8 == 0 && (!a_mn || M % 8 == 0), RNN_ERR_SHAPE);
+  RNN_REQUIRE(N % 8 == 0, RNN_ERR_SHAPE);                       // 16-byte stores of D rows
+  RNN_REQUIRE(a_mn ? (M % 8 == 0) : (K % 8 == 0), RNN_ERR_SHAPE);  // 16-byte row pitch of A (TMA)
+  RNN_REQUIRE(b_mn ? true : (K % 8 == 0), RNN_ERR_SHAPE);          // 16-byte row pitch of B (TMA)
   RNN_REQUIRE(!(a_mn && !b_mn), RNN_ERR_SHAPE);  // (MN,K) combination is not instantiated
   int rc = load_driver_entry_points();
   if (rc != RNN_OK) return rc;

@@ -233,9 +233,9 @@ def tanh_bwd(dy, y):
     return dx
 
 
-def add(a, b):
+def add(a, b, out=None):
     lib = _lib.load(); _req(a, torch.bfloat16, "a"); _req(b, torch.bfloat16, "b")
-    y = torch.empty_like(a)
+    y = out if out is not None else torch.empty_like(a)
     check(lib.rnn_add_bf16(ptr(a), ptr(b), ptr(y), a.numel(), cur_stream()), "rnn_add_bf16")
     return y
 

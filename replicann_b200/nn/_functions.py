@@ -58,52 +58,65 @@ def _bias_f32(b):
 
 
 def _write_param_grad(p, compute):
-    """compute(out, accumulate) enqueues the kernel(s) that produce p's gradient."""
-    tgt, acc = grad_target(p)
-    compute(tgt, acc)
-    _notify(p)
+    """compute(out, accumulate) enqueues the kernel(s) that produce p's gradient.
+
+    Leaf parameters get the result written straight into `p.grad` (None is returned to autograd);
+    any other tensor (e.g. a padded copy of a parameter) gets a fresh gradient tensor back."""
+    if p.is_leaf:
+        tgt, acc = grad_target(p)
+        compute(tgt, acc)
+        _notify(p)
+        return None
+    out = torch.empty_like(p)
+    compute(out, False)
+    return out
 
 
 # ------------------------------------------------------------------------------------------ Conv2d
 class Conv2dFn(Function):
+    """y = [relu](conv2d(x, w) + bias)."""
+
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad):
+    def forward(ctx, x, weight, bias, stride, pad, relu=False):
         xh = nhwc(x)
         wk = nhwc(weight)  # [K,C,R,S] channels_last -> KRSC
-        ctx.stride, ctx.pad = stride, pad
-        ctx.has_bias = bias is not None
+        ctx.stride, ctx.pad, ctx.relu = stride, pad, relu
         if weight.dtype == torch.float32:
             y = RF.conv2d_fprop_f32(xh, wk, bias.detach() if bias is not None else None, stride=stride, pad=pad)
+            if relu:
+                y = RF.relu_fwd(y)
         else:
-            y = RF.conv2d_fprop(xh, wk, stride=stride, pad=pad, shift=_bias_f32(bias))
-        ctx.save_for_backward(xh, weight, bias)
+            y = RF.conv2d_fprop(xh, wk, stride=stride, pad=pad, shift=_bias_f32(bias), relu=relu)
+        ctx.save_for_backward(xh, weight, bias, y if relu else None)
         return nchw(y)
 
     @staticmethod
     def backward(ctx, dy):
-        xh, weight, bias = ctx.saved_tensors
+        xh, weight, bias, y = ctx.saved_tensors
         wk = nhwc(weight)
         dyh = nhwc(dy)
+        if ctx.relu:
+            dyh = RF.relu_bwd(dyh, y)
         stride, pad = ctx.stride, ctx.pad
         f32 = weight.dtype == torch.float32
-        if weight.requires_grad:
+        dw = db = dx = None
+        if ctx.needs_input_grad[1]:
             def wg(out, acc):
                 o = nhwc_param_view(out)
                 if f32:
                     RF.conv2d_wgrad_f32(xh, dyh, tuple(wk.shape), stride=stride, pad=pad, out=o, accumulate=acc)
                 else:
                     RF.conv2d_wgrad(xh, dyh, tuple(wk.shape), stride=stride, pad=pad, out=o, accumulate=acc)
-            _write_param_grad(weight, wg)
-        if bias is not None and bias.requires_grad:
+            dw = _write_param_grad(weight, wg)
+        if bias is not None and ctx.needs_input_grad[2]:
             K = dyh.shape[-1]
-            _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
-        dx = None
+            db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
         if ctx.needs_input_grad[0]:
             if f32:
                 dx = nchw(RF.conv2d_dgrad_f32(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
             else:
                 dx = nchw(RF.conv2d_dgrad(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
-        return dx, None, None, None, None
+        return dx, dw, db, None, None, None
 
 
 def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
@@ -140,25 +153,26 @@ class LinearFn(Function):
         if ctx.relu:
             dy2 = RF.relu_bwd(dy2, y)
         f32 = weight.dtype == torch.float32
-        if weight.requires_grad:
+        dw = db = dx = None
+        if ctx.needs_input_grad[1]:
             def wg(out, acc):
                 if f32:
                     RF.gemm_f32(dy2, x2, a_mn=True, b_mn=True, out=out, accumulate=acc)
+                elif not acc:
+                    RF.gemm(dy2, x2, a_mn=True, b_mn=True, out=out)
                 else:
-                    g = RF.gemm(dy2, x2, a_mn=True, b_mn=True, out=None if acc else out)
-                    if acc:
-                        out.copy_(RF.add(out, g))
-            _write_param_grad(weight, wg)
-        if bias is not None and bias.requires_grad:
-            _write_param_grad(bias, lambda out, acc: RF.colsum(dy2, out=out, accumulate=acc))
-        dx = None
+                    g = RF.gemm(dy2, x2, a_mn=True, b_mn=True)
+                    RF.add(out, g, out=out)
+            dw = _write_param_grad(weight, wg)
+        if bias is not None and ctx.needs_input_grad[2]:
+            db = _write_param_grad(bias, lambda out, acc: RF.colsum(dy2, out=out, accumulate=acc))
         if ctx.needs_input_grad[0]:
             if f32:
                 dx = RF.gemm_f32(dy2, weight.detach(), b_mn=True)
             else:
                 dx = RF.gemm(dy2, weight.detach(), b_mn=True)
             dx = dx.reshape(ctx.xshape)
-        return dx, None, None, None
+        return dx, dw, db, None
 
 
 # ------------------------------------------------------------------------------------------ BatchNorm2d

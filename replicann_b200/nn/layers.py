@@ -30,14 +30,12 @@ class Conv2d(nn.Module):
     """
 
     def __init__(self, in_channels: int, out_channels: int, kernel_size, stride=1, padding=0, *,
-                 bias: bool = True, device=None, dtype=None) -> None:
+                 bias: bool = True, relu: bool = False, device=None, dtype=None) -> None:
         super().__init__()
         kh, kw = _pair(kernel_size)
         sh, sw = _pair(stride)
         ph, pw = _pair(padding)
-        if (sh, ph) != (sw, pw) and False:
-            raise ValueError("unreachable")
-        self._stride, self._padding, self._kernel = (sh, sw), (ph, pw), (kh, kw)
+        self._stride, self._padding, self._kernel, self._relu = (sh, sw), (ph, pw), (kh, kw), relu
         w = torch.empty((out_channels, in_channels, kh, kw), device=device, dtype=dtype)
         w = w.contiguous(memory_format=torch.channels_last)
         self.weight = nn.Parameter(w)
@@ -82,7 +80,7 @@ class Conv2d(nn.Module):
     def forward(self, x: Tensor, /) -> Tensor:
         if x.shape[1] != self.in_channels:
             raise ValueError(f"expected {self.in_channels} input channels, got {x.shape[1]}")
-        return Fn.Conv2dFn.apply(x, self.weight, self.bias, self._stride, self._padding)
+        return Fn.Conv2dFn.apply(x, self.weight, self.bias, self._stride, self._padding, self._relu)
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self._kernel}, stride={self._stride}, "

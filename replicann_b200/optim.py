@@ -1,0 +1,142 @@
+"""Fused optimizers over flat parameter buckets (torch.optim.SGD / AdamW semantics).
+
+All parameters of one dtype live in one flat buffer; `.data` and `.grad` of every parameter are views into
+it (laid out in REVERSE registration order, so gradients complete front-to-back during backward and
+data-parallel buckets are contiguous ranges).  bf16 parameters additionally have an fp32 master copy that
+the update kernel reads and writes together with the bf16 working copy (18 B/param for SGD-momentum).
+The reference has no optimizer or training step; semantics follow torch.optim.
+"""
+from __future__ import annotations
+
+from typing import Iterable
+
+import torch
+
+from . import functional as RF
+
+_ALIGN = 8  # elements: keeps every parameter 16-byte aligned in bf16 (TMA base-address requirement)
+
+
+class _FlatGroup:
+    """One dtype's parameters flattened: work (param dtype), grad (param dtype), master/state (fp32)."""
+
+    def __init__(self, params: list[torch.nn.Parameter]):
+        self.params = params
+        dev, dt = params[0].device, params[0].dtype
+        self.dtype = dt
+        self.offsets = []
+        off = 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
+        self.numel = off
+        self.work = torch.zeros(off, dtype=dt, device=dev)
+        self.grad = torch.zeros(off, dtype=dt, device=dev)
+        for p, o in zip(params, self.offsets):
+            n = p.numel()
+            self._view(self.work, p, o).copy_(p.data)
+            p.data = self._view(self.work, p, o)
+            p.grad = self._view(self.grad, p, o)
+            p._rnn_fresh = True
+            p._rnn_group = self
+            p._rnn_offset = o
+        self.master = self.work if dt == torch.float32 else self.work.float()
+        self.state: dict[str, torch.Tensor] = {}
+
+    @staticmethod
+    def _view(flat: torch.Tensor, p: torch.Tensor, off: int) -> torch.Tensor:
+        n = p.numel()
+        seg = flat[off:off + n]
+        if p.dim() == 4:  # conv filter: logical [K,C,R,S], memory KRSC (channels_last)
+            K, Cn, R, S = p.shape
+            return seg.view(K, R, S, Cn).permute(0, 3, 1, 2)
+        return seg.view(p.shape)
+
+    def zeros_state(self, name: str) -> torch.Tensor:
+        if name not in self.state:
+            self.state[name] = torch.zeros(self.numel, dtype=torch.float32, device=self.work.device)
+        return self.state[name]
+
+
+class _FlatOptimizer:
+    def __init__(self, params: Iterable[torch.nn.Parameter]):
+        plist = [p for p in params if p.requires_grad]
+        if not plist:
+            raise ValueError("optimizer got an empty parameter list")
+        if not all(p.is_cuda for p in plist):
+            raise RuntimeError("replicann_b200 optimizers update CUDA parameters only (no CPU path)")
+        plist = plist[::-1]  # reverse registration order ~ order in which backward produces gradients
+        by_dtype: dict[torch.dtype, list] = {}
+        for p in plist:
+            by_dtype.setdefault(p.dtype, []).append(p)
+        self.groups = [_FlatGroup(ps) for ps in by_dtype.values()]
+        self.grad_scale = 1.0  # set by DataParallel to 1/world_size (all-reduce sums)
+        self._steps = 0
+
+    @property
+    def flat_grads(self) -> list[torch.Tensor]:
+        return [g.grad for g in self.groups]
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        """No memset: the next gradient kernel of each parameter overwrites instead of accumulating."""
+        for g in self.groups:
+            for p in g.params:
+                p._rnn_fresh = True
+
+    def state_dict(self) -> dict:
+        return {"steps": self._steps,
+                "groups": [{"master": g.master.clone(), **{k: v.clone() for k, v in g.state.items()}}
+                           for g in self.groups]}
+
+    def load_state_dict(self, sd: dict) -> None:
+        self._steps = sd["steps"]
+        for g, s in zip(self.groups, sd["groups"]):
+            g.master.copy_(s["master"])
+            for k, v in s.items():
+                if k != "master":
+                    g.zeros_state(k).copy_(v)
+            if g.master is not g.work:
+                RF.cast_f32_to_bf16(g.master, out=g.work)
+
+    def sync_master_from_params(self) -> None:
+        """Call after load_state_dict() on the model: refresh the fp32 master copies from the weights."""
+        for g in self.groups:
+            if g.master is not g.work:
+                RF.cast_bf16_to_f32(g.work, out=g.master)
+
+
+class SGD(_FlatOptimizer):
+    def __init__(self, params, lr: float, *, momentum: float = 0.0, dampening: float = 0.0,
+                 weight_decay: float = 0.0, nesterov: bool = False) -> None:
+        super().__init__(params)
+        if nesterov and (momentum <= 0 or dampening != 0):
+            raise ValueError("Nesterov momentum requires a momentum and zero dampening")
+        self.lr, self.momentum, self.dampening = lr, momentum, dampening
+        self.weight_decay, self.nesterov = weight_decay, nesterov
+
+    @torch.no_grad()
+    def step(self) -> None:
+        first = self._steps == 0
+        for g in self.groups:
+            buf = g.zeros_state("momentum_buffer") if self.momentum != 0 else None
+            wcopy = None if g.master is g.work else g.work
+            RF.sgd_step(g.master, buf, g.grad, wcopy, lr=self.lr, momentum=self.momentum, dampening=self.dampening,
+                        weight_decay=self.weight_decay, nesterov=self.nesterov, first_step=first,
+                        grad_scale=self.grad_scale)
+        self._steps += 1
+
+
+class AdamW(_FlatOptimizer):
+    def __init__(self, params, lr: float = 1e-3, *, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 1e-2) -> None:
+        super().__init__(params)
+        self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+
+    @torch.no_grad()
+    def step(self) -> None:
+        self._steps += 1
+        for g in self.groups:
+            wcopy = None if g.master is g.work else g.work
+            RF.adamw_step(g.master, g.zeros_state("exp_avg"), g.zeros_state("exp_avg_sq"), g.grad, wcopy, lr=self.lr,
+                          betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step=self._steps,
+                          grad_scale=self.grad_scale)

@@ -48,6 +48,7 @@ GEMM_CASES = {
     "gemm_kk_f32": (256, 128, 256, False, False, False, False, True),
     "gemm_kk_splitk": (128, 256, 8192, False, False, True, False, False),
     "gemm_kk_big": (2048, 2048, 2048, False, False, False, False, False),
+    "gemm_kk_multitile": (8192, 1024, 256, False, False, False, False, False),
     "gemm_kmn_256": (256, 256, 512, False, True, False, False, False),
     "gemm_kmn_ragged": (200, 136, 72, False, True, False, False, False),
     "gemm_mnmn_256": (256, 256, 512, True, True, False, False, False),
@@ -87,6 +88,10 @@ CONV_CASES = {
     "conv_7x7_s2": (2, 32, 32, 64, 64, 7, 7, 2, 3),
     "conv_3x3_odd": (2, 7, 7, 128, 64, 3, 3, 2, 1),
     "conv_5x5_p2_k192": (2, 27, 27, 64, 192, 5, 5, 1, 2),
+    # more tiles than SMs: every CTA walks several tiles (accumulator double-buffering, ring wrap-around)
+    "conv_3x3_multitile": (16, 56, 56, 64, 64, 3, 3, 1, 1),
+    "conv_1x1_multitile_k256": (16, 56, 56, 64, 256, 1, 1, 1, 0),
+    "conv_3x3_s2_multitile": (32, 56, 56, 128, 128, 3, 3, 2, 1),
 }
 
 
