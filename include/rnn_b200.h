@@ -44,6 +44,8 @@ typedef enum {
 const char* rnn_last_error(void);
 int rnn_version(void);
 int rnn_sm_count(void); /* SMs of the current device (148 on B200) */
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+unsigned long long rnn_launch_count(void);
 
 /* ---- tensor-core contractions (tcgen05 + TMEM + TMA) -------------------------------------- */
 

@@ -64,9 +64,10 @@ def parse_header(path: os.PathLike | None = None) -> dict:
     text = re.sub(r"/\*.*?\*/", " ", text, flags=re.S)
     text = re.sub(r"//[^\n]*", " ", text)
     sigs = {}
-    for m in re.finditer(r"(const char\s*\*|size_t|int)\s+(rnn_\w+)\s*\(([^;{}]*?)\)\s*;", text, flags=re.S):
+    for m in re.finditer(r"(const char\s*\*|size_t|unsigned long long|int)\s+(rnn_\w+)\s*\(([^;{}]*?)\)\s*;", text, flags=re.S):
         ret, name, args = m.group(1), m.group(2), m.group(3).strip()
-        restype = C.c_char_p if "char" in ret else (C.c_size_t if ret == "size_t" else C.c_int)
+        restype = (C.c_char_p if "char" in ret else C.c_size_t if ret == "size_t"
+                   else C.c_ulonglong if "long long" in ret else C.c_int)
         argtypes = [] if args in ("", "void") else [_ctype(a.strip()) for a in args.split(",")]
         sigs[name] = (restype, argtypes)
     return sigs

@@ -4,7 +4,6 @@ from __future__ import annotations
 
 import torch
 from torch import Tensor
-from torch.autograd import Function
 
 from .. import functional as RF
 from ..nn import _functions as Fn
@@ -28,28 +27,3 @@ def prepare_input(x: Tensor, weight_dtype, cpad: int = STEM_CPAD) -> Tensor:
     if x.dtype != torch.float32:
         raise TypeError(f"fp32 model got input of dtype {x.dtype}")
     return x
-
-
-class PadFilterFn(Function):
-    """[K, C, R, S] filter -> [K, Cpad, R, S] (channels_last) with zeros in the added channels."""
-
-    @staticmethod
-    def forward(ctx, w, cpad):
-        K, Cn, R, S = w.shape
-        out = torch.zeros((K, cpad, R, S), dtype=w.dtype, device=w.device).contiguous(memory_format=torch.channels_last)
-        out[:, :Cn].copy_(w)
-        ctx.c = Cn
-        return out
-
-    @staticmethod
-    def backward(ctx, g):
-        return g[:, :ctx.c].contiguous(memory_format=torch.channels_last), None
-
-
-def stem_conv(x: Tensor, conv, relu: bool = False) -> Tensor:
-    """First convolution of a bf16 CNN on a channel-padded input; fp32 models call the layer directly."""
-    w = conv.weight
-    if w.dtype == torch.bfloat16 and x.shape[1] != w.shape[1]:
-        wp = PadFilterFn.apply(w, x.shape[1])
-        return Fn.Conv2dFn.apply(x, wp, conv.bias, conv.stride, conv.padding, relu)
-    return Fn.Conv2dFn.apply(x, w, conv.bias, conv.stride, conv.padding, relu)

@@ -7,7 +7,7 @@ import torch.nn as nn
 from torch import Tensor
 
 from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d
-from ._stem import prepare_input, stem_conv
+from ._stem import prepare_input
 
 
 class AlexNet(nn.Module):
@@ -35,7 +35,7 @@ class AlexNet(nn.Module):
 
     def forward(self, x: Tensor, /) -> Tensor:
         x = prepare_input(x, self._conv1.weight.dtype)
-        x = self._pool1(stem_conv(x, self._conv1, relu=True))
+        x = self._pool1(self._conv1(x))
         x = self._pool2(self._conv2(x))
         x = self._conv5(self._conv4(self._conv3(x)))
         x = self._flatten(self._avgpool(self._pool5(x)))

@@ -10,7 +10,7 @@ import torch.nn as nn
 from torch import Tensor
 
 from ..nn.layers import AdaptiveAvgPool2d, BatchNorm2d, Conv2d, Linear, MaxPool2d
-from ._stem import prepare_input, stem_conv
+from ._stem import prepare_input
 
 
 class _Bottleneck(nn.Module):
@@ -96,7 +96,7 @@ class ResNet(nn.Module):
 
     def forward(self, x: Tensor, /) -> Tensor:
         x = prepare_input(x, self._conv1.weight.dtype)
-        x = self._bn1(stem_conv(x, self._conv1))
+        x = self._bn1(self._conv1(x))
         x = self._maxpool(x)
         for stage in self._stages:
             x = stage(x)

@@ -6,7 +6,7 @@ import torch.nn as nn
 from torch import Tensor
 
 from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d
-from ._stem import prepare_input, stem_conv
+from ._stem import prepare_input
 
 _CFG_D = (64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M")
 
@@ -38,8 +38,7 @@ class VGG(nn.Module):
     def forward(self, x: Tensor, /) -> Tensor:
         first = self._features[0]
         x = prepare_input(x, first.weight.dtype)
-        x = stem_conv(x, first, relu=True)
-        for layer in list(self._features)[1:]:
+        for layer in self._features:
             x = layer(x)
         x = self._flatten(self._avgpool(x))
         x = self._drop1(self._fc1(x))

@@ -12,6 +12,7 @@
 
 #define RNN_CHECK_LAUNCH()                                   \
   do {                                                       \
+    rnn_count_launch();                                      \
     cudaError_t e__ = cudaGetLastError();                    \
     if (e__ != cudaSuccess) {                                \
       rnn_set_last_error(__FILE__, __LINE__, e__);           \
@@ -39,6 +40,7 @@
 void rnn_set_last_error(const char* file, int line, cudaError_t e);
 void rnn_set_last_message(const char* file, int line, const char* msg);
 int rnn_num_sms();
+void rnn_count_launch();
 
 typedef __nv_bfloat16 bf16;
 

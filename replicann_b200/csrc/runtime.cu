@@ -1,11 +1,16 @@
 // Error reporting and device queries shared by every kernel file.
 #include <string.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace {
 thread_local char g_err[512] = "no error";
+std::atomic<unsigned long long> g_launches{0};
 }
+
+void rnn_count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 void rnn_set_last_error(const char* file, int line, cudaError_t e) {
   const char* base = strrchr(file, '/');
@@ -33,4 +38,5 @@ extern "C" {
 const char* rnn_last_error(void) { return g_err; }
 int rnn_version(void) { return 100; }
 int rnn_sm_count(void) { return rnn_num_sms(); }
+unsigned long long rnn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 }

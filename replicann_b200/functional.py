@@ -12,6 +12,39 @@ from ._lib import check, conv_desc, cur_stream, ptr
 
 _workspaces: dict[int, torch.Tensor] = {}
 
+# Optional per-call device timing used by bench.py: when `_profile` is a list, every instrumented wrapper
+# appends (kind, algorithmic_bytes_or_None, start_event, end_event) recorded on the launching stream.
+_profile: list | None = None
+
+
+def set_profile(sink: list | None) -> None:
+    global _profile
+    _profile = sink
+
+
+class _span:
+    __slots__ = ("kind", "work", "e0")
+
+    def __init__(self, kind: str, work=None):
+        self.kind, self.work, self.e0 = kind, work, None
+
+    def __enter__(self):
+        if _profile is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if self.e0 is not None and _profile is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            _profile.append((self.kind, self.work, self.e0, e1))
+        return False
+
+
+def launch_count() -> int:
+    return int(_lib.load().rnn_launch_count())
+
 
 def workspace(nbytes: int, device) -> torch.Tensor | None:
     """Grow-only per-device scratch buffer (torch caching allocator owns the memory)."""
@@ -56,8 +89,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         _req(bias, torch.float32, "bias")
     nbytes = lib.rnn_gemm_bf16_workspace(M, N, K, int(out_f32), int(bias is not None or relu))
     ws = workspace(nbytes, a.device)
-    check(lib.rnn_gemm_bf16(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
-                            int(out_f32), ptr(ws), nbytes, cur_stream()), "rnn_gemm_bf16")
+    with _span("tc_gemm", 2.0 * M * N * K):
+        check(lib.rnn_gemm_bf16(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
+                                int(out_f32), ptr(ws), nbytes, cur_stream()), "rnn_gemm_bf16")
     return d
 
 
@@ -70,6 +104,10 @@ def _cdesc(x_shape, w_shape, stride, pad):
     return conv_desc(N, H, W, Cin, K, R, S, stride, pad)
 
 
+def _conv_flops(d) -> float:
+    return 2.0 * d.N * d.P * d.Q * d.K * d.C * d.R * d.S
+
+
 def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None, relu=False):
     """x [N,H,W,C] bf16, w [K,R,S,C] bf16 -> y [N,P,Q,K] bf16."""
     lib = _lib.load()
@@ -79,8 +117,9 @@ def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None
     y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x.device)
     if residual is not None:
         _req(residual, torch.bfloat16, "residual")
-    check(lib.rnn_conv2d_fprop_bf16(d, ptr(x), ptr(w), ptr(y), ptr(scale), ptr(shift), ptr(residual), int(relu),
-                                    cur_stream()), "rnn_conv2d_fprop_bf16")
+    with _span("tc_conv_fprop", _conv_flops(d)):
+        check(lib.rnn_conv2d_fprop_bf16(d, ptr(x), ptr(w), ptr(y), ptr(scale), ptr(shift), ptr(residual),
+                                        int(relu), cur_stream()), "rnn_conv2d_fprop_bf16")
     return y
 
 
@@ -92,8 +131,9 @@ def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False)
     if tuple(dy.shape) != (d.N, d.P, d.Q, d.K):
         raise ValueError(f"dy shape {tuple(dy.shape)} != {(d.N, d.P, d.Q, d.K)}")
     dx = out if out is not None else torch.empty(tuple(x_shape), dtype=torch.bfloat16, device=dy.device)
-    check(lib.rnn_conv2d_dgrad_bf16(d, ptr(dy), ptr(w), ptr(dx), int(accumulate), cur_stream()),
-          "rnn_conv2d_dgrad_bf16")
+    with _span("tc_conv_dgrad", _conv_flops(d)):
+        check(lib.rnn_conv2d_dgrad_bf16(d, ptr(dy), ptr(w), ptr(dx), int(accumulate), cur_stream()),
+              "rnn_conv2d_dgrad_bf16")
     return dx
 
 
@@ -105,8 +145,9 @@ def conv2d_wgrad(x, dy, w_shape, *, stride=1, pad=0, out=None, accumulate=False,
     dw = out if out is not None else torch.empty(tuple(w_shape), dtype=out_dtype, device=x.device)
     nbytes = lib.rnn_conv2d_wgrad_workspace(d)
     ws = workspace(nbytes, x.device)
-    check(lib.rnn_conv2d_wgrad_bf16(d, ptr(x), ptr(dy), ptr(dw), int(dw.dtype == torch.float32), int(accumulate),
-                                    ptr(ws), nbytes, cur_stream()), "rnn_conv2d_wgrad_bf16")
+    with _span("tc_conv_wgrad", _conv_flops(d)):
+        check(lib.rnn_conv2d_wgrad_bf16(d, ptr(x), ptr(dy), ptr(dw), int(dw.dtype == torch.float32),
+                                        int(accumulate), ptr(ws), nbytes, cur_stream()), "rnn_conv2d_wgrad_bf16")
     return dw
 
 
@@ -279,9 +320,10 @@ def bn_stats(x2d, gamma, beta, eps, momentum, running_mean, running_var):
     st = torch.empty((4, Cn), dtype=torch.float32, device=x2d.device)
     nbytes = lib.rnn_bn_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
-    check(lib.rnn_bn_stats_bf16(ptr(x2d), M, Cn, ptr(gamma), ptr(beta), float(eps), float(momentum),
+    with _span("bn_stats", 2.0 * M * Cn):
+      check(lib.rnn_bn_stats_bf16(ptr(x2d), M, Cn, ptr(gamma), ptr(beta), float(eps), float(momentum),
                                 ptr(running_mean), ptr(running_var), ptr(st[0]), ptr(st[1]), ptr(st[2]), ptr(st[3]),
-                                ptr(ws), nbytes, cur_stream()), "rnn_bn_stats_bf16")
+                                  ptr(ws), nbytes, cur_stream()), "rnn_bn_stats_bf16")
     return st[0], st[1], st[2], st[3]
 
 
@@ -298,8 +340,9 @@ def bn_apply(x2d, scale, shift, residual=None, relu=False):
     lib = _lib.load(); _req(x2d, torch.bfloat16, "x")
     M, Cn = x2d.shape
     y = torch.empty_like(x2d)
-    check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), M, Cn,
-                                cur_stream()), "rnn_bn_apply_bf16")
+    with _span("bn_apply", 2.0 * M * Cn * (3 if residual is not None else 2)):
+        check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), M, Cn,
+                                    cur_stream()), "rnn_bn_apply_bf16")
     return y
 
 
@@ -311,10 +354,12 @@ def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, a
     sums = torch.empty((2, Cn), dtype=torch.float32, device=x2d.device)
     nbytes = lib.rnn_bn_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
-    check(lib.rnn_bn_bwd_bf16(ptr(dy2d), ptr(x2d), ptr(y_out), ptr(mean), ptr(invstd), ptr(gamma), M, Cn, ptr(dx),
-                              ptr(dres), ptr(dgamma), ptr(dbeta), _is_f32(dgamma) if dgamma is not None else 1,
-                              int(accumulate), ptr(sums[0]), ptr(sums[1]), ptr(ws), nbytes, cur_stream()),
-          "rnn_bn_bwd_bf16")
+    nread = 2 + (1 if y_out is not None else 0)
+    with _span("bn_bwd", 2.0 * M * Cn * (2 * nread + 1 + (1 if want_dres else 0))):
+        check(lib.rnn_bn_bwd_bf16(ptr(dy2d), ptr(x2d), ptr(y_out), ptr(mean), ptr(invstd), ptr(gamma), M, Cn,
+                                  ptr(dx), ptr(dres), ptr(dgamma), ptr(dbeta),
+                                  _is_f32(dgamma) if dgamma is not None else 1, int(accumulate), ptr(sums[0]),
+                                  ptr(sums[1]), ptr(ws), nbytes, cur_stream()), "rnn_bn_bwd_bf16")
     return dx, dres
 
 

@@ -119,6 +119,23 @@ class Conv2dFn(Function):
         return dx, dw, db, None, None, None
 
 
+class PadFilterFn(Function):
+    """[K, C, R, S] filter -> [K, Cpad, R, S] (channels_last) with zeros in the added input channels: lets a
+    3-channel first layer ride the 64-channel K step of the tensor-core kernel on a channel-padded input."""
+
+    @staticmethod
+    def forward(ctx, w, cpad):
+        K, Cn, R, S = w.shape
+        out = torch.zeros((K, cpad, R, S), dtype=w.dtype, device=w.device).contiguous(memory_format=torch.channels_last)
+        out[:, :Cn].copy_(w)
+        ctx.c = Cn
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g[:, :ctx.c].contiguous(memory_format=torch.channels_last), None
+
+
 def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
     """KRSC buffer behind a [K,C,R,S] gradient tensor; it must already be channels_last (no copy allowed,
     the kernel writes through it)."""

@@ -25,8 +25,8 @@ def _pair(v):
 class Conv2d(nn.Module):
     """torch.nn.Conv2d(in, out, k, stride, padding, bias) -- groups=1, dilation=1, zeros padding.
 
-    bf16 weights run the tcgen05 implicit-GEMM kernels (in_channels % 64 == 0; the input may carry
-    zero-padded extra channels, see `padded_in_channels`); fp32 weights run the fp32 direct kernels.
+    bf16 weights run the tcgen05 implicit-GEMM kernels (input channels % 64 == 0; a first layer with
+    fewer channels takes a zero-padded input, see arch/_stem.py); fp32 weights run the fp32 direct kernels.
     """
 
     def __init__(self, in_channels: int, out_channels: int, kernel_size, stride=1, padding=0, *,
@@ -78,9 +78,14 @@ class Conv2d(nn.Module):
         return self._padding
 
     def forward(self, x: Tensor, /) -> Tensor:
+        w = self.weight
         if x.shape[1] != self.in_channels:
-            raise ValueError(f"expected {self.in_channels} input channels, got {x.shape[1]}")
-        return Fn.Conv2dFn.apply(x, self.weight, self.bias, self._stride, self._padding, self._relu)
+            # a channel-padded input (see arch/_stem.prepare_input): zero-pad the filter to match
+            if w.dtype == torch.bfloat16 and x.shape[1] > self.in_channels:
+                w = Fn.PadFilterFn.apply(w, x.shape[1])
+            else:
+                raise ValueError(f"expected {self.in_channels} input channels, got {x.shape[1]}")
+        return Fn.Conv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu)
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self._kernel}, stride={self._stride}, "
