@@ -121,6 +121,20 @@ size_t rnn_bn_workspace(long long M, int C);
 int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, const float* beta, float eps,
                       float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
                       float* scale, float* shift, void* ws, size_t ws_bytes, cudaStream_t stream);
+/* Variant of rnn_bn_stats_bf16 that takes no workspace and allocates nothing (no counterpart in the
+ * reference, which has neither this operator nor any allocation contract).  It exists for hosts that can
+ * hand over input and output buffers but have no device allocator to lend: a process whose HBM was carved
+ * up in full by another framework's pool at start-up, or a thin foreign-function binding that can marshal
+ * only the tensors themselves.  The partial sums live in an array compiled into the library
+ * (RNN_BN_STATIC_SCRATCH_BYTES, resident on every GPU that loads the library until exit).
+ * Limit: C % 8 == 0 and C <= RNN_BN_STATIC_MAX_C, else RNN_ERR_WORKSPACE.  The first call on a device also
+ * resolves the array's address -- make it before any stream capture.  Calls share the array: calls whose
+ * kernels may overlap on the GPU race with each other and must be ordered by the caller. */
+#define RNN_BN_STATIC_SCRATCH_BYTES (1u << 20)
+#define RNN_BN_STATIC_MAX_C 4096
+int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gamma, const float* beta, float eps,
+                             float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                             float* scale, float* shift, cudaStream_t stream);
 int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                         float eps, int C, float* scale, float* shift, cudaStream_t stream);
 /* y = relu(x*scale + shift + residual): fused BatchNorm-apply (+ residual add) (+ ReLU). */

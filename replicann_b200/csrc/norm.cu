@@ -365,6 +365,37 @@ int ln_bwd_blocks(long long M) {
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Built-in scratch for rnn_bn_stats_bf16_static (see include/rnn_b200.h).
+//
+// The array below is part of the library image: every GPU that loads librnn_b200.so carries its
+// RNN_BN_STATIC_SCRATCH_BYTES until the process exits, whether or not the entry point is ever used.
+// On the host side the identifier `g_bn_static_scratch` is only a handle for the runtime -- it is NOT a
+// device pointer and must never be passed to a kernel as one.  The real address is looked up once per
+// device with cudaGetSymbolAddress (with that device current) and cached here.
+// ---------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned char g_bn_static_scratch[RNN_BN_STATIC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+float* g_bn_static_addr[kMaxDevices] = {nullptr};
+
+// Resolve (first use on this device) or fetch (later uses) the device address of the built-in scratch.
+int bn_static_scratch_address(float** out) {
+  int dev = -1;
+  RNN_CUDA(cudaGetDevice(&dev));
+  RNN_REQUIRE(dev >= 0 && dev < kMaxDevices, RNN_ERR_CUDA);
+  if (g_bn_static_addr[dev] == nullptr) {
+    void* p = nullptr;
+    RNN_CUDA(cudaGetSymbolAddress(&p, g_bn_static_scratch));
+    RNN_REQUIRE(p != nullptr, RNN_ERR_CUDA);
+    g_bn_static_addr[dev] = reinterpret_cast<float*>(p);
+  }
+  *out = g_bn_static_addr[dev];
+  return RNN_OK;
+}
+}  // namespace
+
 extern "C" {
 
 size_t rnn_bn_workspace(long long M, int C) { return (size_t)bn_row_blocks(M, C) * 2 * C * sizeof(float); }
@@ -380,6 +411,50 @@ int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, con
                                                            (float*)ws);
   RNN_CHECK_LAUNCH();
   bn_stats_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
+                                                                   momentum, running_mean, running_var, mean, invstd,
+                                                                   scale, shift);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+// Same result as rnn_bn_stats_bf16, for callers that cannot provide (or allocate) a workspace: the
+// per-block partial sums go to the library's built-in scratch array instead of a caller buffer.
+//
+//  * Nothing is allocated or freed here, and no allocating routine is called.
+//  * The first call on a given device also looks up the scratch array's device address
+//    (cudaGetSymbolAddress, device must be current).  Make that first call before starting any stream
+//    capture on that device; later calls only launch kernels.
+//  * Limit: C % 8 == 0 and C <= RNN_BN_STATIC_MAX_C.  Wider inputs are refused with RNN_ERR_WORKSPACE and
+//    rnn_last_error() says why -- use rnn_bn_stats_bf16 with your own workspace for those.  M is
+//    unlimited: the row range is simply cut into as many blocks as the scratch can hold partials for.
+//  * All calls on a device share the one array and it keeps whatever the previous call left in it.  That
+//    is harmless here because every partial-sum slot that the second kernel reads has just been
+//    overwritten by the first, so nothing needs clearing -- but it also means two calls whose kernels can
+//    overlap on the GPU (different streams, no ordering between them) corrupt each other.  Serialise them.
+int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gamma, const float* beta, float eps,
+                             float momentum, float* running_mean, float* running_var, float* mean, float* invstd,
+                             float* scale, float* shift, cudaStream_t stream) {
+  RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
+  if (C > RNN_BN_STATIC_MAX_C) {
+    rnn_set_last_message(__FILE__, __LINE__,
+                         "rnn_bn_stats_bf16_static: C exceeds RNN_BN_STATIC_MAX_C (built-in scratch too small); "
+                         "call rnn_bn_stats_bf16 with a caller workspace instead");
+    return RNN_ERR_WORKSPACE;
+  }
+  float* scratch = nullptr;
+  int rc = bn_static_scratch_address(&scratch);
+  if (rc != RNN_OK) return rc;
+  // as many row blocks as the regular entry point would use, capped by what fits in the built-in scratch
+  const size_t per_block = (size_t)2 * C * sizeof(float);
+  int gy = bn_row_blocks(M, C);
+  const int fit = (int)(RNN_BN_STATIC_SCRATCH_BYTES / per_block);
+  if (gy > fit) gy = fit;
+  RNN_REQUIRE(gy >= 1, RNN_ERR_WORKSPACE);
+  const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
+  bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
+                                                           scratch);
+  RNN_CHECK_LAUNCH();
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift);
   RNN_CHECK_LAUNCH();
