@@ -242,9 +242,21 @@ def run_gpu(args) -> None:
 
     # per-kernel-family device time inside the timed region
     fam: dict[str, list] = {}
-    for kind, work, a, b in prof:
+    detail: dict[tuple, list] = {}
+    for kind, work, a, b, tag in prof:
+        el = a.elapsed_time(b)
         d = fam.setdefault(kind, [0.0, 0.0, 0])
-        d[0] += a.elapsed_time(b); d[1] += (work or 0.0); d[2] += 1
+        d[0] += el; d[1] += (work or 0.0); d[2] += 1
+        dd = detail.setdefault((kind, tag), [0.0, 0.0, 0])
+        dd[0] += el; dd[1] += (work or 0.0); dd[2] += 1
+    if args.detail and rank == 0:
+        with open(args.detail, "w") as fh:
+            fh.write("kind\tshape\tcalls_per_step\tms_per_call\twork_per_call\trate(TFLOP/s or GB/s)\n")
+            for (kind, tag), (el, work, n) in sorted(detail.items(), key=lambda kv: -kv[1][0]):
+                per = el / n
+                w = work / n
+                rate = (w / (per / 1e3) / 1e12) if kind.startswith("tc_") else (w / (per / 1e3) / 1e9)
+                fh.write(f"{kind}\t{tag}\t{n / args.steps:.1f}\t{per:.4f}\t{w:.4g}\t{rate:.1f}\n")
     tc_ms = sum(v[0] for k, v in fam.items() if k.startswith("tc_"))
     tc_calls = sum(v[2] for k, v in fam.items() if k.startswith("tc_"))
     alg_flops = sum(step_flops.values()) * args.steps
@@ -319,6 +331,7 @@ def main() -> None:
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--batch", type=int, default=256, help="per-GPU batch (256 = BASELINE.json config)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--detail", default="", help="write a per-layer kernel timing table to this file")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -77,6 +77,19 @@ size_t rnn_conv2d_wgrad_workspace(const rnn_conv_desc* d);
 int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy, void* dw, int dw_f32,
                           int accumulate, void* ws, size_t ws_bytes, cudaStream_t stream);
 
+/* First-layer convolution for inputs with C <= 8 (RGB stems): eight horizontally adjacent pixels x 8 padded
+ * channels form one 64-wide K step ("packed pixel" view through an overlapping-stride im2col tensor map), so a
+ * 7x7 stem costs 7 K steps instead of 49.  `d` describes the REAL problem (C = 3 ...).  x_packed is
+ * [N, Hp, Wp, 8] bf16, spatially zero-padded (rnn_nchw_f32_to_nhwc_bf16_padded writes it; Hp/Wp/SG from
+ * rnn_conv2d_first_geometry); w_packed / dw_packed are [K, R, SG, 8 taps, 8 ch] with zeros beyond S and C.
+ * Same torch.nn.Conv2d semantics as above; there is no dgrad (the network input needs no gradient). */
+int rnn_conv2d_first_geometry(const rnn_conv_desc* d, int* Hp, int* Wp, int* SG);
+int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                                const float* scale, const float* shift, int relu, cudaStream_t stream);
+size_t rnn_conv2d_first_wgrad_workspace(const rnn_conv_desc* d);
+int rnn_conv2d_first_wgrad_bf16(const rnn_conv_desc* d, const void* x_packed, const void* dy, void* dw_packed,
+                                int dw_f32, void* ws, size_t ws_bytes, cudaStream_t stream);
+
 /* ---- fp32 CUDA-core path (LeNet-5 class networks; BASELINE.json configs[0]) -------------------- */
 /* torch.nn.Conv2d (fp32, NHWC / KRSC) forward incl. bias, and autograd dgrad / wgrad. */
 int rnn_conv2d_fprop_f32(const rnn_conv_desc* d, const float* x, const float* w, const float* bias, float* y,
@@ -96,6 +109,9 @@ int rnn_colsum(const void* x, long long M, int C, void* out, int accumulate, int
 /* ---- elementwise (HBM-bound) -------------------------------------------------------------------- */
 /* Input pipeline: NCHW fp32 -> NHWC bf16 with the channel dimension zero-padded to Cpad. */
 int rnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int W, int Cpad, cudaStream_t stream);
+/* Same, into a spatially zero-padded [N, Hp, Wp, Cpad] buffer (image at rows pad_h.., columns pad_w..). */
+int rnn_nchw_f32_to_nhwc_bf16_padded(const float* x, void* y, int N, int C, int H, int W, int Cpad, int pad_h,
+                                     int pad_w, int Hp, int Wp, cudaStream_t stream);
 int rnn_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int H, int W, int Cpad, cudaStream_t stream);
 /* F.relu (arch/transformer.py:30) and its autograd: dx = dy * (y > 0). */
 int rnn_relu_fwd(const void* x, void* y, long long n, int is_f32, cudaStream_t stream);
@@ -140,12 +156,13 @@ int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* runn
 /* y = relu(x*scale + shift + residual): fused BatchNorm-apply (+ residual add) (+ ReLU). */
 int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, const void* residual, int relu, void* y,
                       long long M, int C, cudaStream_t stream);
-/* Backward of the fused op above.  y_out (nullable) is the forward output, used as the ReLU mask; dres
- * (nullable) receives the gradient of the residual branch.  dgamma/dbeta are fp32 or bf16. */
+/* Backward of the fused op above.  The ReLU mask comes from y_out (the forward output) or, when the forward
+ * had no residual, is recomputed from x with the forward's (fwd_scale, fwd_shift) -- pass one or neither.
+ * dres (nullable) receives the gradient of the residual branch.  dgamma/dbeta are fp32 or bf16. */
 int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out, const float* mean, const float* invstd,
                     const float* gamma, long long M, int C, void* dx, void* dres, void* dgamma, void* dbeta,
-                    int grads_f32, int accumulate_grads, float* sum_dy, float* sum_dy_xhat, void* ws, size_t ws_bytes,
-                    cudaStream_t stream);
+                    int grads_f32, int accumulate_grads, float* sums /* 5*C floats of scratch */,
+                    const float* fwd_scale, const float* fwd_shift, void* ws, size_t ws_bytes, cudaStream_t stream);
 /* nn.LayerNorm(E) over y = LN(x + residual) (arch/transformer.py:65,72,111-112,188); xsum (nullable)
  * receives x + residual for the backward pass; mean / rstd are per-row fp32. */
 int rnn_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, float eps, void* y,

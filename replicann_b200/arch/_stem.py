@@ -18,12 +18,14 @@ def prepare_input(x: Tensor, weight_dtype, cpad: int = STEM_CPAD) -> Tensor:
     step of SURVEY.md section 8f.2); tensors that already match pass through untouched."""
     if weight_dtype == torch.bfloat16:
         if x.dtype == torch.float32:
+            if x.shape[1] <= 8 and not x.requires_grad:
+                return x  # the first Conv2d consumes fp32 NCHW images directly (packed-pixel kernels)
             if not x.is_contiguous():
                 x = x.contiguous()
             return Fn.nchw(RF.nchw_to_nhwc_bf16(x, cpad=cpad))
-        if x.dtype == torch.bfloat16 and x.shape[1] == cpad:
+        if x.dtype == torch.bfloat16:
             return x
-        raise TypeError("bf16 models take fp32 NCHW images (or an already padded bf16 channels_last tensor)")
+        raise TypeError("bf16 models take fp32 NCHW images (or a bf16 channels_last tensor)")
     if x.dtype != torch.float32:
         raise TypeError(f"fp32 model got input of dtype {x.dtype}")
     return x

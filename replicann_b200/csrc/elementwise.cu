@@ -37,6 +37,31 @@ __global__ void nchw_f32_to_nhwc_bf16_kernel(const float* __restrict__ x, bf16* 
   }
 }
 
+// Same conversion into a spatially zero-padded buffer [N, Hp, Wp, Cp]: block (hp, n) writes one padded row;
+// border rows/columns and padded channels are written as zeros, so no separate memset is needed.
+__global__ void nchw_f32_to_nhwc_bf16_padded_kernel(const float* __restrict__ x, bf16* __restrict__ y, int C, int H,
+                                                    int W, int Cp, int pad_h, int pad_w, int Hp, int Wp) {
+  extern __shared__ float tile[];  // [C][W+1]
+  const int n = blockIdx.y, hp = blockIdx.x;
+  const int h = hp - pad_h;
+  const bool inside = h >= 0 && h < H;
+  if (inside) {
+    const float* src = x + ((long long)n * C * H + h) * W;
+    for (int i = threadIdx.x; i < C * W; i += blockDim.x) {
+      const int c = i / W, w = i - c * W;
+      tile[c * (W + 1) + w] = src[(long long)c * H * W + w];
+    }
+  }
+  __syncthreads();
+  bf16* dst = y + ((long long)n * Hp + hp) * Wp * Cp;
+  for (int i = threadIdx.x; i < Wp * Cp; i += blockDim.x) {
+    const int wp = i / Cp, c = i - wp * Cp;
+    const int w = wp - pad_w;
+    const bool ok = inside && w >= 0 && w < W && c < C;
+    dst[i] = __float2bfloat16(ok ? tile[c * (W + 1) + w] : 0.f);
+  }
+}
+
 __global__ void nhwc_bf16_to_nchw_f32_kernel(const bf16* __restrict__ x, float* __restrict__ y, int C, int H,
                                              int W, int Cp) {
   extern __shared__ float tile[];  // [C][W+1]
@@ -195,6 +220,17 @@ int rnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int 
   const size_t smem = (size_t)C * (W + 1) * sizeof(float);
   RNN_REQUIRE(smem <= 48 * 1024, RNN_ERR_SHAPE);
   nchw_f32_to_nhwc_bf16_kernel<<<dim3(H, N), 256, smem, stream>>>(x, reinterpret_cast<bf16*>(y), C, H, W, Cpad);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+int rnn_nchw_f32_to_nhwc_bf16_padded(const float* x, void* y, int N, int C, int H, int W, int Cpad, int pad_h,
+                                     int pad_w, int Hp, int Wp, cudaStream_t stream) {
+  RNN_REQUIRE(N > 0 && C > 0 && H > 0 && W > 0 && Cpad >= C, RNN_ERR_SHAPE);
+  RNN_REQUIRE(pad_h >= 0 && pad_w >= 0 && Hp >= H + pad_h && Wp >= W + pad_w, RNN_ERR_SHAPE);
+  const size_t smem = (size_t)C * (W + 1) * sizeof(float);
+  RNN_REQUIRE(smem <= 48 * 1024, RNN_ERR_SHAPE);
+  nchw_f32_to_nhwc_bf16_padded_kernel<<<dim3(Hp, N), 256, smem, stream>>>(x, reinterpret_cast<bf16*>(y), C, H, W, Cpad,
+                                                                          pad_h, pad_w, Hp, Wp);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

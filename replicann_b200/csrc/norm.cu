@@ -24,8 +24,13 @@ template <bool BWD>
 __global__ void __launch_bounds__(256)
 bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
                  const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
-                 float* __restrict__ partials /* [gridDim.y][2][C] */) {
-  // grid.x tiles the column groups (when C/8 > 256), grid.y tiles rows.
+                 float* __restrict__ partials /* [gridDim.y][2][C] */, const float* __restrict__ fscale = nullptr,
+                 const float* __restrict__ fshift = nullptr) {
+  // grid.x tiles the column groups (when C/8 > 256), grid.y tiles rows.  Each thread owns one 8-channel
+  // vector column and walks its rows four at a time so that 4 (x streams) independent 16-byte loads are
+  // in flight per thread.  In the backward flavour the ReLU mask comes from the saved output `yout`, or is
+  // recomputed from x (fscale/fshift = the forward's scale/shift) when the forward had no residual.
+  constexpr int U = 4;
   const int cgs = C >> 3;
   const int tpr = cgs < 256 ? cgs : 256;          // threads per row
   const int rpp = 256 / tpr;                      // rows per pass
@@ -34,31 +39,58 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
   float s0[8], s1[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) s0[e] = s1[e] = 0.f;
-  float mu[8], is[8];
-  if (BWD && cg < cgs) {
+  float mu[8], is[8], fs[8], fb[8];
+  const bool active = cg < cgs && rlocal < rpp;
+  if (BWD && active) {
 #pragma unroll
-    for (int e = 0; e < 8; ++e) { mu[e] = mean[cg * 8 + e]; is[e] = invstd[cg * 8 + e]; }
+    for (int e = 0; e < 8; ++e) {
+      mu[e] = mean[cg * 8 + e];
+      is[e] = invstd[cg * 8 + e];
+      fs[e] = fscale ? fscale[cg * 8 + e] : 0.f;
+      fb[e] = fscale ? fshift[cg * 8 + e] : 0.f;
+    }
   }
-  if (cg < cgs && rlocal < rpp) {
-    for (long long r = (long long)blockIdx.y * rpp + rlocal; r < M; r += (long long)gridDim.y * rpp) {
-      const long long off = r * C + cg * 8;
-      float v[8];
-      unpack8(ld_stream(x + off), v);
-      if (!BWD) {
+  auto accum = [&](const uint4& ux, const uint4& ug, const uint4& uo) {
+    float v[8];
+    unpack8(ux, v);
+    if (!BWD) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { s0[e] += v[e]; s1[e] += v[e] * v[e]; }
-      } else {
-        float g[8];
-        unpack8(ld_stream(dy + off), g);
-        if (yout) {
-          float o[8];
-          unpack8(ld_stream(yout + off), o);
+      for (int e = 0; e < 8; ++e) { s0[e] += v[e]; s1[e] = fmaf(v[e], v[e], s1[e]); }
+    } else {
+      float g[8];
+      unpack8(ug, g);
+      if (yout) {
+        float o[8];
+        unpack8(uo, o);
 #pragma unroll
-          for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
-        }
+        for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
+      } else if (fscale) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) { s0[e] += g[e]; s1[e] += g[e] * (v[e] - mu[e]) * is[e]; }
+        for (int e = 0; e < 8; ++e) g[e] = fmaf(v[e], fs[e], fb[e]) > 0.f ? g[e] : 0.f;
       }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) { s0[e] += g[e]; s1[e] = fmaf(g[e], (v[e] - mu[e]) * is[e], s1[e]); }
+    }
+  };
+  if (active) {
+    const long long stride = (long long)gridDim.y * rpp;
+    long long r = (long long)blockIdx.y * rpp + rlocal;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    for (; r + (U - 1) * stride < M; r += U * stride) {
+      uint4 ux[U], ug[U], uo[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long off = (r + u * stride) * C + cg * 8;
+        ux[u] = ld_stream(x + off);
+        ug[u] = BWD ? ld_stream(dy + off) : z;
+        uo[u] = (BWD && yout) ? ld_stream(yout + off) : z;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) accum(ux[u], ug[u], uo[u]);
+    }
+    for (; r < M; r += stride) {
+      const long long off = r * C + cg * 8;
+      accum(ld_stream(x + off), BWD ? ld_stream(dy + off) : z, (BWD && yout) ? ld_stream(yout + off) : z);
     }
   }
   // combine the rpp row-lanes of each column group through shared memory
@@ -78,15 +110,39 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
   }
 }
 
-__global__ void bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, float count,
-                                         const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
-                                         float momentum, float* running_mean, float* running_var,
-                                         float* __restrict__ mean, float* __restrict__ invstd,
-                                         float* __restrict__ scale, float* __restrict__ shift) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f, ss = 0.f;
-  for (int p = 0; p < nparts; ++p) { s += partials[(long long)p * 2 * C + c]; ss += partials[(long long)p * 2 * C + C + c]; }
+// Sum the per-block partials: one block handles 32 channels, 8 threads per channel walk the partial rows
+// (coalesced across channels), then a shared-memory tree combines them in a fixed order.
+__device__ __forceinline__ void sum_partials_32x8(const float* __restrict__ partials, int nparts, int C, int c,
+                                                  int lane8, float* sm /* [2][8][32] */, float& s, float& ss) {
+  float a = 0.f, b = 0.f;
+  if (c < C)
+    for (int p = lane8; p < nparts; p += 8) {
+      a += partials[(long long)p * 2 * C + c];
+      b += partials[(long long)p * 2 * C + C + c];
+    }
+  const int cl = threadIdx.x & 31;
+  sm[lane8 * 32 + cl] = a;
+  sm[256 + lane8 * 32 + cl] = b;
+  __syncthreads();
+  s = 0.f; ss = 0.f;
+  if (lane8 == 0) {
+#pragma unroll
+    for (int l = 0; l < 8; ++l) { s += sm[l * 32 + cl]; ss += sm[256 + l * 32 + cl]; }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, float count,
+                         const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
+                         float momentum, float* running_mean, float* running_var,
+                         float* __restrict__ mean, float* __restrict__ invstd,
+                         float* __restrict__ scale, float* __restrict__ shift) {
+  __shared__ float sm[512];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int lane8 = threadIdx.x >> 5;
+  float s, ss;
+  sum_partials_32x8(partials, nparts, C, c, lane8, sm, s, ss);
+  if (lane8 != 0 || c >= C) return;
   const float m = s / count;
   float var = ss / count - m * m;
   var = var < 0.f ? 0.f : var;
@@ -115,15 +171,30 @@ __global__ void bn_eval_prepare_kernel(const float* __restrict__ gamma, const fl
   shift[c] = b - rm[c] * g * is;
 }
 
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
-                                       float* __restrict__ sum_dy, float* __restrict__ sum_dy_xhat,
-                                       void* dgamma, void* dbeta, int grads_f32, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  float s = 0.f, ss = 0.f;
-  for (int p = 0; p < nparts; ++p) { s += partials[(long long)p * 2 * C + c]; ss += partials[(long long)p * 2 * C + C + c]; }
+__global__ void __launch_bounds__(256)
+bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
+                       float* __restrict__ sum_dy, float* __restrict__ sum_dy_xhat,
+                       void* dgamma, void* dbeta, int grads_f32, int accumulate,
+                       const float* __restrict__ mean, const float* __restrict__ invstd,
+                       const float* __restrict__ gamma, float inv_count, float* __restrict__ coef /* [3][C] */) {
+  __shared__ float sm[512];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int lane8 = threadIdx.x >> 5;
+  float s, ss;
+  sum_partials_32x8(partials, nparts, C, c, lane8, sm, s, ss);
+  if (lane8 != 0 || c >= C) return;
   sum_dy[c] = s;
   sum_dy_xhat[c] = ss;
+  {
+    // dx = gamma*invstd*(dy' - sum_dy/M - xhat*sum_dy_xhat/M), xhat = (x-mean)*invstd
+    //    = A*dy' + B*x + D  with per-channel A, B, D: the apply kernel needs three vector loads per 8 channels
+    const float is = invstd[c], gm = gamma ? gamma[c] : 1.f;
+    const float A = gm * is;
+    const float B = -gm * is * is * ss * inv_count;
+    coef[c] = A;
+    coef[C + c] = B;
+    coef[2 * C + c] = -A * s * inv_count - B * mean[c];
+  }
   if (dgamma) {
     if (grads_f32) {
       float* dg = (float*)dgamma; float* db = (float*)dbeta;
@@ -148,8 +219,8 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
     const float4 a1 = __ldg(reinterpret_cast<const float4*>(scale + cg * 8 + 4));
     const float4 b0 = __ldg(reinterpret_cast<const float4*>(shift + cg * 8));
     const float4 b1 = __ldg(reinterpret_cast<const float4*>(shift + cg * 8 + 4));
-    v[0] = v[0] * a0.x + b0.x; v[1] = v[1] * a0.y + b0.y; v[2] = v[2] * a0.z + b0.z; v[3] = v[3] * a0.w + b0.w;
-    v[4] = v[4] * a1.x + b1.x; v[5] = v[5] * a1.y + b1.y; v[6] = v[6] * a1.z + b1.z; v[7] = v[7] * a1.w + b1.w;
+    v[0] = fmaf(v[0], a0.x, b0.x); v[1] = fmaf(v[1], a0.y, b0.y); v[2] = fmaf(v[2], a0.z, b0.z); v[3] = fmaf(v[3], a0.w, b0.w);
+    v[4] = fmaf(v[4], a1.x, b1.x); v[5] = fmaf(v[5], a1.y, b1.y); v[6] = fmaf(v[6], a1.z, b1.z); v[7] = fmaf(v[7], a1.w, b1.w);
     if (residual) {
       float r[8];
       unpack8(ld_stream(residual + i * 8), r);
@@ -166,9 +237,10 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
 
 __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
-                    const float* __restrict__ mean, const float* __restrict__ invstd, const float* __restrict__ gamma,
-                    const float* __restrict__ sum_dy, const float* __restrict__ sum_dy_xhat, float inv_count,
-                    bf16* __restrict__ dx, bf16* __restrict__ dres, long long nvec, int cgs) {
+                    const float* __restrict__ coef /* [3][C]: A, B, D */, bf16* __restrict__ dx,
+                    bf16* __restrict__ dres, long long nvec, int cgs, const float* __restrict__ fscale,
+                    const float* __restrict__ fshift) {
+  const int C = cgs * 8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
     const int c0 = (int)(i % cgs) * 8;
     float g[8], v[8];
@@ -179,17 +251,25 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
       unpack8(ld_stream(yout + i * 8), o);
 #pragma unroll
       for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
+    } else if (fscale) {
+      float fs[8], fb[8];
+      *reinterpret_cast<float4*>(fs) = __ldg(reinterpret_cast<const float4*>(fscale + c0));
+      *reinterpret_cast<float4*>(fs + 4) = __ldg(reinterpret_cast<const float4*>(fscale + c0 + 4));
+      *reinterpret_cast<float4*>(fb) = __ldg(reinterpret_cast<const float4*>(fshift + c0));
+      *reinterpret_cast<float4*>(fb + 4) = __ldg(reinterpret_cast<const float4*>(fshift + c0 + 4));
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = fmaf(v[e], fs[e], fb[e]) > 0.f ? g[e] : 0.f;
     }
     if (dres) st_stream(dres + i * 8, pack8(g));
-    float r[8];
+    float a[8], b[8], d[8], r[8];
+    *reinterpret_cast<float4*>(a) = __ldg(reinterpret_cast<const float4*>(coef + c0));
+    *reinterpret_cast<float4*>(a + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
+    *reinterpret_cast<float4*>(b) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
+    *reinterpret_cast<float4*>(b + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
+    *reinterpret_cast<float4*>(d) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
+    *reinterpret_cast<float4*>(d + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
 #pragma unroll
-    for (int e = 0; e < 8; ++e) {
-      const int c = c0 + e;
-      const float is = __ldg(invstd + c);
-      const float xhat = (v[e] - __ldg(mean + c)) * is;
-      const float gm = gamma ? __ldg(gamma + c) : 1.f;
-      r[e] = gm * is * (g[e] - __ldg(sum_dy + c) * inv_count - xhat * __ldg(sum_dy_xhat + c) * inv_count);
-    }
+    for (int e = 0; e < 8; ++e) r[e] = fmaf(a[e], g[e], fmaf(b[e], v[e], d[e]));
     st_stream(dx + i * 8, pack8(r));
   }
 }
@@ -199,11 +279,12 @@ int bn_row_blocks(long long M, int C) {
   const int tpr = cgs < 256 ? cgs : 256;
   const int rpp = 256 / tpr;
   const int gx = (cgs + tpr - 1) / tpr;
-  long long gy = (M + rpp - 1) / rpp;
-  // enough rows per block to amortise the tail reduction; cap the grid at ~8 blocks per SM
-  long long cap = (long long)rnn_num_sms() * 8 / gx;
+  // every thread should see >= 4 rows (one unrolled batch); at most ~4 resident blocks per SM in total
+  long long gy = (M + (long long)rpp * 4 - 1) / ((long long)rpp * 4);
+  long long cap = (long long)rnn_num_sms() * 4 / gx;
   if (cap < 1) cap = 1;
   if (gy > cap) gy = cap;
+  if (gy < 1) gy = 1;
   return (int)gy;
 }
 
@@ -410,7 +491,7 @@ int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, con
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            (float*)ws);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift);
   RNN_CHECK_LAUNCH();
@@ -454,7 +535,7 @@ int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gam
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            scratch);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift);
   RNN_CHECK_LAUNCH();
@@ -486,24 +567,30 @@ int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, con
 int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable: ReLU output */, const float* mean,
                     const float* invstd, const float* gamma, long long M, int C, void* dx,
                     void* dres /* nullable */, void* dgamma, void* dbeta, int grads_f32, int accumulate_grads,
-                    float* sum_dy, float* sum_dy_xhat, void* ws, size_t ws_bytes, cudaStream_t stream) {
+                    float* sums /* [5][C] scratch: sum_dy, sum_dy_xhat, A, B, D */, const float* fwd_scale,
+                    const float* fwd_shift, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  float* sum_dy = sums;
+  float* sum_dy_xhat = sums + C;
+  float* coef = sums + 2 * (long long)C;
+  RNN_REQUIRE((fwd_scale == nullptr) == (fwd_shift == nullptr), RNN_ERR_SHAPE);
+  RNN_REQUIRE(!(y_out != nullptr && fwd_scale != nullptr), RNN_ERR_SHAPE);  // one source for the ReLU mask
   RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
   const int gy = bn_row_blocks(M, C);
   RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)gy * 2 * C * sizeof(float), RNN_ERR_WORKSPACE);
   const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
   bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
-                                                          invstd, M, C, (float*)ws);
+                                                          invstd, M, C, (float*)ws, fwd_scale, fwd_shift);
   RNN_CHECK_LAUNCH();
-  bn_bwd_finalize_kernel<<<ceil_div_i(C, 128), 128, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
-                                                                 dbeta, grads_f32, accumulate_grads);
+  bn_bwd_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
+                                                                dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
+                                                                1.f / (float)M, coef);
   RNN_CHECK_LAUNCH();
   const long long nvec = M * (C / 8);
   long long blocks = (nvec + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * 16;
   if (blocks > cap) blocks = cap;
-  bn_bwd_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y_out, mean, invstd,
-                                                       gamma, sum_dy, sum_dy_xhat, 1.f / (float)M, (bf16*)dx,
-                                                       (bf16*)dres, nvec, C / 8);
+  bn_bwd_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y_out, coef,
+                                                       (bf16*)dx, (bf16*)dres, nvec, C / 8, fwd_scale, fwd_shift);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

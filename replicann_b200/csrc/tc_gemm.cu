@@ -749,4 +749,143 @@ int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy,
                        stream);
 }
 
+
+// =============================================================================================
+// First-layer convolution (few input channels): "packed pixel" implicit GEMM.
+//
+// A 3-channel image wastes 61/64 of every 64-channel K step.  Instead the input is stored NHWC with the
+// channels padded to 8 and physically zero-padded in space; eight horizontally adjacent pixels (8 x 8
+// channels = 64 bf16 = 128 B, contiguous in memory) are then presented to the im2col TMA as ONE pixel of a
+// virtual tensor whose W stride is a single real pixel (overlapping strides are legal for TMA).  One K step
+// so covers 8 horizontal filter taps; the filter is laid out to match, [K][R][SG][8 taps][8 ch] with
+// SG = ceil(S/8) and zeros where s >= S or c >= C.  ResNet's 7x7 stem: 7 K steps instead of 49.
+// =============================================================================================
+struct FirstGeom {
+  int Hp, Wp, SG, Wv, up_w, up_h, ntaps;
+};
+
+static int first_geom(const rnn_conv_desc* d, FirstGeom* g) {
+  RNN_REQUIRE(d != nullptr, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->N > 0 && d->H > 0 && d->W > 0 && d->C > 0 && d->C <= 8 && d->K > 0 && d->K % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->R > 0 && d->S > 0 && d->stride_h > 0 && d->stride_w > 0 && d->pad_h >= 0 && d->pad_w >= 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->P == (d->H + 2 * d->pad_h - d->R) / d->stride_h + 1, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->Q == (d->W + 2 * d->pad_w - d->S) / d->stride_w + 1, RNN_ERR_SHAPE);
+  g->SG = (d->S + 7) / 8;
+  g->Hp = d->H + 2 * d->pad_h;
+  const int need = d->stride_w * (d->Q - 1) + 8 * g->SG;
+  g->Wp = d->W + 2 * d->pad_w > need ? d->W + 2 * d->pad_w : need;
+  g->Wv = g->Wp - 7;
+  g->up_w = d->stride_w * (d->Q - 1) - (g->Wv - 1);
+  g->up_h = d->stride_h * (d->P - 1) - (g->Hp - 1);
+  g->ntaps = d->R * g->SG;
+  RNN_REQUIRE(g->ntaps <= MAX_TAPS && 8 * (g->SG - 1) <= 255 && d->R - 1 <= 255, RNN_ERR_SHAPE);
+  return RNN_OK;
+}
+
+static void first_taps(const rnn_conv_desc* d, const FirstGeom& g, TcParams* p) {
+  for (int r = 0; r < d->R; ++r)
+    for (int sg = 0; sg < g.SG; ++sg) {
+      TapDesc& t = p->taps[r * g.SG + sg];
+      t.ow = (int16_t)(8 * sg); t.oh = (int16_t)r; t.bcol = (r * g.SG + sg) * 64;
+    }
+}
+
+/* Padded-input geometry a caller must allocate for: x_packed is [N, Hp, Wp, 8] bf16 with the image at
+ * rows pad_h.., columns pad_w.. and zeros elsewhere; the filter is [K, R, SG, 64] bf16. */
+int rnn_conv2d_first_geometry(const rnn_conv_desc* d, int* Hp, int* Wp, int* SG) {
+  FirstGeom g;
+  int rc = first_geom(d, &g);
+  if (rc != RNN_OK) return rc;
+  if (Hp) *Hp = g.Hp;
+  if (Wp) *Wp = g.Wp;
+  if (SG) *SG = g.SG;
+  return RNN_OK;
+}
+
+int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                                const float* scale, const float* shift, int relu, cudaStream_t stream) {
+  FirstGeom g;
+  int rc = first_geom(d, &g);
+  if (rc != RNN_OK) return rc;
+  rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const int BN = pick_bn(d->K);
+  CUtensorMap ta, tb;
+  rc = make_tmap_im2col(&ta, x_packed, 64, g.Wv, g.Hp, d->N, 8, (long long)g.Wp * 8, (long long)g.Hp * g.Wp * 8, 0, 0,
+                        g.up_w, g.up_h, d->stride_w, d->stride_h, BM);
+  if (rc != RNN_OK) return rc;
+  const long long kcols = (long long)g.ntaps * 64;
+  rc = make_tmap_2d(&tb, w_packed, d->K, kcols, kcols, BN);
+  if (rc != RNN_OK) return rc;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  const long long M = (long long)d->N * d->P * d->Q;
+  RNN_REQUIRE(M < (1ll << 31), RNN_ERR_SHAPE);
+  p.M = (int)M; p.N = d->K;
+  p.cchunks = 1; p.ntaps = g.ntaps; p.k_iters = g.ntaps; p.splits = 1;
+  p.n_mblk = ceil_div_i(M, BM); p.n_nblk = ceil_div_i(d->K, BN);
+  p.Wo = d->Q; p.HoWo = d->P * d->Q;
+  p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = 0; p.lo_h = 0;
+  p.ldd = d->K;
+  p.D = y; p.scale = scale; p.shift = shift; p.relu = relu;
+  first_taps(d, g, &p);
+  return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);
+}
+
+static WgradPlan plan_first_wgrad(const rnn_conv_desc* d, const FirstGeom& g) {
+  WgradPlan w;
+  w.BN = 64;
+  w.n_mblk = ceil_div_i(d->K, BM);
+  w.ncblk = 1;
+  const long long mpix = (long long)d->N * d->P * d->Q;
+  w.k_iters = ceil_div_i(mpix, BK);
+  const int base = w.n_mblk * g.ntaps;
+  int s = ceil_div_i(rnn_num_sms(), base);
+  if (s > w.k_iters / 4) s = w.k_iters / 4;
+  if (s < 1) s = 1;
+  w.splits = s;
+  w.ws_bytes = (size_t)s * d->K * g.ntaps * 64 * sizeof(float);
+  return w;
+}
+
+size_t rnn_conv2d_first_wgrad_workspace(const rnn_conv_desc* d) {
+  FirstGeom g;
+  if (first_geom(d, &g) != RNN_OK) return 0;
+  return plan_first_wgrad(d, g).ws_bytes;
+}
+
+/* dw_packed[K, R, SG, 64] (bf16, or fp32 when dw_f32) = gradient w.r.t. the packed filter. */
+int rnn_conv2d_first_wgrad_bf16(const rnn_conv_desc* d, const void* x_packed, const void* dy, void* dw_packed,
+                                int dw_f32, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  FirstGeom g;
+  int rc = first_geom(d, &g);
+  if (rc != RNN_OK) return rc;
+  rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const WgradPlan w = plan_first_wgrad(d, g);
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= w.ws_bytes, RNN_ERR_WORKSPACE);
+  const long long mpix = (long long)d->N * d->P * d->Q;
+  RNN_REQUIRE(mpix < (1ll << 31), RNN_ERR_SHAPE);
+  CUtensorMap ta, tb;
+  rc = make_tmap_2d(&ta, dy, mpix, d->K, d->K, 64);
+  if (rc != RNN_OK) return rc;
+  rc = make_tmap_im2col(&tb, x_packed, 64, g.Wv, g.Hp, d->N, 8, (long long)g.Wp * 8, (long long)g.Hp * g.Wp * 8, 0, 0,
+                        g.up_w, g.up_h, d->stride_w, d->stride_h, 64);
+  if (rc != RNN_OK) return rc;
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = d->K; p.N = 64;
+  p.k_iters = w.k_iters; p.splits = w.splits;
+  p.ntaps = g.ntaps; p.ncblk = 1; p.tapC = 64;
+  p.n_mblk = w.n_mblk; p.n_nblk = g.ntaps;
+  p.Wo = d->Q; p.HoWo = d->P * d->Q;
+  p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = 0; p.lo_h = 0;
+  p.ws = reinterpret_cast<float*>(ws);
+  p.ldw = (long long)g.ntaps * 64;
+  first_taps(d, g, &p);
+  rc = launch_bn<KIND_WGRAD, true, true>(w.BN, ta, tb, p, stream);
+  if (rc != RNN_OK) return rc;
+  return launch_reduce(p.ws, p.splits, (long long)d->K * p.ldw, (int)p.ldw, nullptr, 0, 0, dw_packed, dw_f32, stream);
+}
+
 }  // extern "C"

@@ -23,10 +23,10 @@ def set_profile(sink: list | None) -> None:
 
 
 class _span:
-    __slots__ = ("kind", "work", "e0")
+    __slots__ = ("kind", "work", "e0", "tag")
 
-    def __init__(self, kind: str, work=None):
-        self.kind, self.work, self.e0 = kind, work, None
+    def __init__(self, kind: str, work=None, tag: str = ""):
+        self.kind, self.work, self.e0, self.tag = kind, work, None, tag
 
     def __enter__(self):
         if _profile is not None:
@@ -38,7 +38,7 @@ class _span:
         if self.e0 is not None and _profile is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
-            _profile.append((self.kind, self.work, self.e0, e1))
+            _profile.append((self.kind, self.work, self.e0, e1, self.tag))
         return False
 
 
@@ -89,7 +89,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
         _req(bias, torch.float32, "bias")
     nbytes = lib.rnn_gemm_bf16_workspace(M, N, K, int(out_f32), int(bias is not None or relu))
     ws = workspace(nbytes, a.device)
-    with _span("tc_gemm", 2.0 * M * N * K):
+    with _span("tc_gemm", 2.0 * M * N * K, f"M{M} N{N} K{K} a_mn{int(a_mn)} b_mn{int(b_mn)}"):
         check(lib.rnn_gemm_bf16(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
                                 int(out_f32), ptr(ws), nbytes, cur_stream()), "rnn_gemm_bf16")
     return d
@@ -108,6 +108,10 @@ def _conv_flops(d) -> float:
     return 2.0 * d.N * d.P * d.Q * d.K * d.C * d.R * d.S
 
 
+def _conv_tag(d) -> str:
+    return f"N{d.N} {d.H}x{d.W} C{d.C} K{d.K} {d.R}x{d.S} s{d.stride_h} p{d.pad_h}"
+
+
 def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None, relu=False):
     """x [N,H,W,C] bf16, w [K,R,S,C] bf16 -> y [N,P,Q,K] bf16."""
     lib = _lib.load()
@@ -117,10 +121,52 @@ def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None
     y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x.device)
     if residual is not None:
         _req(residual, torch.bfloat16, "residual")
-    with _span("tc_conv_fprop", _conv_flops(d)):
+    with _span("tc_conv_fprop", _conv_flops(d), _conv_tag(d)):
         check(lib.rnn_conv2d_fprop_bf16(d, ptr(x), ptr(w), ptr(y), ptr(scale), ptr(shift), ptr(residual),
                                         int(relu), cur_stream()), "rnn_conv2d_fprop_bf16")
     return y
+
+
+# ---- first layer (C <= 8): packed-pixel layout -------------------------------------------------------
+def first_conv_geometry(d):
+    import ctypes as C
+    hp, wp, sg = C.c_int(), C.c_int(), C.c_int()
+    check(_lib.load().rnn_conv2d_first_geometry(d, C.byref(hp), C.byref(wp), C.byref(sg)), "rnn_conv2d_first_geometry")
+    return hp.value, wp.value, sg.value
+
+
+def pack_first_input(x_nchw_f32, d):
+    """fp32 NCHW images -> bf16 [N, Hp, Wp, 8], spatially zero-padded, channels padded to 8."""
+    lib = _lib.load()
+    _req(x_nchw_f32, torch.float32, "x")
+    hp, wp, _ = first_conv_geometry(d)
+    N, Cn, H, W = x_nchw_f32.shape
+    y = torch.empty((N, hp, wp, 8), dtype=torch.bfloat16, device=x_nchw_f32.device)
+    check(lib.rnn_nchw_f32_to_nhwc_bf16_padded(ptr(x_nchw_f32), ptr(y), N, Cn, H, W, 8, d.pad_h, d.pad_w, hp, wp,
+                                               cur_stream()), "rnn_nchw_f32_to_nhwc_bf16_padded")
+    return y
+
+
+def first_conv_fprop(x_packed, w_packed, d, *, scale=None, shift=None, relu=False):
+    lib = _lib.load()
+    _req(x_packed, torch.bfloat16, "x_packed"); _req(w_packed, torch.bfloat16, "w_packed")
+    y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x_packed.device)
+    with _span("tc_conv_fprop", _conv_flops(d), "first " + _conv_tag(d)):
+        check(lib.rnn_conv2d_first_fprop_bf16(d, ptr(x_packed), ptr(w_packed), ptr(y), ptr(scale), ptr(shift), int(relu),
+                                              cur_stream()), "rnn_conv2d_first_fprop_bf16")
+    return y
+
+
+def first_conv_wgrad(x_packed, dy, d, sg, *, out_dtype=torch.bfloat16):
+    lib = _lib.load()
+    _req(x_packed, torch.bfloat16, "x_packed"); _req(dy, torch.bfloat16, "dy")
+    dw = torch.empty((d.K, d.R, sg, 64), dtype=out_dtype, device=dy.device)
+    nbytes = lib.rnn_conv2d_first_wgrad_workspace(d)
+    ws = workspace(nbytes, dy.device)
+    with _span("tc_conv_wgrad", _conv_flops(d), "first " + _conv_tag(d)):
+        check(lib.rnn_conv2d_first_wgrad_bf16(d, ptr(x_packed), ptr(dy), ptr(dw), int(out_dtype == torch.float32),
+                                              ptr(ws), nbytes, cur_stream()), "rnn_conv2d_first_wgrad_bf16")
+    return dw
 
 
 def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False):
@@ -131,7 +177,7 @@ def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False)
     if tuple(dy.shape) != (d.N, d.P, d.Q, d.K):
         raise ValueError(f"dy shape {tuple(dy.shape)} != {(d.N, d.P, d.Q, d.K)}")
     dx = out if out is not None else torch.empty(tuple(x_shape), dtype=torch.bfloat16, device=dy.device)
-    with _span("tc_conv_dgrad", _conv_flops(d)):
+    with _span("tc_conv_dgrad", _conv_flops(d), _conv_tag(d)):
         check(lib.rnn_conv2d_dgrad_bf16(d, ptr(dy), ptr(w), ptr(dx), int(accumulate), cur_stream()),
               "rnn_conv2d_dgrad_bf16")
     return dx
@@ -145,7 +191,7 @@ def conv2d_wgrad(x, dy, w_shape, *, stride=1, pad=0, out=None, accumulate=False,
     dw = out if out is not None else torch.empty(tuple(w_shape), dtype=out_dtype, device=x.device)
     nbytes = lib.rnn_conv2d_wgrad_workspace(d)
     ws = workspace(nbytes, x.device)
-    with _span("tc_conv_wgrad", _conv_flops(d)):
+    with _span("tc_conv_wgrad", _conv_flops(d), _conv_tag(d)):
         check(lib.rnn_conv2d_wgrad_bf16(d, ptr(x), ptr(dy), ptr(dw), int(dw.dtype == torch.float32),
                                         int(accumulate), ptr(ws), nbytes, cur_stream()), "rnn_conv2d_wgrad_bf16")
     return dw
@@ -320,7 +366,7 @@ def bn_stats(x2d, gamma, beta, eps, momentum, running_mean, running_var):
     st = torch.empty((4, Cn), dtype=torch.float32, device=x2d.device)
     nbytes = lib.rnn_bn_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
-    with _span("bn_stats", 2.0 * M * Cn):
+    with _span("bn_stats", 2.0 * M * Cn, f"M{M} C{Cn}"):
       check(lib.rnn_bn_stats_bf16(ptr(x2d), M, Cn, ptr(gamma), ptr(beta), float(eps), float(momentum),
                                 ptr(running_mean), ptr(running_var), ptr(st[0]), ptr(st[1]), ptr(st[2]), ptr(st[3]),
                                   ptr(ws), nbytes, cur_stream()), "rnn_bn_stats_bf16")
@@ -340,26 +386,28 @@ def bn_apply(x2d, scale, shift, residual=None, relu=False):
     lib = _lib.load(); _req(x2d, torch.bfloat16, "x")
     M, Cn = x2d.shape
     y = torch.empty_like(x2d)
-    with _span("bn_apply", 2.0 * M * Cn * (3 if residual is not None else 2)):
+    with _span("bn_apply", 2.0 * M * Cn * (3 if residual is not None else 2), f"M{M} C{Cn} res{int(residual is not None)}"):
         check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), M, Cn,
                                     cur_stream()), "rnn_bn_apply_bf16")
     return y
 
 
-def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, accumulate):
+def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, accumulate, fwd_scale=None,
+           fwd_shift=None):
     lib = _lib.load(); _req(dy2d, torch.bfloat16, "dy")
     M, Cn = x2d.shape
     dx = torch.empty_like(x2d)
     dres = torch.empty_like(x2d) if want_dres else None
-    sums = torch.empty((2, Cn), dtype=torch.float32, device=x2d.device)
+    sums = torch.empty((5, Cn), dtype=torch.float32, device=x2d.device)
     nbytes = lib.rnn_bn_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
     nread = 2 + (1 if y_out is not None else 0)
-    with _span("bn_bwd", 2.0 * M * Cn * (2 * nread + 1 + (1 if want_dres else 0))):
+    with _span("bn_bwd", 2.0 * M * Cn * (2 * nread + 1 + (1 if want_dres else 0)), f"M{M} C{Cn} y{int(y_out is not None)} res{int(want_dres)}"):
         check(lib.rnn_bn_bwd_bf16(ptr(dy2d), ptr(x2d), ptr(y_out), ptr(mean), ptr(invstd), ptr(gamma), M, Cn,
                                   ptr(dx), ptr(dres), ptr(dgamma), ptr(dbeta),
-                                  _is_f32(dgamma) if dgamma is not None else 1, int(accumulate), ptr(sums[0]),
-                                  ptr(sums[1]), ptr(ws), nbytes, cur_stream()), "rnn_bn_bwd_bf16")
+                                  _is_f32(dgamma) if dgamma is not None else 1, int(accumulate), ptr(sums),
+                                  ptr(fwd_scale), ptr(fwd_shift), ptr(ws), nbytes, cur_stream()),
+              "rnn_bn_bwd_bf16")
     return dx, dres
 
 

@@ -136,6 +136,50 @@ class PadFilterFn(Function):
         return g[:, :ctx.c].contiguous(memory_format=torch.channels_last), None
 
 
+class FirstConv2dFn(Function):
+    """First layer of a bf16 CNN applied directly to fp32 NCHW images (C <= 8): the layout/cast kernel, the
+    packed-pixel tcgen05 convolution (see rnn_conv2d_first_fprop_bf16) and its filter gradient.  No input
+    gradient is produced (images do not require grad)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, stride, pad, relu):
+        from .._lib import conv_desc
+        N, Cn, H, W = x.shape
+        K, _, R, S = weight.shape
+        d = conv_desc(N, H, W, Cn, K, R, S, stride, pad)
+        _, _, sg = RF.first_conv_geometry(d)
+        xp = RF.pack_first_input(x if x.is_contiguous() else x.contiguous(), d)
+        # filter [K,C,R,S] -> [K,R,SG*8 taps,8 ch] with zeros beyond S and C (tiny; data movement only)
+        wp = torch.zeros((K, R, sg * 8, 8), dtype=weight.dtype, device=weight.device)
+        wp[:, :, :S, :Cn].copy_(weight.detach().permute(0, 2, 3, 1))
+        y = RF.first_conv_fprop(xp, wp.reshape(K, R, sg, 64), d, shift=_bias_f32(bias), relu=relu)
+        ctx.d, ctx.sg, ctx.relu = d, sg, relu
+        ctx.save_for_backward(xp, weight, bias, y if relu else None)
+        return nchw(y)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xp, weight, bias, y = ctx.saved_tensors
+        d, sg = ctx.d, ctx.sg
+        dyh = nhwc(dy)
+        if ctx.relu:
+            dyh = RF.relu_bwd(dyh, y)
+        dw = db = None
+        if ctx.needs_input_grad[1]:
+            def wg(out, acc):
+                g = RF.first_conv_wgrad(xp, dyh, d, sg)
+                gv = g.reshape(d.K, d.R, sg * 8, 8)[:, :, :d.S, :d.C].permute(0, 3, 1, 2)
+                if acc:
+                    out.add_(gv)
+                else:
+                    out.copy_(gv)
+            dw = _write_param_grad(weight, wg)
+        if bias is not None and ctx.needs_input_grad[2]:
+            K = dyh.shape[-1]
+            db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
+        return None, dw, db, None, None, None
+
+
 def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
     """KRSC buffer behind a [K,C,R,S] gradient tensor; it must already be channels_last (no copy allowed,
     the kernel writes through it)."""
@@ -211,13 +255,17 @@ class BatchNormFn(Function):
             mean, invstd = running_mean, torch.rsqrt(running_var + eps)
         y2 = RF.bn_apply(x2, scale, shift, r2, relu)
         ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
-        ctx.save_for_backward(x2, y2 if relu else None, mean, invstd, gamma, beta)
+        # ReLU mask for backward: the saved output when a residual was added, otherwise recomputed from x
+        # with the forward's scale/shift (saves reading y twice in the backward kernels)
+        from_x = relu and residual is None
+        ctx.save_for_backward(x2, y2 if (relu and not from_x) else None, mean, invstd, gamma, beta,
+                              scale if from_x else None, shift if from_x else None)
         ctx.shape = xh.shape
         return nchw(y2.reshape(xh.shape))
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y2, mean, invstd, gamma, beta = ctx.saved_tensors
+        x2, y2, mean, invstd, gamma, beta, fscale, fshift = ctx.saved_tensors
         if not ctx.training:
             raise RuntimeError("BatchNorm2d backward in eval mode is not supported by replicann_b200")
         Cn = x2.shape[1]
@@ -231,7 +279,8 @@ class BatchNormFn(Function):
             dg = db = None
             acc = False
         dx2, dres2 = RF.bn_bwd(dy2, x2, y2, mean, invstd, gamma.detach() if gamma is not None else None,
-                               want_dres=ctx.has_res, dgamma=dg, dbeta=db, accumulate=acc)
+                               want_dres=ctx.has_res, dgamma=dg, dbeta=db, accumulate=acc, fwd_scale=fscale,
+                               fwd_shift=fshift)
         if need_g:
             _notify(gamma)
             _notify(beta)

@@ -79,6 +79,10 @@ class Conv2d(nn.Module):
 
     def forward(self, x: Tensor, /) -> Tensor:
         w = self.weight
+        if (w.dtype == torch.bfloat16 and x.dtype == torch.float32 and self.in_channels <= 8
+                and x.shape[1] == self.in_channels and not x.requires_grad):
+            # network input: fp32 NCHW images straight into the packed-pixel first-layer kernels
+            return Fn.FirstConv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu)
         if x.shape[1] != self.in_channels:
             # a channel-padded input (see arch/_stem.prepare_input): zero-pad the filter to match
             if w.dtype == torch.bfloat16 and x.shape[1] > self.in_channels:

@@ -157,3 +157,40 @@ def run_conv_wgrad(name: str, f32: bool = False) -> dict:
                           out_dtype=torch.float32 if f32 else torch.bfloat16)
     torch.cuda.synchronize()
     return _stats(got, ref)
+
+
+# ----------------------------------------------------------------------------------------- first layer
+FIRST_CASES = {
+    # name: (N, H, W, C, K, R, S, stride, pad)
+    "first_7x7_s2_p3": (4, 64, 64, 3, 64, 7, 7, 2, 3),       # ResNet stem
+    "first_11x11_s4_p2": (2, 67, 67, 3, 64, 11, 11, 4, 2),   # AlexNet stem (two 8-tap groups)
+    "first_3x3_p1": (2, 32, 40, 3, 64, 3, 3, 1, 1),          # VGG stem
+    "first_5x5_c1": (3, 28, 28, 1, 16, 5, 5, 1, 2),
+    "first_7x7_multitile": (32, 224, 224, 3, 64, 7, 7, 2, 3),
+}
+
+
+def run_first_conv(name: str) -> dict:
+    import torch.nn as nn
+    from replicann_b200.nn.layers import Conv2d
+    N, H, W, C, K, R, S, stride, pad = FIRST_CASES[name]
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn((N, C, H, W), generator=g)
+    ref = nn.Conv2d(C, K, (R, S), stride, pad)
+    ours = Conv2d(C, K, (R, S), stride, pad, relu=True).cuda().to(torch.bfloat16)
+    ours.load_state_dict(ref.state_dict())
+    ref.load_state_dict({k: v.float().cpu() for k, v in ours.state_dict().items()})
+    xr = x.to(torch.bfloat16).float()
+    yr = F.relu(ref(xr))
+    dy = _rand(tuple(yr.shape), 22).float()
+    yr.backward(dy)
+    yo = ours(x.cuda())
+    yo.backward(dy.cuda().to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+    torch.cuda.synchronize()
+    st = _stats(yo, yr)
+    sw = _stats(ours.weight.grad, ref.weight.grad)
+    sb = _stats(ours.bias.grad, ref.bias.grad)
+    st["wgrad_rel"], st["wgrad_bad"] = sw["rel"], sw["n_bad"]
+    st["bgrad_rel"] = sb["rel"]
+    st["n_bad"] += sw["n_bad"] + sb["n_bad"]
+    return st

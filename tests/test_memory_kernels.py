@@ -25,7 +25,8 @@ def rnd(shape, seed, dtype=torch.float32, scale=1.0):
 
 
 # ------------------------------------------------------------------------------------------ BatchNorm
-@pytest.mark.parametrize("M,C", [(2 * 14 * 14, 64), (3 * 7 * 7, 256), (1000, 2048), (513, 192), (4096, 8)])
+@pytest.mark.parametrize("M,C", [(2 * 14 * 14, 64), (3 * 7 * 7, 256), (1000, 2048), (513, 192), (4096, 8),
+                                 (8 * 56 * 56, 64), (40000, 256)])
 @pytest.mark.parametrize("relu,res", [(True, False), (True, True), (False, False)])
 def test_batchnorm_fwd_bwd(M, C, relu, res):
     f = RF()
@@ -61,8 +62,11 @@ def test_batchnorm_fwd_bwd(M, C, relu, res):
     assert rel_err(rmd, rm_ref) < 1e-4 and rel_err(rvd, rv_ref) < 1e-3
     dgamma = torch.empty(C, device="cuda")
     dbeta = torch.empty(C, device="cuda")
-    dx, dres = f.bn_bwd(dy.cuda(), xd, y if relu else None, mean, invstd, gd, want_dres=res, dgamma=dgamma,
-                        dbeta=dbeta, accumulate=False)
+    # ReLU mask: from the saved output when a residual was added, else recomputed from x (scale, shift)
+    from_x = relu and not res
+    dx, dres = f.bn_bwd(dy.cuda(), xd, y if (relu and not from_x) else None, mean, invstd, gd, want_dres=res,
+                        dgamma=dgamma, dbeta=dbeta, accumulate=False, fwd_scale=scale if from_x else None,
+                        fwd_shift=shift if from_x else None)
     assert rel_err(dx, xr.grad.reshape(M, C)) < 1e-2
     assert rel_err(dgamma, gr.grad) < 1e-2 and rel_err(dbeta, br.grad) < 1e-2
     if res:

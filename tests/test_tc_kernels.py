@@ -44,3 +44,8 @@ def test_conv_wgrad(name):
 
 def test_conv_wgrad_f32():
     _ok(T.run_conv_wgrad("conv_3x3_p1", f32=True))
+
+
+@pytest.mark.parametrize("name", list(T.FIRST_CASES))
+def test_first_layer_packed_pixel_conv(name):
+    _ok(T.run_first_conv(name))

@@ -21,6 +21,7 @@ def main():
     cases += [("fprop_epi", n, lambda n=n: T.run_conv_fprop(n, epilogue=True)) for n in ("conv_3x3_p1",)]
     cases += [("dgrad", n, lambda n=n: T.run_conv_dgrad(n)) for n in T.CONV_CASES]
     cases += [("wgrad", n, lambda n=n: T.run_conv_wgrad(n)) for n in T.CONV_CASES]
+    cases += [("first", n, lambda n=n: T.run_first_conv(n)) for n in T.FIRST_CASES]
     for kind, name, fn in cases:
         tag = f"{kind}:{name}"
         if filt and not any(f in tag for f in filt):
