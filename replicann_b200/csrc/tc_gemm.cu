@@ -54,6 +54,7 @@ struct TcParams {
   const float* shift;   // per-column shift / bias (nullable)
   const bf16* residual; // added before ReLU (nullable), same indexing as D
   int relu;
+  int tma_store;        // epilogue writes through the third tensor map (dense row mapping only)
   TapDesc taps[MAX_TAPS];
 };
 
@@ -62,20 +63,23 @@ struct Cfg {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
-  static constexpr int TMEM_COLS = 2 * BN;  // 128 / 256 / 512: powers of two
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 1024 /*align*/ + 256 /*barriers*/;
+  static constexpr int ACC_STRIDE = BN == 192 ? 256 : BN;  // TMEM columns between the two accumulators
+  static constexpr int TMEM_COLS = 2 * ACC_STRIDE;         // 128 / 256 / 512: powers of two
+  static constexpr int STAGING_BYTES = 4 * 2 * 4096;       // per epilogue warp: 2 x (32 rows x 128 B)
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
 template <int BN, int KIND, bool A_MN, bool B_MN>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-          const __grid_constant__ TcParams p) {
+          const __grid_constant__ CUtensorMap tmD, const __grid_constant__ TcParams p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + C::STAGES * C::STAGE_BYTES);
+  uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
   uint64_t* empty_bar = full_bar + C::STAGES;
   uint64_t* tfull_bar = empty_bar + C::STAGES;
   uint64_t* tempty_bar = tfull_bar + 2;
@@ -88,6 +92,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmA);
     tc::prefetch_tmap(&tmB);
+    if (p.tma_store) tc::prefetch_tmap(&tmD);
     for (int s = 0; s < C::STAGES; ++s) {
       tc::mbar_init(&full_bar[s], 1);
       tc::mbar_init(&empty_bar[s], 1);
@@ -130,16 +135,32 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           w0 = j * p.ts_w + p.lo_w;
           h0 = i * p.ts_h + p.lo_h;
         }
-        int wtap = 0;
+        // WGRAD: the N dimension is the flattened (tap, channel) space in 64-wide sub-blocks; a tile covers
+        // BN/64 consecutive sub-blocks, which may straddle taps (e.g. 3 taps x 64 channels for BN = 192).
+        int sb0 = 0, nsb_valid = BN / 64;
         if (KIND == KIND_WGRAD) {
-          wtap = nblk / p.ncblk;
-          n0 = (nblk - wtap * p.ncblk) * BN;  // channel offset inside the tap
+          sb0 = nblk * (BN / 64);
+          const int total_sb = p.ntaps * p.ncblk;  // ncblk = 64-channel blocks per tap
+          if (sb0 + nsb_valid > total_sb) nsb_valid = total_sb - sb0;
+        }
+        int sb_c0[BN / 64];
+        uint16_t sb_ow[BN / 64], sb_oh[BN / 64];
+        if (KIND == KIND_WGRAD) {
+#pragma unroll
+          for (int j = 0; j < BN / 64; ++j) {
+            const int sb = sb0 + (j < nsb_valid ? j : 0);
+            const int tap = sb / p.ncblk;
+            sb_c0[j] = (sb - tap * p.ncblk) * 64;
+            sb_ow[j] = (uint16_t)p.taps[tap].ow;
+            sb_oh[j] = (uint16_t)p.taps[tap].oh;
+          }
         }
         for (int it = k_lo; it < k_hi; ++it) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * C::STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
-          tc::mbar_expect_tx(&full_bar[stage], C::STAGE_BYTES);
+          tc::mbar_expect_tx(&full_bar[stage],
+                             KIND == KIND_WGRAD ? (uint32_t)(A_BYTES + nsb_valid * 8192) : (uint32_t)C::STAGE_BYTES);
           if (KIND == KIND_GEMM) {
             const int kc = it * BK;
             if (!A_MN) {
@@ -173,13 +194,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             const int img = pix0 / p.HoWo;
             const int rem = pix0 - img * p.HoWo;
             const int i = rem / p.Wo, j2 = rem - i * p.Wo;
-            const TapDesc td = p.taps[wtap];
             tc::tma_load_2d(sA, &tmA, &full_bar[stage], m0, pix0);
             tc::tma_load_2d(sA + 8192, &tmA, &full_bar[stage], m0 + 64, pix0);
 #pragma unroll
-            for (int j = 0; j < BN / 64; ++j)
-              tc::tma_load_im2col_4d(sB + j * 8192, &tmB, &full_bar[stage], n0 + j * 64, j2 * p.ts_w + p.lo_w,
-                                     i * p.ts_h + p.lo_h, img, (uint16_t)td.ow, (uint16_t)td.oh);
+            for (int j = 0; j < BN / 64; ++j) {
+              if (j < nsb_valid)
+                tc::tma_load_im2col_4d(sB + j * 8192, &tmB, &full_bar[stage], sb_c0[j], j2 * p.ts_w + p.lo_w,
+                                       i * p.ts_h + p.lo_h, img, sb_ow[j], sb_oh[j]);
+            }
           }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -199,7 +221,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
         tc::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * BN);
+        const uint32_t d_tmem = tmem_base + (uint32_t)(acc * C::ACC_STRIDE);
         for (int it = k_lo; it < k_hi; ++it) {
           tc::mbar_wait(&full_bar[stage], phase);
           tc::tc_fence_after();
@@ -222,7 +244,11 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else {
     // ===================================================================== epilogue (warps 2..5)
+    // TMEM -> registers (one row per thread) -> per-warp smem staging (XOR-swizzled 16-byte pieces) ->
+    // coalesced 128-bit global stores: each store instruction writes 4 rows x 128 contiguous bytes.
     const int q = warp & 3;  // TMEM lane quarter this warp may read
+    uint8_t* stage_w = staging + q * 8192;  // two 4 KB buffers
+    int sbuf = 0;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -232,16 +258,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       const int split = t / p.n_mblk;
       const int row = mblk * BM + q * 32 + lane;
       const bool row_ok = row < p.M;
-      int col_base, col_lim_local;  // first D column of this tile; valid columns inside the tile
-      if (KIND == KIND_WGRAD) {
-        const int wtap = nblk / p.ncblk;
-        const int c0 = (nblk - wtap * p.ncblk) * BN;
-        col_base = wtap * p.tapC + c0;
-        col_lim_local = p.N - c0;
-      } else {
-        col_base = nblk * BN;
-        col_lim_local = p.N - col_base;
-      }
+      const int col_base = nblk * BN;
+      const int col_lim_local = p.N - col_base;  // valid columns inside the tile
       long long out_row = row;
       if (KIND == KIND_CONV && p.pix_map && row_ok) {
         const int img = row / p.HoWo;
@@ -249,36 +267,83 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int i = rem / p.Wo, j = rem - i * p.Wo;
         out_row = (long long)img * p.OHOW + (long long)(i * p.os_h + p.oa) * p.OW + (j * p.os_w + p.ob);
       }
+      // byte address of this thread's row at the tile's first column (0 = row does not exist)
+      unsigned long long row_ptr = 0;
+      if (row_ok) {
+        row_ptr = p.ws != nullptr
+                      ? reinterpret_cast<unsigned long long>(p.ws + ((long long)split * p.M + row) * p.ldw + col_base)
+                      : reinterpret_cast<unsigned long long>(reinterpret_cast<bf16*>(p.D) + out_row * p.ldd + col_base);
+      }
       tc::mbar_wait(&tfull_bar[acc], acc_phase);
       tc::tc_fence_after();
-#pragma unroll 1
-      for (int chunk = 0; chunk < BN / 32; ++chunk) {
-        uint32_t r[32];
+      const uint32_t t_acc = tmem_base + (uint32_t)(acc * C::ACC_STRIDE) + ((uint32_t)(q * 32) << 16);
+      // staged write of one 128-byte-per-row chunk: v = this thread's 8 x 16 B, chunk_bytes0 = byte offset of
+      // the chunk inside the row, valid16 = number of 16-byte pieces of the chunk that are inside D
+      // TMA-store variant: the swizzled staging buffer is exactly the SWIZZLE_128B box the output tensor map
+      // expects; one lane hands it to the TMA engine, which also clips rows/columns outside D.
+      auto flush_tma = [&](const uint4* v, int col0, int row0) {
+        if (lane == 0) tc::tma_store_wait_read<1>();  // the store issued two chunks ago has drained its buffer
         __syncwarp();
-        tc::tmem_ld32(tmem_base + (uint32_t)(acc * BN + chunk * 32) + ((uint32_t)(q * 32) << 16), r);
-        tc::tmem_ld_wait();
-        if (!row_ok) {
-          // rows past M hold no data; the aligned TMEM load above still had to run warp-wide
-        } else if (p.ws != nullptr) {
-          float* dst = p.ws + ((long long)split * p.M + row) * p.ldw + col_base + chunk * 32;
+        uint8_t* buf = stage_w + sbuf * 4096;
+        uint4* srow = reinterpret_cast<uint4*>(buf + lane * 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) srow[j ^ (lane & 7)] = v[j];
+        tc::fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) {
+          if (p.ws != nullptr) tc::tma_store_3d(&tmD, buf, col0, row0, split);
+          else tc::tma_store_2d(&tmD, buf, col0, row0);
+          tc::tma_store_commit();
+        }
+        sbuf ^= 1;
+      };
+      auto flush = [&](const uint4* v, int chunk_byte0, int valid16) {
+        uint4* srow = reinterpret_cast<uint4*>(stage_w + lane * 128);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) srow[j ^ (lane & 7)] = v[j];
+        __syncwarp();
+        const int j = lane & 7;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = (lane >> 3) + 4 * i;
+          const uint4 val = reinterpret_cast<const uint4*>(stage_w + rr * 128)[j ^ (rr & 7)];
+          const unsigned long long pr = __shfl_sync(0xffffffffu, row_ptr, rr);
+          if (pr != 0 && j < valid16) *reinterpret_cast<uint4*>(pr + chunk_byte0 + j * 16) = val;
+        }
+        __syncwarp();
+      };
+      if (p.ws != nullptr) {
+        // fp32 partials / fp32 output: 32 columns = 128 bytes per row per chunk
+#pragma unroll 1
+        for (int chunk = 0; chunk < BN / 32; ++chunk) {
+          uint32_t r[32];
+          __syncwarp();
+          tc::tmem_ld32(t_acc + (uint32_t)(chunk * 32), r);
+          tc::tmem_ld_wait();
+          int valid16 = (col_lim_local - chunk * 32) / 4;
+          valid16 = valid16 < 0 ? 0 : (valid16 > 8 ? 8 : valid16);
+          if (p.tma_store) flush_tma(reinterpret_cast<const uint4*>(r), col_base + chunk * 32, mblk * BM + q * 32);
+          else flush(reinterpret_cast<const uint4*>(r), chunk * 128, valid16);
+        }
+      } else {
+        // bf16 output with the fused epilogue: 64 columns = 128 bytes per row per chunk
+#pragma unroll 1
+        for (int chunk = 0; chunk < BN / 64; ++chunk) {
+          uint32_t r[64];
+          __syncwarp();
+          tc::tmem_ld32(t_acc + (uint32_t)(chunk * 64), r);
+          tc::tmem_ld32(t_acc + (uint32_t)(chunk * 64 + 32), r + 32);
+          tc::tmem_ld_wait();
+          uint4 out[8];
+          const int c_first = col_base + chunk * 64;
+          const bf16* res = (p.residual && row_ok) ? p.residual + out_row * p.ldd + c_first : nullptr;
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
-            if (chunk * 32 + g * 4 < col_lim_local) {
-              float4 v = make_float4(__uint_as_float(r[4 * g]), __uint_as_float(r[4 * g + 1]),
-                                     __uint_as_float(r[4 * g + 2]), __uint_as_float(r[4 * g + 3]));
-              *reinterpret_cast<float4*>(dst + g * 4) = v;
-            }
-          }
-        } else {
-          bf16* dst = reinterpret_cast<bf16*>(p.D) + out_row * p.ldd + col_base + chunk * 32;
-          const bf16* res = p.residual ? p.residual + out_row * p.ldd + col_base + chunk * 32 : nullptr;
+            float v[8];
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            if (chunk * 32 + g * 8 < col_lim_local) {
-              float v[8];
-#pragma unroll
-              for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * g + e]);
-              const int c = col_base + chunk * 32 + g * 8;
+            for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * g + e]);
+            if (chunk * 64 + g * 8 < col_lim_local) {
+              const int c = c_first + g * 8;
               if (p.scale) {
                 const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
                 const float4 s1 = __ldg(reinterpret_cast<const float4*>(p.scale + c + 4));
@@ -301,9 +366,13 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
               }
-              *reinterpret_cast<uint4*>(dst + g * 8) = pack8(v);
             }
+            out[g] = pack8(v);
           }
+          int valid16 = (col_lim_local - chunk * 64) / 8;
+          valid16 = valid16 < 0 ? 0 : (valid16 > 8 ? 8 : valid16);
+          if (p.tma_store) flush_tma(out, c_first, mblk * BM + q * 32);
+          else flush(out, chunk * 128, valid16);
         }
       }
       tc::tc_fence_before();
@@ -311,6 +380,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       if (lane == 0) tc::mbar_arrive(&tempty_bar[acc]);
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
+    if (p.tma_store && lane == 0) tc::tma_store_wait<0>();
   }
 
   tc::tc_fence_before();
@@ -423,8 +493,46 @@ int make_tmap_im2col(CUtensorMap* m, const void* ptr, int C, int W, int H, int N
   return RNN_OK;
 }
 
+// Output tensor map for the epilogue's TMA stores: bf16 D[M, ldd] (box 64 x 32) or fp32 partials
+// ws[splits][M][ldw] (box 32 x 32 x 1), SWIZZLE_128B.  Scattered-row outputs (strided dgrad) keep the
+// register->smem->global store path and get a dummy map.
+int make_tmap_out(CUtensorMap* m, TcParams* p) {
+  p->tma_store = 0;
+  memset(m, 0, sizeof(*m));
+  if (p->pix_map) return RNN_OK;
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  CUresult r;
+  if (p->ws != nullptr) {
+    if ((p->ldw * 4) % 16 != 0 || (reinterpret_cast<uintptr_t>(p->ws) & 15u)) return RNN_OK;
+    cuuint64_t gdim[3] = {(cuuint64_t)p->ldw, (cuuint64_t)p->M, (cuuint64_t)p->splits};
+    cuuint64_t gstr[2] = {(cuuint64_t)p->ldw * 4, (cuuint64_t)p->ldw * 4 * (cuuint64_t)p->M};
+    cuuint32_t box[3] = {32u, 32u, 1u};
+    r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, p->ws, gdim, gstr, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    if (p->residual != nullptr) return RNN_OK;  // residual path reads rows per thread; keep it simple
+    if ((p->ldd * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(p->D) & 15u)) return RNN_OK;
+    cuuint64_t gdim[2] = {(cuuint64_t)p->N, (cuuint64_t)p->M};
+    cuuint64_t gstr[1] = {(cuuint64_t)p->ldd * 2};
+    cuuint32_t box[2] = {64u, 32u};
+    r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, p->D, gdim, gstr, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
+  RNN_REQUIRE(r == CUDA_SUCCESS, RNN_ERR_TENSORMAP);
+  p->tma_store = 1;
+  return RNN_OK;
+}
+
 template <int BN, int KIND, bool A_MN, bool B_MN>
-int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
+  TcParams p = p_in;
+  CUtensorMap td;
+  {
+    const int rc = make_tmap_out(&td, &p);
+    if (rc != RNN_OK) return rc;
+  }
   static bool attr_set = false;
   auto kern = tc_kernel<BN, KIND, A_MN, B_MN>;
   if (!attr_set) {
@@ -433,7 +541,7 @@ int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p,
   }
   const int tiles = p.n_mblk * p.n_nblk * p.splits;
   const int grid = tiles < rnn_num_sms() ? tiles : rnn_num_sms();
-  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, p);
+  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, td, p);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
@@ -443,6 +551,7 @@ int launch_bn(int BN, const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
   switch (BN) {
     case 64: return launch_inst<64, KIND, A_MN, B_MN>(ta, tb, p, s);
     case 128: return launch_inst<128, KIND, A_MN, B_MN>(ta, tb, p, s);
+    case 192: return launch_inst<192, KIND, A_MN, B_MN>(ta, tb, p, s);
     case 256: return launch_inst<256, KIND, A_MN, B_MN>(ta, tb, p, s);
   }
   return RNN_ERR_SHAPE;
@@ -484,21 +593,33 @@ struct WgradPlan {
   size_t ws_bytes;
 };
 
-WgradPlan plan_wgrad(const rnn_conv_desc* d) {
+// Tile width (in columns of the [K, taps*C] gradient matrix) for `nsb` 64-wide sub-blocks.
+int wgrad_bn(int nsb) {
+  if (nsb % 4 == 0) return 256;
+  if (nsb % 3 == 0) return 192;
+  if (nsb % 2 == 0) return nsb > 8 ? 256 : 128;
+  return nsb >= 5 ? 256 : 64;
+}
+
+WgradPlan plan_wgrad_cols(int K, int ntaps, int C, long long mpix) {
   WgradPlan w;
-  w.BN = (d->C % 256 == 0) ? 256 : (d->C % 128 == 0 ? 128 : 64);
-  w.n_mblk = ceil_div_i(d->K, BM);
-  w.ncblk = ceil_div_i(d->C, w.BN);
-  const long long mpix = (long long)d->N * d->P * d->Q;
+  const int nsb = ntaps * (C / 64);
+  w.BN = wgrad_bn(nsb);
+  w.n_mblk = ceil_div_i(K, BM);
+  w.ncblk = ceil_div_i(nsb, w.BN / 64);  // number of N tiles
   w.k_iters = ceil_div_i(mpix, BK);
-  const int base = w.n_mblk * w.ncblk * d->R * d->S;
+  const int base = w.n_mblk * w.ncblk;
   const int sms = rnn_num_sms();
   int s = ceil_div_i(sms, base);
   if (s > w.k_iters / 4) s = w.k_iters / 4;
   if (s < 1) s = 1;
   w.splits = s;
-  w.ws_bytes = (size_t)s * d->K * d->R * d->S * d->C * sizeof(float);
+  w.ws_bytes = (size_t)s * K * ntaps * C * sizeof(float);
   return w;
+}
+
+WgradPlan plan_wgrad(const rnn_conv_desc* d) {
+  return plan_wgrad_cols(d->K, d->R * d->S, d->C, (long long)d->N * d->P * d->Q);
 }
 
 }  // namespace
@@ -727,13 +848,13 @@ int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy,
 
   TcParams p;
   memset(&p, 0, sizeof(p));
-  p.M = d->K; p.N = d->C;
+  p.M = d->K; p.N = d->R * d->S * d->C;   // D = [K, taps*C]
   p.k_iters = w.k_iters;
   p.splits = w.splits;
   p.ntaps = d->R * d->S;
-  p.ncblk = w.ncblk; p.tapC = d->C;
+  p.ncblk = d->C / 64;                    // 64-channel sub-blocks per tap
   p.n_mblk = w.n_mblk;
-  p.n_nblk = p.ntaps * w.ncblk;
+  p.n_nblk = w.ncblk;
   p.Wo = d->Q; p.HoWo = d->P * d->Q;
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
   p.ws = reinterpret_cast<float*>(ws);
@@ -833,19 +954,7 @@ int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, co
 }
 
 static WgradPlan plan_first_wgrad(const rnn_conv_desc* d, const FirstGeom& g) {
-  WgradPlan w;
-  w.BN = 64;
-  w.n_mblk = ceil_div_i(d->K, BM);
-  w.ncblk = 1;
-  const long long mpix = (long long)d->N * d->P * d->Q;
-  w.k_iters = ceil_div_i(mpix, BK);
-  const int base = w.n_mblk * g.ntaps;
-  int s = ceil_div_i(rnn_num_sms(), base);
-  if (s > w.k_iters / 4) s = w.k_iters / 4;
-  if (s < 1) s = 1;
-  w.splits = s;
-  w.ws_bytes = (size_t)s * d->K * g.ntaps * 64 * sizeof(float);
-  return w;
+  return plan_wgrad_cols(d->K, g.ntaps, 64, (long long)d->N * d->P * d->Q);
 }
 
 size_t rnn_conv2d_first_wgrad_workspace(const rnn_conv_desc* d) {
@@ -874,10 +983,10 @@ int rnn_conv2d_first_wgrad_bf16(const rnn_conv_desc* d, const void* x_packed, co
   if (rc != RNN_OK) return rc;
   TcParams p;
   memset(&p, 0, sizeof(p));
-  p.M = d->K; p.N = 64;
+  p.M = d->K; p.N = g.ntaps * 64;
   p.k_iters = w.k_iters; p.splits = w.splits;
-  p.ntaps = g.ntaps; p.ncblk = 1; p.tapC = 64;
-  p.n_mblk = w.n_mblk; p.n_nblk = g.ntaps;
+  p.ntaps = g.ntaps; p.ncblk = 1;
+  p.n_mblk = w.n_mblk; p.n_nblk = w.ncblk;
   p.Wo = d->Q; p.HoWo = d->P * d->Q;
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = 0; p.lo_h = 0;
   p.ws = reinterpret_cast<float*>(ws);
