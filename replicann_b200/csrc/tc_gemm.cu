@@ -69,7 +69,9 @@ struct Cfg {
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
-template <int BN, int KIND, bool A_MN, bool B_MN>
+// FUSED = the bf16 epilogue applies scale / shift / residual / ReLU; the plain variant (most convolutions of
+// a BatchNorm network, every dgrad) compiles to convert + store only.
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmD, const __grid_constant__ TcParams p) {
@@ -336,13 +338,13 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           tc::tmem_ld_wait();
           uint4 out[8];
           const int c_first = col_base + chunk * 64;
-          const bf16* res = (p.residual && row_ok) ? p.residual + out_row * p.ldd + c_first : nullptr;
+          const bf16* res = (FUSED && p.residual && row_ok) ? p.residual + out_row * p.ldd + c_first : nullptr;
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
             float v[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) v[e] = __uint_as_float(r[8 * g + e]);
-            if (chunk * 64 + g * 8 < col_lim_local) {
+            if (FUSED && chunk * 64 + g * 8 < col_lim_local) {
               const int c = c_first + g * 8;
               if (p.scale) {
                 const float4 s0 = __ldg(reinterpret_cast<const float4*>(p.scale + c));
@@ -525,8 +527,8 @@ int make_tmap_out(CUtensorMap* m, TcParams* p) {
   return RNN_OK;
 }
 
-template <int BN, int KIND, bool A_MN, bool B_MN>
-int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED>
+int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
   TcParams p = p_in;
   CUtensorMap td;
   {
@@ -534,7 +536,7 @@ int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_
     if (rc != RNN_OK) return rc;
   }
   static bool attr_set = false;
-  auto kern = tc_kernel<BN, KIND, A_MN, B_MN>;
+  auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED>;
   if (!attr_set) {
     RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
     attr_set = true;
@@ -544,6 +546,16 @@ int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_
   kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, td, p);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
+}
+
+template <int BN, int KIND, bool A_MN, bool B_MN>
+int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+  // wgrad and the MN-major-A GEMM (Linear wgrad) never carry a fused epilogue
+  if constexpr (KIND != KIND_WGRAD && !A_MN) {
+    if (p.ws == nullptr && (p.scale || p.shift || p.residual || p.relu))
+      return launch_inst2<BN, KIND, A_MN, B_MN, true>(ta, tb, p, stream);
+  }
+  return launch_inst2<BN, KIND, A_MN, B_MN, false>(ta, tb, p, stream);
 }
 
 template <int KIND, bool A_MN, bool B_MN>
