@@ -130,7 +130,7 @@ def run_reference(args) -> None:
                          "sample": f"{args.steps} ResNet-50 fp32 training steps of {batch} images, numpy oracle"},
         "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
@@ -318,12 +318,45 @@ def run_gpu(args) -> None:
         }
         if cpu_base is not None:
             line["cpu_baseline"] = cpu_base
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+class _StdoutGuard:
+    """Libraries (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line on stdout.
+    Everything except the final line is diverted to stderr."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.real = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def emit(self, line: str) -> None:
+        sys.stdout.flush()
+        os.write(self.real, (line + "\n").encode())
+
+    def __exit__(self, *exc):
+        sys.stdout.flush()
+        os.dup2(self.real, 1)
+        os.close(self.real)
+        return False
+
+
+_GUARD = None
+
+
+def _emit(obj) -> None:
+    line = json.dumps(obj)
+    if _GUARD is not None:
+        _GUARD.emit(line)
+    else:
+        print(line, flush=True)
+
+
 def main() -> None:
+    global _GUARD
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -333,10 +366,13 @@ def main() -> None:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--detail", default="", help="write a per-layer kernel timing table to this file")
     args = ap.parse_args()
-    if args.impl == "reference":
-        run_reference(args)
-    else:
-        run_gpu(args)
+    with _StdoutGuard() as g:
+        _GUARD = g
+        if args.impl == "reference":
+            run_reference(args)
+        else:
+            run_gpu(args)
+        _GUARD = None
 
 
 if __name__ == "__main__":

@@ -199,6 +199,29 @@ int rnn_softmax_ce(const void* logits, const long long* target, long long rows, 
 /* torch.argmax(x, dim=-1): first maximum wins. */
 int rnn_argmax(const void* x, long long* out, long long rows, int cols, int is_f32, cudaStream_t stream);
 
+/* ---- fused attention ------------------------------------------------------------------------------- */
+/* All heads of one multi-head module in one launch.  q/k/v/z/dz are addressed as
+ * base + b*bs + row*rs + head*hs + d (elements): the packed projection output and the reference's
+ * torch.cat(heads, -1) layout (nn/attention.py:157-160,180).  mask: [mask_b][T][Tk] through (mask_bs, mask_rs);
+ * mask_kind 1 = bool/uint8, nonzero masks OUT (-inf, :39-40); 2 = float32 additive (:41-42). */
+typedef struct {
+  int B, H, T, Tk, hs;
+  long long q_bs, q_rs, k_bs, k_rs, v_bs, v_rs, z_bs, z_rs, dz_bs, dz_rs;
+  float scale;          /* 1/sqrt(in_dim): the EMBEDDING size (nn/attention.py:24) */
+  int mask_kind;
+  long long mask_bs, mask_rs;
+  float p_drop;         /* dropout on the attention weights (:46); 0 in eval mode */
+  unsigned long long seed, offset;
+} rnn_attn_desc;
+/* _AttentionHead._attention (nn/attention.py:28-50) for H heads: z = dropout(softmax(q k^T*scale (+mask))) v.
+ * lse [B,H,T] (nullable in inference) is saved for the backward pass. */
+int rnn_attention_fwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask, void* z,
+                      float* lse, int is_f32, cudaStream_t stream);
+/* autograd of the same: dq, dk, dv (same strides as q, k, v); delta is [B,H,T] fp32 scratch. */
+int rnn_attention_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                      const void* z, const void* dz, const float* lse, float* delta, void* dq, void* dk, void* dv,
+                      int is_f32, cudaStream_t stream);
+
 /* ---- fused optimizers over flat buckets ---------------------------------------------------------- */
 /* torch.optim.SGD (momentum, dampening, nesterov, weight_decay) on an fp32 master copy. */
 int rnn_sgd_step(float* w, float* buf, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16, long long n,

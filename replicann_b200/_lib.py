@@ -24,6 +24,13 @@ class ConvDesc(C.Structure):
                 ("N", "H", "W", "C", "K", "R", "S", "stride_h", "stride_w", "pad_h", "pad_w", "P", "Q")]
 
 
+class AttnDesc(C.Structure):
+    _fields_ = ([(n, C.c_int) for n in ("B", "H", "T", "Tk", "hs")] +
+                [(n, C.c_longlong) for n in ("q_bs", "q_rs", "k_bs", "k_rs", "v_bs", "v_rs", "z_bs", "z_rs", "dz_bs", "dz_rs")] +
+                [("scale", C.c_float), ("mask_kind", C.c_int), ("mask_bs", C.c_longlong), ("mask_rs", C.c_longlong),
+                 ("p_drop", C.c_float), ("seed", C.c_ulonglong), ("offset", C.c_ulonglong)])
+
+
 def conv_desc(N, H, W, Cin, K, R, S, stride, pad) -> ConvDesc:
     sh, sw = (stride, stride) if isinstance(stride, int) else stride
     ph, pw = (pad, pad) if isinstance(pad, int) else pad
@@ -41,6 +48,8 @@ def _ctype(decl: str):
     if "*" in d:
         if "rnn_conv_desc" in d:
             return C.POINTER(ConvDesc)
+        if "rnn_attn_desc" in d:
+            return C.POINTER(AttnDesc)
         if d.startswith("const char"):
             return C.c_char_p
         return C.c_void_p

@@ -559,3 +559,62 @@ def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight
                              int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
                              float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
                              float(grad_scale), cur_stream()), "rnn_adamw_step")
+
+
+# =========================================================================================== attention
+def _attn_desc(B, H, T, Tk, hs, q, k, v, z, dz, scale, mask, p_drop, seed, offset):
+    from ._lib import AttnDesc
+    d = AttnDesc()
+    d.B, d.H, d.T, d.Tk, d.hs = B, H, T, Tk, hs
+    d.q_bs, d.q_rs = q.stride(0), q.stride(1)
+    d.k_bs, d.k_rs = k.stride(0), k.stride(1)
+    d.v_bs, d.v_rs = v.stride(0), v.stride(1)
+    d.z_bs, d.z_rs = z.stride(0), z.stride(1)
+    if dz is not None:
+        d.dz_bs, d.dz_rs = dz.stride(0), dz.stride(1)
+    d.scale = float(scale)
+    d.p_drop, d.seed, d.offset = float(p_drop), int(seed), int(offset)
+    if mask is None:
+        d.mask_kind = 0
+    else:
+        d.mask_kind = 1 if mask.dtype in (torch.bool, torch.uint8) else 2
+        if mask.dim() == 2:
+            d.mask_bs, d.mask_rs = 0, mask.stride(0)
+        else:
+            d.mask_bs, d.mask_rs = (mask.stride(0) if mask.shape[0] > 1 else 0), mask.stride(1)
+    return d
+
+
+def _check_qkv(t, name):
+    if t.dim() != 3 or t.stride(2) != 1:
+        raise ValueError(f"{name} must be [B, T, H*hs] with unit stride in the last dimension")
+
+
+def attention_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, offset=0, need_lse=True):
+    """q [B,T,H*hs], k/v [B,Tk,H*hs] (views allowed) -> z [B,T,H*hs] contiguous, lse [B,H,T] fp32."""
+    lib = _lib.load(); _cuda(q, k, v, mask)
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _check_qkv(t, n)
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    z = torch.empty((B, T, n_heads * hs), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, n_heads, T), dtype=torch.float32, device=q.device) if need_lse else None
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, None, scale, mask, p_drop, seed, offset)
+    check(lib.rnn_attention_fwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(lse), _is_f32(q), cur_stream()),
+          "rnn_attention_fwd")
+    return z, lse
+
+
+def attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):
+    """Writes dq/dk/dv (pre-allocated, same strides as q/k/v)."""
+    lib = _lib.load(); _cuda(q, k, v, z, dz)
+    _check_qkv(dz, "dz")
+    for a, b, n in ((dq, q, "dq"), (dk, k, "dk"), (dv, v, "dv")):
+        if a.stride() != b.stride() or a.shape != b.shape:
+            raise ValueError(f"{n} must have the shape and strides of its forward tensor")
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    delta = torch.empty((B, n_heads, T), dtype=torch.float32, device=q.device)
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, dz, scale, mask, p_drop, seed, offset)
+    check(lib.rnn_attention_bwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(dz), ptr(lse), ptr(delta), ptr(dq),
+                                ptr(dk), ptr(dv), _is_f32(q), cur_stream()), "rnn_attention_bwd")

@@ -456,3 +456,44 @@ class SoftmaxFn(Function):
         (y,) = ctx.saved_tensors
         d2 = dy.reshape(y.shape)
         return RF.softmax_bwd(d2 if d2.is_contiguous() else d2.contiguous(), y).reshape(ctx.shape)
+
+
+# ------------------------------------------------------------------------------------------ attention
+class AttentionFn(Function):
+    """z = dropout(softmax(q k^T * scale (+ mask))) v for all heads at once (nn/attention.py:28-50).
+
+    `packed=True`: the first argument is the packed projection [B, T, 3*H*hs] (q | k | v column blocks) and
+    a single packed gradient is returned; otherwise q, k, v are separate [B, T(k), H*hs] tensors."""
+
+    @staticmethod
+    def forward(ctx, q_or_qkv, k, v, mask, scale, p_drop, n_heads, hs, seed, offset, packed):
+        Hh = n_heads * hs
+        if packed:
+            qkv = q_or_qkv if q_or_qkv.is_contiguous() else q_or_qkv.contiguous()
+            q, k, v = qkv[..., :Hh], qkv[..., Hh:2 * Hh], qkv[..., 2 * Hh:]
+        else:
+            q = q_or_qkv if q_or_qkv.stride(-1) == 1 else q_or_qkv.contiguous()
+            k = k if k.stride(-1) == 1 else k.contiguous()
+            v = v if v.stride(-1) == 1 else v.contiguous()
+        z, lse = RF.attention_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
+        ctx.cfg = (scale, p_drop, n_heads, hs, seed, offset, packed)
+        ctx.save_for_backward(q, k, v, z, lse, mask)
+        return z
+
+    @staticmethod
+    def backward(ctx, dz):
+        q, k, v, z, lse, mask = ctx.saved_tensors
+        scale, p_drop, n_heads, hs, seed, offset, packed = ctx.cfg
+        dz = dz if dz.stride(-1) == 1 else dz.contiguous()
+        Hh = n_heads * hs
+        if packed:
+            dqkv = torch.empty((q.shape[0], q.shape[1], 3 * Hh), dtype=q.dtype, device=q.device)
+            dq, dk, dv = dqkv[..., :Hh], dqkv[..., Hh:2 * Hh], dqkv[..., 2 * Hh:]
+        else:
+            dq = torch.empty_strided(q.shape, q.stride(), dtype=q.dtype, device=q.device)
+            dk = torch.empty_strided(k.shape, k.stride(), dtype=k.dtype, device=k.device)
+            dv = torch.empty_strided(v.shape, v.stride(), dtype=v.dtype, device=v.device)
+        RF.attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
+        if packed:
+            return dqkv, None, None, None, None, None, None, None, None, None, None
+        return dq, dk, dv, None, None, None, None, None, None, None, None
