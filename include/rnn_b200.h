@@ -173,12 +173,13 @@ int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const 
                       void* ws, size_t ws_bytes, cudaStream_t stream);
 
 /* ---- pooling (NHWC) ------------------------------------------------------------------------------ */
-/* torch.nn.MaxPool2d(return_indices=True): indices are h*W+w inside the input plane (int32), first
- * maximum in window order, NaN propagates -- bit-exact with ATen. */
-int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, int N, int H, int W, int C, int R, int S, int sh, int sw,
-                      int ph, int pw, int is_f32, cudaStream_t stream);
-int rnn_maxpool2d_bwd(const void* dy, const int* indices, void* dx, int N, int H, int W, int C, int R, int S, int sh,
-                      int sw, int ph, int pw, int is_f32, cudaStream_t stream);
+/* torch.nn.MaxPool2d(return_indices=True): indices (nullable) are h*W+w inside the input plane (int32), first
+ * maximum in window order, NaN propagates -- bit-exact with ATen.  window_idx (nullable) is the same argmax as
+ * a 1-byte position inside the window (r*S+s), the compact form the backward pass reads; pass either to bwd. */
+int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
+                      int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream);
+int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
+                      int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream);
 /* torch.nn.AvgPool2d (count_include_pad=True, ceil_mode=False). */
 int rnn_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
                       int is_f32, cudaStream_t stream);

@@ -110,25 +110,19 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
   }
 }
 
-// Sum the per-block partials: one block handles 32 channels, 8 threads per channel walk the partial rows
-// (coalesced across channels), then a shared-memory tree combines them in a fixed order.
-__device__ __forceinline__ void sum_partials_32x8(const float* __restrict__ partials, int nparts, int C, int c,
-                                                  int lane8, float* sm /* [2][8][32] */, float& s, float& ss) {
+// Sum the per-block partials: one WARP per channel (8 channels per 256-thread block); the 32 lanes stride
+// over the partial rows and a shuffle tree combines them in a fixed order (deterministic).
+__device__ __forceinline__ void sum_partials_warp(const float* __restrict__ partials, int nparts, int C, int c,
+                                                  float& s, float& ss) {
+  const int lane = threadIdx.x & 31;
   float a = 0.f, b = 0.f;
   if (c < C)
-    for (int p = lane8; p < nparts; p += 8) {
+    for (int p = lane; p < nparts; p += 32) {
       a += partials[(long long)p * 2 * C + c];
       b += partials[(long long)p * 2 * C + C + c];
     }
-  const int cl = threadIdx.x & 31;
-  sm[lane8 * 32 + cl] = a;
-  sm[256 + lane8 * 32 + cl] = b;
-  __syncthreads();
-  s = 0.f; ss = 0.f;
-  if (lane8 == 0) {
-#pragma unroll
-    for (int l = 0; l < 8; ++l) { s += sm[l * 32 + cl]; ss += sm[256 + l * 32 + cl]; }
-  }
+  s = warp_sum(a);
+  ss = warp_sum(b);
 }
 
 __global__ void __launch_bounds__(256)
@@ -137,12 +131,10 @@ bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, 
                          float momentum, float* running_mean, float* running_var,
                          float* __restrict__ mean, float* __restrict__ invstd,
                          float* __restrict__ scale, float* __restrict__ shift) {
-  __shared__ float sm[512];
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int lane8 = threadIdx.x >> 5;
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
   float s, ss;
-  sum_partials_32x8(partials, nparts, C, c, lane8, sm, s, ss);
-  if (lane8 != 0 || c >= C) return;
+  sum_partials_warp(partials, nparts, C, c, s, ss);
+  if ((threadIdx.x & 31) != 0 || c >= C) return;
   const float m = s / count;
   float var = ss / count - m * m;
   var = var < 0.f ? 0.f : var;
@@ -177,12 +169,10 @@ bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
                        void* dgamma, void* dbeta, int grads_f32, int accumulate,
                        const float* __restrict__ mean, const float* __restrict__ invstd,
                        const float* __restrict__ gamma, float inv_count, float* __restrict__ coef /* [3][C] */) {
-  __shared__ float sm[512];
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
-  const int lane8 = threadIdx.x >> 5;
+  const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
   float s, ss;
-  sum_partials_32x8(partials, nparts, C, c, lane8, sm, s, ss);
-  if (lane8 != 0 || c >= C) return;
+  sum_partials_warp(partials, nparts, C, c, s, ss);
+  if ((threadIdx.x & 31) != 0 || c >= C) return;
   sum_dy[c] = s;
   sum_dy_xhat[c] = ss;
   {
@@ -491,7 +481,7 @@ int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, con
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            (float*)ws);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift);
   RNN_CHECK_LAUNCH();
@@ -535,7 +525,7 @@ int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gam
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            scratch);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift);
   RNN_CHECK_LAUNCH();
@@ -581,7 +571,7 @@ int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable
   bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
                                                           invstd, M, C, (float*)ws, fwd_scale, fwd_shift);
   RNN_CHECK_LAUNCH();
-  bn_bwd_finalize_kernel<<<ceil_div_i(C, 32), 256, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
+  bn_bwd_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
                                                                 dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
                                                                 1.f / (float)M, coef);
   RNN_CHECK_LAUNCH();

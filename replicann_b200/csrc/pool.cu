@@ -38,7 +38,8 @@ struct PoolGeom {
 
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
-maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx, PoolGeom g) {
+maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx,
+                   unsigned char* __restrict__ widx, PoolGeom g) {
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.P * g.Q * cgs;
@@ -69,13 +70,21 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
 #pragma unroll
       for (int e = 0; e < VW; ++e) idx[o + e] = bi[e];
     }
+    if (widx) {  // position inside the (unclipped) window: 1 byte instead of 4 for the backward pass
+#pragma unroll
+      for (int e = 0; e < VW; ++e) {
+        const int bh = bi[e] / g.W, bw = bi[e] - bh * g.W;
+        widx[o + e] = (unsigned char)((bh - h0) * g.S + (bw - w0));
+      }
+    }
   }
 }
 
 // Gather form of the backward pass: every input element sums the dy of the windows whose argmax it is.
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
-maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, T* __restrict__ dx, PoolGeom g) {
+maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const unsigned char* __restrict__ widx,
+                   T* __restrict__ dx, PoolGeom g) {
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.H * g.W * cgs;
@@ -99,9 +108,16 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, T* __r
         const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
         float d[VW];
         PV<T, VEC>::load(dy + o, d);
+        if (widx) {
+          const int local = (h - (p * g.sh - g.ph)) * g.S + (w - (q * g.sw - g.pw));
 #pragma unroll
-        for (int e = 0; e < VW; ++e)
-          if (idx[o + e] == me) acc[e] += d[e];
+          for (int e = 0; e < VW; ++e)
+            if ((int)widx[o + e] == local) acc[e] += d[e];
+        } else {
+#pragma unroll
+          for (int e = 0; e < VW; ++e)
+            if (idx[o + e] == me) acc[e] += d[e];
+        }
       }
     PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
   }
@@ -247,8 +263,9 @@ int make_geom(PoolGeom* g, int N, int H, int W, int C, int R, int S, int sh, int
 
 extern "C" {
 
-int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, int N, int H, int W, int C, int R, int S, int sh, int sw,
-                      int ph, int pw, int is_f32, cudaStream_t stream) {
+int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
+                      int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+  RNN_REQUIRE(R * S <= 255, RNN_ERR_SHAPE);
   PoolGeom g;
   const int vw = is_f32 ? 4 : 8;
   const bool vec = C % vw == 0;
@@ -256,17 +273,18 @@ int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, int N, int H, int W,
   if (rc != RNN_OK) return rc;
   const long long total = (long long)N * g.P * g.Q * (vec ? C / vw : C);
   if (is_f32) {
-    if (vec) maxpool_fwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, g);
-    else maxpool_fwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, g);
+    if (vec) maxpool_fwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g);
+    else maxpool_fwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g);
   } else {
-    if (vec) maxpool_fwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, g);
-    else maxpool_fwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, g);
+    if (vec) maxpool_fwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g);
+    else maxpool_fwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g);
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
-int rnn_maxpool2d_bwd(const void* dy, const int* indices, void* dx, int N, int H, int W, int C, int R, int S, int sh,
-                      int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
+                      int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+  RNN_REQUIRE((indices != nullptr) != (window_idx != nullptr), RNN_ERR_SHAPE);  // exactly one index source
   PoolGeom g;
   const int vw = is_f32 ? 4 : 8;
   const bool vec = C % vw == 0;
@@ -274,11 +292,11 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, void* dx, int N, int H
   if (rc != RNN_OK) return rc;
   const long long total = (long long)N * H * W * (vec ? C / vw : C);
   if (is_f32) {
-    if (vec) maxpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, (float*)dx, g);
-    else maxpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, (float*)dx, g);
+    if (vec) maxpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g);
+    else maxpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g);
   } else {
-    if (vec) maxpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, (bf16*)dx, g);
-    else maxpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, (bf16*)dx, g);
+    if (vec) maxpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g);
+    else maxpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g);
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;

@@ -445,25 +445,27 @@ def _pool_args(x, k, s, p):
     return N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q
 
 
-def maxpool2d_fwd(x, k, s, p, return_indices=True):
+def maxpool2d_fwd(x, k, s, p, return_indices=True, return_window_idx=False):
+    """Returns (y, idx int32 or None, window_idx uint8 or None)."""
     lib = _lib.load(); _cuda(x); _contig(x, "x")
     N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q = _pool_args(x, k, s, p)
     y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
     idx = torch.empty((N, P, Q, Cn), dtype=torch.int32, device=x.device) if return_indices else None
-    check(lib.rnn_maxpool2d_fwd(ptr(x), ptr(y), ptr(idx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x),
+    widx = torch.empty((N, P, Q, Cn), dtype=torch.uint8, device=x.device) if return_window_idx else None
+    check(lib.rnn_maxpool2d_fwd(ptr(x), ptr(y), ptr(idx), ptr(widx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x),
                                 cur_stream()), "rnn_maxpool2d_fwd")
-    return y, idx
+    return y, idx, widx
 
 
-def maxpool2d_bwd(dy, idx, x_shape, k, s, p):
+def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None):
     lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
     N, H, W, Cn = x_shape
     kh, kw = (k, k) if isinstance(k, int) else k
     sh, sw = (s, s) if isinstance(s, int) else s
     ph, pw = (p, p) if isinstance(p, int) else p
     dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
-    check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy),
-                                cur_stream()), "rnn_maxpool2d_bwd")
+    check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx) if window_idx is None else None, ptr(window_idx), ptr(dx), N, H, W,
+                                Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()), "rnn_maxpool2d_bwd")
     return dx
 
 

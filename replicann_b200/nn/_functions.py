@@ -384,20 +384,27 @@ class DropoutFn(Function):
 
 # ------------------------------------------------------------------------------------------ pooling
 class MaxPool2dFn(Function):
+    """Returns (y, indices).  `indices` (ATen's flat argmax) is only produced on request; the backward pass
+    uses the 1-byte in-window argmax."""
+
     @staticmethod
-    def forward(ctx, x, k, s, p):
+    def forward(ctx, x, k, s, p, want_indices):
         xh = nhwc(x)
-        y, idx = RF.maxpool2d_fwd(xh, k, s, p)
+        y, idx, widx = RF.maxpool2d_fwd(xh, k, s, p, return_indices=want_indices, return_window_idx=True)
         ctx.cfg = (tuple(xh.shape), k, s, p)
-        ctx.save_for_backward(idx)
+        ctx.save_for_backward(widx)
+        if idx is None:
+            idx = torch.empty(0, dtype=torch.int32, device=x.device)
+            ctx.mark_non_differentiable(idx)
+            return nchw(y), idx
         ctx.mark_non_differentiable(idx)
         return nchw(y), nchw(idx)
 
     @staticmethod
     def backward(ctx, dy, _didx):
-        (idx,) = ctx.saved_tensors
+        (widx,) = ctx.saved_tensors
         shape, k, s, p = ctx.cfg
-        return nchw(RF.maxpool2d_bwd(nhwc(dy), idx, shape, k, s, p)), None, None, None
+        return nchw(RF.maxpool2d_bwd(nhwc(dy), None, shape, k, s, p, window_idx=widx)), None, None, None, None
 
 
 class AvgPool2dFn(Function):

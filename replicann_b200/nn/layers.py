@@ -146,6 +146,7 @@ class BatchNorm2d(nn.Module):
         self.register_buffer("running_mean", torch.zeros(num_features, device=device, dtype=torch.float32))
         self.register_buffer("running_var", torch.ones(num_features, device=device, dtype=torch.float32))
         self.register_buffer("num_batches_tracked", torch.tensor(0, dtype=torch.long, device=device))
+        self._batches_pending = 0  # counted on the host; folded into the buffer when the state is read
 
     def _apply(self, fn, recurse=True):
         super()._apply(fn, recurse)
@@ -170,9 +171,22 @@ class BatchNorm2d(nn.Module):
     def momentum(self) -> float:
         return self._momentum
 
+    def _flush_counter(self) -> None:
+        if self._batches_pending:
+            self.num_batches_tracked += self._batches_pending
+            self._batches_pending = 0
+
+    def state_dict(self, *args, **kwargs):
+        self._flush_counter()
+        return super().state_dict(*args, **kwargs)
+
+    def _save_to_state_dict(self, destination, prefix, keep_vars):
+        self._flush_counter()
+        super()._save_to_state_dict(destination, prefix, keep_vars)
+
     def forward(self, x: Tensor, /, residual: Tensor | None = None) -> Tensor:
         if self.training:
-            self.num_batches_tracked += 1
+            self._batches_pending += 1  # no per-step device kernel for a counter nothing on the GPU reads
         return Fn.BatchNormFn.apply(x, self.weight, self.bias, residual, self.running_mean, self.running_var,
                                     self.training, self._momentum, self._eps, self._relu)
 
@@ -226,7 +240,7 @@ class MaxPool2d(nn.Module):
         self._return_indices = return_indices
 
     def forward(self, x: Tensor, /):
-        y, idx = Fn.MaxPool2dFn.apply(x, self._k, self._s, self._p)
+        y, idx = Fn.MaxPool2dFn.apply(x, self._k, self._s, self._p, self._return_indices)
         if self._return_indices:
             return y, idx.long()
         return y

@@ -2,17 +2,28 @@
 
 The reference has no training entry point; this is the B200 form of
 `loss = F.cross_entropy(model(x), y); loss.backward(); opt.step()`.
+
+`cuda_graph=True` captures one whole step (every kernel of forward, backward and the optimizer, ~500
+launches for ResNet-50) into a CUDA graph after a few eager warm-up steps and replays it afterwards: the
+launch-bound gaps between the many small kernels disappear and the host does one launch per step.
 """
 from __future__ import annotations
 
 import torch
 
-from .nn.layers import cross_entropy
+from .nn.layers import Dropout, cross_entropy
 
 
 class Trainer:
-    def __init__(self, model: torch.nn.Module, optimizer, *, loss_fn=cross_entropy, data_parallel=None) -> None:
+    def __init__(self, model: torch.nn.Module, optimizer, *, loss_fn=cross_entropy, data_parallel=None,
+                 cuda_graph: bool = False, graph_warmup: int = 3) -> None:
         self._model, self._opt, self._loss_fn, self._dp = model, optimizer, loss_fn, data_parallel
+        self._want_graph, self._graph_warmup = cuda_graph, graph_warmup
+        self._graph = None
+        self._eager_steps = 0
+        self._gx = self._gy = self._gloss = None
+        if cuda_graph:
+            self._check_graph_safe()
 
     @property
     def model(self) -> torch.nn.Module:
@@ -22,8 +33,23 @@ class Trainer:
     def optimizer(self):
         return self._opt
 
-    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        """One optimisation step on a batch already resident on the device; returns the (device) loss."""
+    @property
+    def graph_captured(self) -> bool:
+        return self._graph is not None
+
+    def _check_graph_safe(self) -> None:
+        """A captured step replays identical kernel arguments, so anything that must change from step to
+        step on the host side (dropout counters, Adam's bias correction, NCCL work handles) rules it out."""
+        from .optim import SGD
+        if not isinstance(self._opt, SGD):
+            raise ValueError("cuda_graph=True supports the SGD optimizer only (AdamW's step count is a host value)")
+        if self._dp is not None and self._dp.world_size > 1:
+            raise ValueError("cuda_graph=True is single-GPU for now (the overlapped all-reduce runs eagerly)")
+        for m in self._model.modules():
+            if isinstance(m, Dropout) and m.p > 0 and self._model.training:
+                raise ValueError("cuda_graph=True needs a model without active dropout (the RNG counter is host-side)")
+
+    def _eager_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self._opt.zero_grad()
         if self._dp is not None:
             self._dp.begin_step()
@@ -34,8 +60,40 @@ class Trainer:
         self._opt.step()
         return loss.detach()
 
+    def _capture(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        self._gx = torch.empty_like(x)
+        self._gy = torch.empty_like(y)
+        self._gx.copy_(x)
+        self._gy.copy_(y)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._gloss = self._eager_step(self._gx, self._gy)
+        self._graph = g
+
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One optimisation step on a batch already resident on the device; returns the (device) loss."""
+        if not self._want_graph:
+            return self._eager_step(x, y)
+        if self._graph is None:
+            if self._eager_steps < self._graph_warmup:
+                self._eager_steps += 1
+                return self._eager_step(x, y)
+            self._capture(x, y)
+        elif x.shape != self._gx.shape or x.dtype != self._gx.dtype:
+            raise ValueError("the captured step takes batches of the shape and dtype it was captured with")
+        self._gx.copy_(x, non_blocking=True)
+        self._gy.copy_(y, non_blocking=True)
+        self._graph.replay()
+        return self._gloss
+
     def step_from_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> float:
         """End-to-end step: pinned host batch -> device, train step, loss back to the host."""
+        if self._graph is not None:
+            self._gx.copy_(x_host, non_blocking=True)
+            self._gy.copy_(y_host, non_blocking=True)
+            self._graph.replay()
+            return float(self._gloss.item())
         dev = next(self._model.parameters()).device
         x = x_host.to(dev, non_blocking=True)
         y = y_host.to(dev, non_blocking=True)

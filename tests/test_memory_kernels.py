@@ -120,13 +120,16 @@ def test_maxpool_indices_bit_exact(dtype, N, H, W, C, k, s, p):
     x = (x * 2).round() / 2
     xr = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
     ref, ridx = F.max_pool2d(xr, k, s, p, return_indices=True)
-    y, idx = f.maxpool2d_fwd(x.cuda(), k, s, p)
+    y, idx, widx = f.maxpool2d_fwd(x.cuda(), k, s, p, return_window_idx=True)
     assert torch.equal(y.float().cpu(), ref.permute(0, 2, 3, 1))
     assert torch.equal(idx.cpu().long(), ridx.permute(0, 2, 3, 1))  # bit-exact argmax
     dy = rnd(tuple(y.shape), 2, dtype)
     ref.backward(dy.float().permute(0, 3, 1, 2))
+    tol = 1e-5 if dtype == torch.float32 else 1e-2
     dx = f.maxpool2d_bwd(dy.cuda(), idx, tuple(x.shape), k, s, p)
-    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < (1e-5 if dtype == torch.float32 else 1e-2)
+    assert rel_err(dx, xr.grad.permute(0, 2, 3, 1)) < tol
+    dx2 = f.maxpool2d_bwd(dy.cuda(), None, tuple(x.shape), k, s, p, window_idx=widx)  # 1-byte argmax form
+    assert torch.equal(dx2, dx)
 
 
 def test_maxpool_nan_propagates():
@@ -134,7 +137,7 @@ def test_maxpool_nan_propagates():
     x = rnd((1, 4, 4, 8), 1)
     x[0, 1, 1, 3] = float("nan")
     ref, ridx = F.max_pool2d(x.permute(0, 3, 1, 2), 2, 2, 0, return_indices=True)
-    y, idx = f.maxpool2d_fwd(x.cuda(), 2, 2, 0)
+    y, idx, _ = f.maxpool2d_fwd(x.cuda(), 2, 2, 0)
     assert torch.equal(idx.cpu().long(), ridx.permute(0, 2, 3, 1))
     assert torch.isnan(y.cpu()[0, 0, 0, 3])
 
