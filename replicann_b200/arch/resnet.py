@@ -9,6 +9,7 @@ import torch
 import torch.nn as nn
 from torch import Tensor
 
+from ..nn._functions import BottleneckFn
 from ..nn.layers import AdaptiveAvgPool2d, BatchNorm2d, Conv2d, Linear, MaxPool2d
 from ._stem import prepare_input
 
@@ -31,12 +32,34 @@ class _Bottleneck(nn.Module):
         else:
             self._down_conv = None
             self._down_bn = None
+        self._fused = True
 
     def forward(self, x: Tensor, /) -> Tensor:
+        if self._fused and x.dtype == torch.bfloat16 and x.is_cuda:
+            return self._forward_fused(x)
         identity = x if self._down_conv is None else self._down_bn(self._down_conv(x))
         y = self._bn1(self._conv1(x))
         y = self._bn2(self._conv2(y))
         return self._bn3(self._conv3(y), identity)
+
+    def _forward_fused(self, x: Tensor) -> Tensor:
+        """Whole block as one autograd node (see BottleneckFn): same kernels, no elementwise gradient adds."""
+        bns = [self._bn1, self._bn2, self._bn3] + ([self._down_bn] if self._down_bn is not None else [])
+        if self.training:
+            for b in bns:
+                b._batches_pending += 1
+        cfg = tuple((b.eps, b.momentum) for b in bns)
+        if len(cfg) == 3:
+            cfg = cfg + ((1e-5, 0.1),)
+        stats = [t for b in bns for t in (b.running_mean, b.running_var)]
+        d = self._down_conv
+        return BottleneckFn.apply(x, self._conv2.stride[0], self.training, cfg,
+                                  self._conv1.weight, self._bn1.weight, self._bn1.bias,
+                                  self._conv2.weight, self._bn2.weight, self._bn2.bias,
+                                  self._conv3.weight, self._bn3.weight, self._bn3.bias,
+                                  d.weight if d is not None else None,
+                                  self._down_bn.weight if d is not None else None,
+                                  self._down_bn.bias if d is not None else None, *stats)
 
 
 class _BasicBlock(nn.Module):

@@ -55,6 +55,7 @@ struct TcParams {
   const bf16* residual; // added before ReLU (nullable), same indexing as D
   int relu;
   int tma_store;        // epilogue writes through the third tensor map (dense row mapping only)
+  int reduce_add;       // TMA stores add into D instead of overwriting it (gradient accumulation)
   TapDesc taps[MAX_TAPS];
 };
 
@@ -294,6 +295,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         __syncwarp();
         if (lane == 0) {
           if (p.ws != nullptr) tc::tma_store_3d(&tmD, buf, col0, row0, split);
+          else if (p.reduce_add) tc::tma_reduce_add_2d(&tmD, buf, col0, row0);
           else tc::tma_store_2d(&tmD, buf, col0, row0);
           tc::tma_store_commit();
         }
@@ -819,7 +821,10 @@ int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w,
       p.pix_map = (d->stride_h != 1 || d->stride_w != 1) ? 1 : 0;
       p.OW = d->W; p.OHOW = d->H * d->W; p.os_h = d->stride_h; p.os_w = d->stride_w; p.oa = a; p.ob = b;
       p.D = dx;
-      p.residual = accumulate ? reinterpret_cast<const bf16*>(dx) : nullptr;
+      // accumulation: dense outputs add through the TMA reduce-store (bf16 add at the destination, the same
+      // rounding as adding two bf16 gradient tensors); scattered (strided) outputs read-modify-write per thread
+      if (accumulate && !p.pix_map) p.reduce_add = 1;
+      else p.residual = accumulate ? reinterpret_cast<const bf16*>(dx) : nullptr;
       for (int i = 0; i < nh; ++i)
         for (int j = 0; j < nw; ++j) {
           TapDesc& t = p.taps[i * nw + j];

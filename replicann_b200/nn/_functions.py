@@ -504,3 +504,100 @@ class AttentionFn(Function):
         if packed:
             return dqkv, None, None, None, None, None, None, None, None, None, None
         return dq, dk, dv, None, None, None, None, None, None, None, None
+
+
+# ------------------------------------------------------------------------------------------ fused residual block
+class BottleneckFn(Function):
+    """One ResNet bottleneck block as a single autograd node:
+        y = relu(bn3(conv3(relu(bn2(conv2(relu(bn1(conv1(x)))))))) + identity),  identity = x | down_bn(down_conv(x))
+    Forward runs the same kernels as the layer-by-layer path.  The hand-written backward chains them without
+    autograd in between, which lets the input gradient be produced in ONE buffer: the residual-branch gradient
+    written by the bn3 backward kernel is the accumulation target of the conv1 (and downsample) dgrad kernels,
+    so the elementwise `grad_a + grad_b` pass autograd would otherwise run over the block input disappears.
+    """
+
+    @staticmethod
+    def forward(ctx, x, stride, training, cfg, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, *stats):
+        # stats: (rm1, rv1, rm2, rv2, rm3, rv3[, rmd, rvd]); cfg: ((eps, momentum) x 4)
+        xh = nhwc(x)
+        k1, k2, k3 = nhwc(w1), nhwc(w2), nhwc(w3)
+
+        def bn(y4, gamma, beta, rm, rv, em, residual, relu):
+            C_ = y4.shape[-1]
+            y2 = y4.reshape(-1, C_)
+            if training:
+                mean, invstd, scale, shift = RF.bn_stats(y2, gamma.detach(), beta.detach(), em[0], em[1], rm, rv)
+            else:
+                scale, shift = RF.bn_eval_prepare(gamma.detach(), beta.detach(), rm, rv, em[0])
+                mean, invstd = rm, torch.rsqrt(rv + em[0])
+            r2 = residual.reshape(-1, C_) if residual is not None else None
+            z2 = RF.bn_apply(y2, scale, shift, r2, relu)
+            return z2.reshape(y4.shape), (mean, invstd, scale, shift)
+
+        y1 = RF.conv2d_fprop(xh, k1)
+        z1, s1 = bn(y1, g1, b1, stats[0], stats[1], cfg[0], None, True)
+        y2 = RF.conv2d_fprop(z1, k2, stride=stride, pad=1)
+        z2, s2 = bn(y2, g2, b2, stats[2], stats[3], cfg[1], None, True)
+        y3 = RF.conv2d_fprop(z2, k3)
+        if wd is not None:
+            kd = nhwc(wd)
+            yd = RF.conv2d_fprop(xh, kd, stride=stride)
+            idt, sd = bn(yd, gd, bd, stats[6], stats[7], cfg[3], None, False)
+        else:
+            yd, idt, sd = None, xh, None
+        out, s3 = bn(y3, g3, b3, stats[4], stats[5], cfg[2], idt, True)
+        ctx.stride, ctx.training, ctx.has_down = stride, training, wd is not None
+        ctx.save_for_backward(xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, out,
+                              *s1, *s2, *s3, *(sd if sd is not None else ()))
+        return nchw(out)
+
+    @staticmethod
+    def backward(ctx, dout):
+        if not ctx.training:
+            raise RuntimeError("BottleneckFn backward in eval mode is not supported")
+        sv = ctx.saved_tensors
+        (xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, out) = sv[:20]
+        s1, s2, s3 = sv[20:24], sv[24:28], sv[28:32]
+        sd = sv[32:36] if ctx.has_down else None
+        stride = ctx.stride
+        k1, k2, k3 = nhwc(w1), nhwc(w2), nhwc(w3)
+        dout_h = nhwc(dout)
+
+        def bn_b(dy4, y4, st, gamma, beta, yout4, want_dres, from_x):
+            C_ = y4.shape[-1]
+            dg, acc = grad_target(gamma)
+            db, acc_b = grad_target(beta)
+            dx2, dres2 = RF.bn_bwd(dy4.reshape(-1, C_), y4.reshape(-1, C_),
+                                   yout4.reshape(-1, C_) if yout4 is not None else None, st[0], st[1], gamma.detach(),
+                                   want_dres=want_dres, dgamma=dg, dbeta=db, accumulate=acc or acc_b,
+                                   fwd_scale=st[2] if from_x else None, fwd_shift=st[3] if from_x else None)
+            _notify(gamma); _notify(beta)
+            return dx2.reshape(y4.shape), (dres2.reshape(y4.shape) if dres2 is not None else None)
+
+        def wgrad(w, xin, dy, s, p):
+            kshape = tuple(nhwc(w).shape)
+            _write_param_grad(w, lambda o, acc: RF.conv2d_wgrad(xin, dy, kshape, stride=s, pad=p,
+                                                                out=nhwc_param_view(o), accumulate=acc))
+
+        # bn3 (+ residual, ReLU): gradient of conv3's output and of the identity branch
+        dy3, dres = bn_b(dout_h, y3, s3, g3, b3, out, True, False)
+        wgrad(w3, z2, dy3, 1, 0)
+        dz2 = RF.conv2d_dgrad(dy3, k3, tuple(z2.shape))
+        dy2, _ = bn_b(dz2, y2, s2, g2, b2, None, False, True)
+        wgrad(w2, z1, dy2, stride, 1)
+        dz1 = RF.conv2d_dgrad(dy2, k2, tuple(z1.shape), stride=stride, pad=1)
+        dy1, _ = bn_b(dz1, y1, s1, g1, b1, None, False, True)
+        wgrad(w1, xh, dy1, 1, 0)
+        need_dx = ctx.needs_input_grad[0]
+        dx = None
+        if ctx.has_down:
+            kd = nhwc(wd)
+            dyd, _ = bn_b(dres, yd, sd, gd, bd, None, False, False)
+            wgrad(wd, xh, dyd, stride, 0)
+            if need_dx:
+                dx = RF.conv2d_dgrad(dyd, kd, tuple(xh.shape), stride=stride)
+                RF.conv2d_dgrad(dy1, k1, tuple(xh.shape), out=dx, accumulate=True)
+        elif need_dx:
+            # identity shortcut: dres already IS d(out)/d(x) through the skip; conv1's dgrad accumulates into it
+            dx = RF.conv2d_dgrad(dy1, k1, tuple(xh.shape), out=dres, accumulate=True)
+        return (nchw(dx) if dx is not None else None,) + (None,) * (15 + (8 if ctx.has_down else 6))

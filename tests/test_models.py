@@ -189,3 +189,28 @@ def test_state_dict_roundtrip_and_eval_mode():
         assert rel(ours(x.cuda()), ref(x)) < 2e-2
     sd = ours.state_dict()
     assert set(k for k in ref.state_dict()) <= set(sd)
+
+
+def test_fused_bottleneck_matches_layerwise_path():
+    """BottleneckFn (one autograd node, in-place residual-gradient accumulation) vs the layer-by-layer path."""
+    from replicann_b200.arch.resnet import ResNet
+    torch.manual_seed(0)
+    g = torch.Generator().manual_seed(7)
+    x = torch.randn(8, 3, 64, 64, generator=g).cuda()
+    y = torch.randint(0, 16, (8,), generator=g).cuda()
+    res = {}
+    for fused in (True, False):
+        torch.manual_seed(1)
+        m = ResNet((2, 1), bottleneck=True, n_classes=16).cuda().to(torch.bfloat16)
+        for mod in m.modules():
+            if hasattr(mod, "_fused"):
+                mod._fused = fused
+        logits = m(x)
+        F.cross_entropy(logits.float(), y).backward()
+        res[fused] = (logits.detach(), {n: p.grad.clone() for n, p in m.named_parameters()},
+                      {k: v.clone() for k, v in m.state_dict().items() if "running" in k})
+    assert torch.equal(res[True][0], res[False][0])                 # identical forward kernels
+    for k in res[True][2]:
+        assert torch.equal(res[True][2][k], res[False][2][k]), k     # identical running statistics
+    for n, gr in res[True][1].items():
+        assert cosine(gr, res[False][1][n]) > 0.99, n   # rounding-order noise only (see noise-floor note)
