@@ -591,21 +591,39 @@ int pick_bn(int n) {
 }
 
 // Split-K policy for plain GEMMs: split only when the tile grid leaves most SMs idle.
+int pick_splits(int base, int k_iters);
+
 int gemm_splits(int M, int N, int K, int BN) {
   const int tiles = ceil_div_i(M, BM) * ceil_div_i(N, BN);
   const int k_iters = ceil_div_i(K, BK);
-  const int sms = rnn_num_sms();
-  if (tiles * 2 > sms || k_iters < 8) return 1;
-  int s = sms / tiles;
-  if (s > k_iters / 4) s = k_iters / 4;
-  if (s > 32) s = 32;
-  return s < 1 ? 1 : s;
+  if (tiles * 2 > rnn_num_sms() || k_iters < 8) return 1;
+  return pick_splits(tiles, k_iters);
 }
 
 struct WgradPlan {
   int BN, n_mblk, ncblk, k_iters, splits;
   size_t ws_bytes;
 };
+
+// Split factor for a reduction of `k_iters` steps over `base` output tiles on a persistent grid of one CTA per
+// SM: maximise wave efficiency tiles / (ceil(tiles / SMs) * SMs) -- a 149th tile costs a whole extra wave --
+// keep at least 4 K-steps per split, and among near-equal choices take the smallest (fewer partials).
+int pick_splits(int base, int k_iters) {
+  const int sms = rnn_num_sms();
+  int max_s = k_iters / 4;
+  if (max_s > 64) max_s = 64;
+  if (max_s < 1) max_s = 1;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int s = 1; s <= max_s; ++s) {
+    const long long tiles = (long long)base * s;
+    const long long waves = (tiles + sms - 1) / sms;
+    const double eff = (double)tiles / (double)(waves * sms);
+    if (eff > best_eff + 0.03) { best_eff = eff; best = s; }
+    if (waves > 4) break;  // enough parallelism already; more splits only add partial traffic
+  }
+  return best;
+}
 
 // Tile width (in columns of the [K, taps*C] gradient matrix) for `nsb` 64-wide sub-blocks.
 int wgrad_bn(int nsb) {
@@ -623,10 +641,7 @@ WgradPlan plan_wgrad_cols(int K, int ntaps, int C, long long mpix) {
   w.ncblk = ceil_div_i(nsb, w.BN / 64);  // number of N tiles
   w.k_iters = ceil_div_i(mpix, BK);
   const int base = w.n_mblk * w.ncblk;
-  const int sms = rnn_num_sms();
-  int s = ceil_div_i(sms, base);
-  if (s > w.k_iters / 4) s = w.k_iters / 4;
-  if (s < 1) s = 1;
+  const int s = pick_splits(base, w.k_iters);
   w.splits = s;
   w.ws_bytes = (size_t)s * K * ntaps * C * sizeof(float);
   return w;

@@ -98,3 +98,52 @@ class Trainer:
         x = x_host.to(dev, non_blocking=True)
         y = y_host.to(dev, non_blocking=True)
         return float(self.step(x, y).item())
+
+
+class HostFeeder:
+    """Double-buffered host -> device input pipeline for `Trainer` (the step immediately upstream of the hot
+    path).  `submit()` starts the asynchronous copy of a pinned host batch into one of
+    two device staging buffers on a dedicated copy stream; `step()` makes the compute stream wait for the
+    oldest submitted batch and runs one training step on it.  Submitting batch i+1 before stepping on batch i
+    overlaps its PCIe transfer with the step's kernels."""
+
+    def __init__(self, trainer: Trainer, device=None) -> None:
+        self._trainer = trainer
+        self._dev = device if device is not None else next(trainer.model.parameters()).device
+        self._stream = torch.cuda.Stream(device=self._dev)
+        self._slots: list = [None, None]      # (x_dev, y_dev, ready_event, consumed_event)
+        self._w = self._r = 0
+        self._pending = 0
+
+    def submit(self, x_host: torch.Tensor, y_host: torch.Tensor) -> None:
+        if self._pending >= 2:
+            raise RuntimeError("HostFeeder holds two batches already: call step() before submitting more")
+        i = self._w
+        slot = self._slots[i]
+        if slot is None or slot[0].shape != x_host.shape or slot[0].dtype != x_host.dtype:
+            slot = [torch.empty(x_host.shape, dtype=x_host.dtype, device=self._dev),
+                    torch.empty(y_host.shape, dtype=y_host.dtype, device=self._dev),
+                    torch.cuda.Event(), None]
+            self._slots[i] = slot
+        with torch.cuda.stream(self._stream):
+            if slot[3] is not None:
+                self._stream.wait_event(slot[3])   # the step that last read this slot has finished with it
+            slot[0].copy_(x_host, non_blocking=True)
+            slot[1].copy_(y_host, non_blocking=True)
+            slot[2].record(self._stream)
+        self._w ^= 1
+        self._pending += 1
+
+    def step(self) -> torch.Tensor:
+        if self._pending == 0:
+            raise RuntimeError("HostFeeder.step() without a submitted batch")
+        slot = self._slots[self._r]
+        cur = torch.cuda.current_stream(self._dev)
+        cur.wait_event(slot[2])
+        loss = self._trainer.step(slot[0], slot[1])
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        slot[3] = ev
+        self._r ^= 1
+        self._pending -= 1
+        return loss
