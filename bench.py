@@ -134,34 +134,6 @@ def run_reference(args) -> None:
 
 
 # ------------------------------------------------------------------------------------------ GPU arm
-def _conv_linear_flops(model, x_shape):
-    """Algorithmic FLOPs of one training step of the contractions: 2*N*K*C*R*S*P*Q per convolution for each
-    of fprop, dgrad, wgrad (no dgrad for the first layer), 2*M*N*K x3 for Linear.  Nominal channel counts."""
-    import torch
-    from replicann_b200.nn.layers import Conv2d, Linear
-    flops = {"fprop": 0.0, "dgrad": 0.0, "wgrad": 0.0}
-    hooks, first = [], [True]
-
-    def conv_hook(m, inp, out):
-        N, K, P, Q = out.shape
-        f = 2.0 * N * K * P * Q * m.in_channels * m.kernel_size[0] * m.kernel_size[1]
-        flops["fprop"] += f; flops["wgrad"] += f
-        if not first[0]:
-            flops["dgrad"] += f
-        first[0] = False
-
-    def lin_hook(m, inp, out):
-        f = 2.0 * out.numel() * m.in_features
-        flops["fprop"] += f; flops["wgrad"] += f; flops["dgrad"] += f
-
-    for m in model.modules():
-        if isinstance(m, Conv2d):
-            hooks.append(m.register_forward_hook(conv_hook))
-        elif isinstance(m, Linear):
-            hooks.append(m.register_forward_hook(lin_hook))
-    return flops, hooks
-
-
 def run_gpu(args) -> None:
     import torch
     import torch.distributed as dist
@@ -199,7 +171,6 @@ def run_gpu(args) -> None:
     x = x_host.to(dev)
     y = y_host.to(dev)
 
-    flops, hooks = _conv_linear_flops(model, x.shape)
 
     def barrier():
         if world > 1:
@@ -210,10 +181,6 @@ def run_gpu(args) -> None:
     i = 0
     while i < warm or (use_graph and not trainer.graph_captured) or (use_graph and i < warm + 2):
         loss = trainer.step(x, y)   # eager steps first; with cuda_graph the capture happens here, untimed
-        if i == 0:
-            for h in hooks:
-                h.remove()
-            step_flops = dict(flops)
         i += 1
     warm = i
     torch.cuda.synchronize()
@@ -282,7 +249,8 @@ def run_gpu(args) -> None:
                 fh.write(f"{kind}\t{tag}\t{n / args.steps:.1f}\t{per:.4f}\t{w:.4g}\t{rate:.1f}\n")
     tc_ms = sum(v[0] for k, v in fam.items() if k.startswith("tc_"))
     tc_calls = sum(v[2] for k, v in fam.items() if k.startswith("tc_"))
-    alg_flops = sum(step_flops.values()) * args.steps
+    # algorithmic FLOPs: every tensor-core launch records 2*N*K*C*R*S*P*Q (nominal channels) / 2*M*N*K
+    alg_flops = sum(v[1] for k, v in fam.items() if k.startswith("tc_"))
     peaks = _peaks()
     tc_tflops = alg_flops / (tc_ms / 1e3) / 1e12 if tc_ms > 0 else 0.0
     peak_tf = peaks["bf16_tflops_sustained"]

@@ -16,10 +16,6 @@ namespace {
 // --------------------------------------------------------------------------------- BatchNorm
 // Thread layout for an [M, C] bf16 matrix: each thread owns one 8-channel vector column (cg) and
 // walks rows r0, r0 + rows_per_pass, ...   blockDim.x = 256; cgs = C/8 column groups.
-struct ColMap {
-  int cgs, rows_per_blk_pass;
-};
-
 template <bool BWD>
 __global__ void __launch_bounds__(256)
 bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
@@ -116,11 +112,22 @@ __device__ __forceinline__ void sum_partials_warp(const float* __restrict__ part
                                                   float& s, float& ss) {
   const int lane = threadIdx.x & 31;
   float a = 0.f, b = 0.f;
-  if (c < C)
-    for (int p = lane; p < nparts; p += 32) {
+  if (c < C) {
+    // four independent row loads in flight per lane: the loop is latency-bound (partials sit in L2)
+    int p = lane;
+    for (; p + 96 < nparts; p += 128) {
+      float a0 = partials[(long long)p * 2 * C + c], b0 = partials[(long long)p * 2 * C + C + c];
+      float a1 = partials[(long long)(p + 32) * 2 * C + c], b1 = partials[(long long)(p + 32) * 2 * C + C + c];
+      float a2 = partials[(long long)(p + 64) * 2 * C + c], b2 = partials[(long long)(p + 64) * 2 * C + C + c];
+      float a3 = partials[(long long)(p + 96) * 2 * C + c], b3 = partials[(long long)(p + 96) * 2 * C + C + c];
+      a += (a0 + a1) + (a2 + a3);
+      b += (b0 + b1) + (b2 + b3);
+    }
+    for (; p < nparts; p += 32) {
       a += partials[(long long)p * 2 * C + c];
       b += partials[(long long)p * 2 * C + C + c];
     }
+  }
   s = warp_sum(a);
   ss = warp_sum(b);
 }

@@ -42,7 +42,7 @@ struct TcParams {
   int Wo, HoWo, ts_w, ts_h, lo_w, lo_h;
   int cchunks;          // CONV: 64-channel chunks per tap
   int ntaps;
-  int ncblk, tapC;      // WGRAD: column blocks per tap, channels per tap
+  int ncblk;            // WGRAD: 64-channel sub-blocks per tap
   // output mapping
   long long ldd;        // row stride of D (elements)
   int pix_map;          // CONV: rows of D are scattered pixels (strided dgrad)
