@@ -43,8 +43,8 @@ class Trainer:
         from .optim import SGD
         if not isinstance(self._opt, SGD):
             raise ValueError("cuda_graph=True supports the SGD optimizer only (AdamW's step count is a host value)")
-        if self._dp is not None and self._dp.world_size > 1:
-            raise ValueError("cuda_graph=True is single-GPU for now (the overlapped all-reduce runs eagerly)")
+        # With data parallelism the bucketed all-reduces are captured too: they run on the communication
+        # stream, which forks from / joins the capturing stream through events (NCCL collectives are capturable).
         for m in self._model.modules():
             if isinstance(m, Dropout) and m.p > 0 and self._model.training:
                 raise ValueError("cuda_graph=True needs a model without active dropout (the RNG counter is host-side)")
@@ -67,8 +67,14 @@ class Trainer:
         self._gy.copy_(y)
         torch.cuda.synchronize()
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
-            self._gloss = self._eager_step(self._gx, self._gy)
+        if self._dp is not None and self._dp.world_size > 1:
+            # a failed NCCL capture must not take the other ranks down with a hang: relaxed capture mode lets
+            # the communicator's own bookkeeping calls through
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                self._gloss = self._eager_step(self._gx, self._gy)
+        else:
+            with torch.cuda.graph(g):
+                self._gloss = self._eager_step(self._gx, self._gy)
         self._graph = g
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
