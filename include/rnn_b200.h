@@ -153,16 +153,20 @@ int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gam
                              float* scale, float* shift, cudaStream_t stream);
 int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* running_mean, const float* running_var,
                         float eps, int C, float* scale, float* shift, cudaStream_t stream);
-/* y = relu(x*scale + shift + residual): fused BatchNorm-apply (+ residual add) (+ ReLU). */
+/* y = relu(x*scale + shift + residual): fused BatchNorm-apply (+ residual add) (+ ReLU).  relu_mask (nullable,
+ * M*C/8 bytes) receives one bit per element (y > 0) -- the compact ReLU mask the backward kernels can read
+ * instead of y. */
 int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, const void* residual, int relu, void* y,
-                      long long M, int C, cudaStream_t stream);
-/* Backward of the fused op above.  The ReLU mask comes from y_out (the forward output) or, when the forward
- * had no residual, is recomputed from x with the forward's (fwd_scale, fwd_shift) -- pass one or neither.
+                      unsigned char* relu_mask, long long M, int C, cudaStream_t stream);
+/* Backward of the fused op above.  The ReLU mask comes from y_out (the forward output), from the forward's
+ * relu_mask bits, or -- when the forward had no residual -- is recomputed from x with the forward's
+ * (fwd_scale, fwd_shift): pass at most one of the three.
  * dres (nullable) receives the gradient of the residual branch.  dgamma/dbeta are fp32 or bf16. */
 int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out, const float* mean, const float* invstd,
                     const float* gamma, long long M, int C, void* dx, void* dres, void* dgamma, void* dbeta,
                     int grads_f32, int accumulate_grads, float* sums /* 5*C floats of scratch */,
-                    const float* fwd_scale, const float* fwd_shift, void* ws, size_t ws_bytes, cudaStream_t stream);
+                    const float* fwd_scale, const float* fwd_shift, const unsigned char* relu_mask, void* ws,
+                    size_t ws_bytes, cudaStream_t stream);
 /* nn.LayerNorm(E) over y = LN(x + residual) (arch/transformer.py:65,72,111-112,188); xsum (nullable)
  * receives x + residual for the backward pass; mean / rstd are per-row fp32. */
 int rnn_layernorm_fwd(const void* x, const void* residual, const void* gamma, const void* beta, float eps, void* y,

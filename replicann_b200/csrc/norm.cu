@@ -21,7 +21,7 @@ __global__ void __launch_bounds__(256)
 bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
                  const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
                  float* __restrict__ partials /* [gridDim.y][2][C] */, const float* __restrict__ fscale = nullptr,
-                 const float* __restrict__ fshift = nullptr) {
+                 const float* __restrict__ fshift = nullptr, const unsigned char* __restrict__ bitmask = nullptr) {
   // grid.x tiles the column groups (when C/8 > 256), grid.y tiles rows.  Each thread owns one 8-channel
   // vector column and walks its rows four at a time so that 4 (x streams) independent 16-byte loads are
   // in flight per thread.  In the backward flavour the ReLU mask comes from the saved output `yout`, or is
@@ -46,7 +46,7 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
       fb[e] = fscale ? fshift[cg * 8 + e] : 0.f;
     }
   }
-  auto accum = [&](const uint4& ux, const uint4& ug, const uint4& uo) {
+  auto accum = [&](const uint4& ux, const uint4& ug, const uint4& uo, unsigned mbits) {
     float v[8];
     unpack8(ux, v);
     if (!BWD) {
@@ -63,6 +63,9 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
       } else if (fscale) {
 #pragma unroll
         for (int e = 0; e < 8; ++e) g[e] = fmaf(v[e], fs[e], fb[e]) > 0.f ? g[e] : 0.f;
+      } else if (bitmask) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = ((mbits >> e) & 1u) ? g[e] : 0.f;
       }
 #pragma unroll
       for (int e = 0; e < 8; ++e) { s0[e] += g[e]; s1[e] = fmaf(g[e], (v[e] - mu[e]) * is[e], s1[e]); }
@@ -74,19 +77,22 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
     const uint4 z = make_uint4(0, 0, 0, 0);
     for (; r + (U - 1) * stride < M; r += U * stride) {
       uint4 ux[U], ug[U], uo[U];
+      unsigned mb[U];
 #pragma unroll
       for (int u = 0; u < U; ++u) {
         const long long off = (r + u * stride) * C + cg * 8;
         ux[u] = ld_stream(x + off);
         ug[u] = BWD ? ld_stream(dy + off) : z;
         uo[u] = (BWD && yout) ? ld_stream(yout + off) : z;
+        mb[u] = (BWD && bitmask) ? bitmask[(r + u * stride) * cgs + cg] : 0u;
       }
 #pragma unroll
-      for (int u = 0; u < U; ++u) accum(ux[u], ug[u], uo[u]);
+      for (int u = 0; u < U; ++u) accum(ux[u], ug[u], uo[u], mb[u]);
     }
     for (; r < M; r += stride) {
       const long long off = r * C + cg * 8;
-      accum(ld_stream(x + off), BWD ? ld_stream(dy + off) : z, (BWD && yout) ? ld_stream(yout + off) : z);
+      accum(ld_stream(x + off), BWD ? ld_stream(dy + off) : z, (BWD && yout) ? ld_stream(yout + off) : z,
+            (BWD && bitmask) ? bitmask[r * cgs + cg] : 0u);
     }
   }
   // combine the rpp row-lanes of each column group through shared memory
@@ -207,7 +213,8 @@ bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
 
 __global__ void __launch_bounds__(256)
 bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
-                const bf16* __restrict__ residual, int relu, bf16* __restrict__ y, long long nvec, int cgs) {
+                const bf16* __restrict__ residual, int relu, bf16* __restrict__ y, long long nvec, int cgs,
+                unsigned char* __restrict__ relu_mask) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
     const int cg = (int)(i % cgs);
     float v[8];
@@ -228,7 +235,16 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
 #pragma unroll
       for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
     }
-    st_stream(y + i * 8, pack8(v));
+    const uint4 packed = pack8(v);
+    st_stream(y + i * 8, packed);
+    if (relu_mask) {  // one bit per element: (stored bf16 output > 0), for the backward kernels
+      float o[8];
+      unpack8(packed, o);
+      unsigned m = 0;
+#pragma unroll
+      for (int e = 0; e < 8; ++e) m |= (o[e] > 0.f ? 1u : 0u) << e;
+      relu_mask[i] = (unsigned char)m;
+    }
   }
 }
 
@@ -236,7 +252,7 @@ __global__ void __launch_bounds__(256)
 bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
                     const float* __restrict__ coef /* [3][C]: A, B, D */, bf16* __restrict__ dx,
                     bf16* __restrict__ dres, long long nvec, int cgs, const float* __restrict__ fscale,
-                    const float* __restrict__ fshift) {
+                    const float* __restrict__ fshift, const unsigned char* __restrict__ bitmask) {
   const int C = cgs * 8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
     const int c0 = (int)(i % cgs) * 8;
@@ -256,6 +272,10 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
       *reinterpret_cast<float4*>(fb + 4) = __ldg(reinterpret_cast<const float4*>(fshift + c0 + 4));
 #pragma unroll
       for (int e = 0; e < 8; ++e) g[e] = fmaf(v[e], fs[e], fb[e]) > 0.f ? g[e] : 0.f;
+    } else if (bitmask) {
+      const unsigned mbits = bitmask[i];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) g[e] = ((mbits >> e) & 1u) ? g[e] : 0.f;
     }
     if (dres) st_stream(dres + i * 8, pack8(g));
     float a[8], b[8], d[8], r[8];
@@ -549,14 +569,14 @@ int rnn_bn_eval_prepare(const float* gamma, const float* beta, const float* runn
 }
 
 int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, const void* residual, int relu, void* y,
-                      long long M, int C, cudaStream_t stream) {
+                      unsigned char* relu_mask, long long M, int C, cudaStream_t stream) {
   RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
   const long long nvec = M * (C / 8);
   long long blocks = (nvec + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * 16;
   if (blocks > cap) blocks = cap;
   bn_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)x, scale, shift, (const bf16*)residual, relu, (bf16*)y,
-                                                   nvec, C / 8);
+                                                   nvec, C / 8, relu ? relu_mask : nullptr);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
@@ -565,18 +585,19 @@ int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable
                     const float* invstd, const float* gamma, long long M, int C, void* dx,
                     void* dres /* nullable */, void* dgamma, void* dbeta, int grads_f32, int accumulate_grads,
                     float* sums /* [5][C] scratch: sum_dy, sum_dy_xhat, A, B, D */, const float* fwd_scale,
-                    const float* fwd_shift, void* ws, size_t ws_bytes, cudaStream_t stream) {
+                    const float* fwd_shift, const unsigned char* relu_mask, void* ws, size_t ws_bytes,
+                    cudaStream_t stream) {
   float* sum_dy = sums;
   float* sum_dy_xhat = sums + C;
   float* coef = sums + 2 * (long long)C;
   RNN_REQUIRE((fwd_scale == nullptr) == (fwd_shift == nullptr), RNN_ERR_SHAPE);
-  RNN_REQUIRE(!(y_out != nullptr && fwd_scale != nullptr), RNN_ERR_SHAPE);  // one source for the ReLU mask
+  RNN_REQUIRE((y_out != nullptr) + (fwd_scale != nullptr) + (relu_mask != nullptr) <= 1, RNN_ERR_SHAPE);  // one mask source
   RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
   const int gy = bn_row_blocks(M, C);
   RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)gy * 2 * C * sizeof(float), RNN_ERR_WORKSPACE);
   const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
   bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
-                                                          invstd, M, C, (float*)ws, fwd_scale, fwd_shift);
+                                                          invstd, M, C, (float*)ws, fwd_scale, fwd_shift, relu_mask);
   RNN_CHECK_LAUNCH();
   bn_bwd_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
                                                                 dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
@@ -587,7 +608,7 @@ int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable
   const long long cap = (long long)rnn_num_sms() * 16;
   if (blocks > cap) blocks = cap;
   bn_bwd_apply_kernel<<<(int)blocks, 256, 0, stream>>>((const bf16*)dy, (const bf16*)x, (const bf16*)y_out, coef,
-                                                       (bf16*)dx, (bf16*)dres, nvec, C / 8, fwd_scale, fwd_shift);
+                                                       (bf16*)dx, (bf16*)dres, nvec, C / 8, fwd_scale, fwd_shift, relu_mask);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

@@ -382,18 +382,20 @@ def bn_eval_prepare(gamma, beta, running_mean, running_var, eps):
     return st[0], st[1]
 
 
-def bn_apply(x2d, scale, shift, residual=None, relu=False):
+def bn_apply(x2d, scale, shift, residual=None, relu=False, want_mask=False):
+    """want_mask: also return the 1-bit-per-element ReLU mask (uint8 [M, C/8]); returns (y, mask) then."""
     lib = _lib.load(); _req(x2d, torch.bfloat16, "x")
     M, Cn = x2d.shape
     y = torch.empty_like(x2d)
+    mask = torch.empty((M, Cn // 8), dtype=torch.uint8, device=x2d.device) if (want_mask and relu) else None
     with _span("bn_apply", 2.0 * M * Cn * (3 if residual is not None else 2), f"M{M} C{Cn} res{int(residual is not None)}"):
-        check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), M, Cn,
-                                    cur_stream()), "rnn_bn_apply_bf16")
-    return y
+        check(lib.rnn_bn_apply_bf16(ptr(x2d), ptr(scale), ptr(shift), ptr(residual), int(relu), ptr(y), ptr(mask), M,
+                                    Cn, cur_stream()), "rnn_bn_apply_bf16")
+    return (y, mask) if want_mask else y
 
 
 def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, accumulate, fwd_scale=None,
-           fwd_shift=None):
+           fwd_shift=None, relu_mask=None):
     lib = _lib.load(); _req(dy2d, torch.bfloat16, "dy")
     M, Cn = x2d.shape
     dx = torch.empty_like(x2d)
@@ -401,12 +403,12 @@ def bn_bwd(dy2d, x2d, y_out, mean, invstd, gamma, *, want_dres, dgamma, dbeta, a
     sums = torch.empty((5, Cn), dtype=torch.float32, device=x2d.device)
     nbytes = lib.rnn_bn_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
-    nread = 2 + (1 if y_out is not None else 0)
+    nread = 2 + (1 if y_out is not None else 0) + (0.0625 if relu_mask is not None else 0)
     with _span("bn_bwd", 2.0 * M * Cn * (2 * nread + 1 + (1 if want_dres else 0)), f"M{M} C{Cn} y{int(y_out is not None)} res{int(want_dres)}"):
         check(lib.rnn_bn_bwd_bf16(ptr(dy2d), ptr(x2d), ptr(y_out), ptr(mean), ptr(invstd), ptr(gamma), M, Cn,
                                   ptr(dx), ptr(dres), ptr(dgamma), ptr(dbeta),
                                   _is_f32(dgamma) if dgamma is not None else 1, int(accumulate), ptr(sums),
-                                  ptr(fwd_scale), ptr(fwd_shift), ptr(ws), nbytes, cur_stream()),
+                                  ptr(fwd_scale), ptr(fwd_shift), ptr(relu_mask), ptr(ws), nbytes, cur_stream()),
               "rnn_bn_bwd_bf16")
     return dx, dres
 

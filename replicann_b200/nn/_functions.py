@@ -253,19 +253,21 @@ class BatchNormFn(Function):
         else:
             scale, shift = RF.bn_eval_prepare(g, b, running_mean, running_var, eps)
             mean, invstd = running_mean, torch.rsqrt(running_var + eps)
-        y2 = RF.bn_apply(x2, scale, shift, r2, relu)
-        ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
-        # ReLU mask for backward: the saved output when a residual was added, otherwise recomputed from x
-        # with the forward's scale/shift (saves reading y twice in the backward kernels)
+        # ReLU mask for backward: recomputed from x with the forward's scale/shift when no residual was added,
+        # otherwise a 1-bit-per-element mask written by the apply kernel (16x less traffic than re-reading y)
         from_x = relu and residual is None
-        ctx.save_for_backward(x2, y2 if (relu and not from_x) else None, mean, invstd, gamma, beta,
+        want_mask = relu and not from_x
+        out = RF.bn_apply(x2, scale, shift, r2, relu, want_mask=want_mask)
+        y2, mask = out if want_mask else (out, None)
+        ctx.relu, ctx.training, ctx.has_res = relu, training, residual is not None
+        ctx.save_for_backward(x2, mask, mean, invstd, gamma, beta,
                               scale if from_x else None, shift if from_x else None)
         ctx.shape = xh.shape
         return nchw(y2.reshape(xh.shape))
 
     @staticmethod
     def backward(ctx, dy):
-        x2, y2, mean, invstd, gamma, beta, fscale, fshift = ctx.saved_tensors
+        x2, mask, mean, invstd, gamma, beta, fscale, fshift = ctx.saved_tensors
         if not ctx.training:
             raise RuntimeError("BatchNorm2d backward in eval mode is not supported by replicann_b200")
         Cn = x2.shape[1]
@@ -278,9 +280,9 @@ class BatchNormFn(Function):
         else:
             dg = db = None
             acc = False
-        dx2, dres2 = RF.bn_bwd(dy2, x2, y2, mean, invstd, gamma.detach() if gamma is not None else None,
+        dx2, dres2 = RF.bn_bwd(dy2, x2, None, mean, invstd, gamma.detach() if gamma is not None else None,
                                want_dres=ctx.has_res, dgamma=dg, dbeta=db, accumulate=acc, fwd_scale=fscale,
-                               fwd_shift=fshift)
+                               fwd_shift=fshift, relu_mask=mask)
         if need_g:
             _notify(gamma)
             _notify(beta)
@@ -531,23 +533,26 @@ class BottleneckFn(Function):
                 scale, shift = RF.bn_eval_prepare(gamma.detach(), beta.detach(), rm, rv, em[0])
                 mean, invstd = rm, torch.rsqrt(rv + em[0])
             r2 = residual.reshape(-1, C_) if residual is not None else None
+            if residual is not None and relu:
+                z2, mask = RF.bn_apply(y2, scale, shift, r2, relu, want_mask=True)
+                return z2.reshape(y4.shape), (mean, invstd, scale, shift), mask
             z2 = RF.bn_apply(y2, scale, shift, r2, relu)
-            return z2.reshape(y4.shape), (mean, invstd, scale, shift)
+            return z2.reshape(y4.shape), (mean, invstd, scale, shift), None
 
         y1 = RF.conv2d_fprop(xh, k1)
-        z1, s1 = bn(y1, g1, b1, stats[0], stats[1], cfg[0], None, True)
+        z1, s1, _ = bn(y1, g1, b1, stats[0], stats[1], cfg[0], None, True)
         y2 = RF.conv2d_fprop(z1, k2, stride=stride, pad=1)
-        z2, s2 = bn(y2, g2, b2, stats[2], stats[3], cfg[1], None, True)
+        z2, s2, _ = bn(y2, g2, b2, stats[2], stats[3], cfg[1], None, True)
         y3 = RF.conv2d_fprop(z2, k3)
         if wd is not None:
             kd = nhwc(wd)
             yd = RF.conv2d_fprop(xh, kd, stride=stride)
-            idt, sd = bn(yd, gd, bd, stats[6], stats[7], cfg[3], None, False)
+            idt, sd, _ = bn(yd, gd, bd, stats[6], stats[7], cfg[3], None, False)
         else:
             yd, idt, sd = None, xh, None
-        out, s3 = bn(y3, g3, b3, stats[4], stats[5], cfg[2], idt, True)
+        out, s3, omask = bn(y3, g3, b3, stats[4], stats[5], cfg[2], idt, True)
         ctx.stride, ctx.training, ctx.has_down = stride, training, wd is not None
-        ctx.save_for_backward(xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, out,
+        ctx.save_for_backward(xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, omask,
                               *s1, *s2, *s3, *(sd if sd is not None else ()))
         return nchw(out)
 
@@ -556,21 +561,21 @@ class BottleneckFn(Function):
         if not ctx.training:
             raise RuntimeError("BottleneckFn backward in eval mode is not supported")
         sv = ctx.saved_tensors
-        (xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, out) = sv[:20]
+        (xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, omask) = sv[:20]
         s1, s2, s3 = sv[20:24], sv[24:28], sv[28:32]
         sd = sv[32:36] if ctx.has_down else None
         stride = ctx.stride
         k1, k2, k3 = nhwc(w1), nhwc(w2), nhwc(w3)
         dout_h = nhwc(dout)
 
-        def bn_b(dy4, y4, st, gamma, beta, yout4, want_dres, from_x):
+        def bn_b(dy4, y4, st, gamma, beta, mask, want_dres, from_x):
             C_ = y4.shape[-1]
             dg, acc = grad_target(gamma)
             db, acc_b = grad_target(beta)
-            dx2, dres2 = RF.bn_bwd(dy4.reshape(-1, C_), y4.reshape(-1, C_),
-                                   yout4.reshape(-1, C_) if yout4 is not None else None, st[0], st[1], gamma.detach(),
+            dx2, dres2 = RF.bn_bwd(dy4.reshape(-1, C_), y4.reshape(-1, C_), None, st[0], st[1], gamma.detach(),
                                    want_dres=want_dres, dgamma=dg, dbeta=db, accumulate=acc or acc_b,
-                                   fwd_scale=st[2] if from_x else None, fwd_shift=st[3] if from_x else None)
+                                   fwd_scale=st[2] if from_x else None, fwd_shift=st[3] if from_x else None,
+                                   relu_mask=mask)
             _notify(gamma); _notify(beta)
             return dx2.reshape(y4.shape), (dres2.reshape(y4.shape) if dres2 is not None else None)
 
@@ -580,7 +585,7 @@ class BottleneckFn(Function):
                                                                 out=nhwc_param_view(o), accumulate=acc))
 
         # bn3 (+ residual, ReLU): gradient of conv3's output and of the identity branch
-        dy3, dres = bn_b(dout_h, y3, s3, g3, b3, out, True, False)
+        dy3, dres = bn_b(dout_h, y3, s3, g3, b3, omask, True, False)
         wgrad(w3, z2, dy3, 1, 0)
         dz2 = RF.conv2d_dgrad(dy3, k3, tuple(z2.shape))
         dy2, _ = bn_b(dz2, y2, s2, g2, b2, None, False, True)

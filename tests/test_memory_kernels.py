@@ -40,7 +40,11 @@ def test_batchnorm_fwd_bwd(M, C, relu, res):
     rmd, rvd = rm.cuda(), rv.cuda()
     gd, bd = gamma.cuda(), beta.cuda()
     mean, invstd, scale, shift = f.bn_stats(xd, gd, bd, 1e-5, 0.1, rmd, rvd)
-    y = f.bn_apply(xd, scale, shift, resid.cuda() if res else None, relu)
+    y, bits = f.bn_apply(xd, scale, shift, resid.cuda() if res else None, relu, want_mask=True)
+    if relu:  # the 1-bit mask is exactly (stored output > 0)
+        exp_bits = (y > 0).reshape(M, C // 8, 8).to(torch.int32)
+        weights = (2 ** torch.arange(8, device="cuda", dtype=torch.int32)).reshape(1, 1, 8)
+        assert torch.equal(bits.to(torch.int32), (exp_bits * weights).sum(-1))
 
     # reference: torch BatchNorm on [M, C, 1, 1]
     xr = x.float().reshape(M, C, 1, 1).requires_grad_(True)
@@ -67,6 +71,11 @@ def test_batchnorm_fwd_bwd(M, C, relu, res):
     dx, dres = f.bn_bwd(dy.cuda(), xd, y if (relu and not from_x) else None, mean, invstd, gd, want_dres=res,
                         dgamma=dgamma, dbeta=dbeta, accumulate=False, fwd_scale=scale if from_x else None,
                         fwd_shift=shift if from_x else None)
+    if relu and not from_x:  # same backward driven by the bit mask instead of the saved output
+        dg2, db2 = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
+        dx2, dres2 = f.bn_bwd(dy.cuda(), xd, None, mean, invstd, gd, want_dres=res, dgamma=dg2, dbeta=db2,
+                              accumulate=False, relu_mask=bits)
+        assert torch.equal(dx2, dx) and torch.equal(dres2, dres) and torch.equal(dg2, dgamma)
     assert rel_err(dx, xr.grad.reshape(M, C)) < 1e-2
     assert rel_err(dgamma, gr.grad) < 1e-2 and rel_err(dbeta, br.grad) < 1e-2
     if res:

@@ -20,9 +20,9 @@ dg, db = torch.empty(C, device="cuda"), torch.empty(C, device="cuda")
 
 def run():
     mean, invstd, scale, shift = RF.bn_stats(x, g, b, 1e-5, 0.1, rm, rv)
-    y = RF.bn_apply(x, scale, shift, r, True)
-    RF.bn_bwd(dy, x, y if res else None, mean, invstd, g, want_dres=res, dgamma=dg, dbeta=db, accumulate=False,
-              fwd_scale=None if res else scale, fwd_shift=None if res else shift)
+    y, bits = RF.bn_apply(x, scale, shift, r, True, want_mask=True)
+    RF.bn_bwd(dy, x, None, mean, invstd, g, want_dres=res, dgamma=dg, dbeta=db, accumulate=False,
+              fwd_scale=None if res else scale, fwd_shift=None if res else shift, relu_mask=bits if res else None)
 
 
 for _ in range(3):
