@@ -69,6 +69,14 @@ typedef struct {
  * y = y*scale[k] + shift[k] (bias / folded BatchNorm), y += residual, y = relu(y).   C % 64 == 0. */
 int rnn_conv2d_fprop_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
                           const float* shift, const void* residual, int relu, cudaStream_t stream);
+/* Conv2d forward + torch.nn.BatchNorm2d (training) batch statistics of its output in one pass: the epilogue
+ * accumulates per-channel sums of the bf16 values it stores; mean / invstd / scale / shift and the running
+ * statistics come out as from rnn_bn_stats_bf16.  K must be a multiple of its N tile (64 / 128 / 256). */
+size_t rnn_conv2d_fprop_bn_stats_workspace(const rnn_conv_desc* d);
+int rnn_conv2d_fprop_bn_stats_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* gamma,
+                                   const float* beta, float eps, float momentum, float* running_mean,
+                                   float* running_var, float* mean, float* invstd, float* scale, float* shift,
+                                   void* ws, size_t ws_bytes, cudaStream_t stream);
 /* autograd of Conv2d w.r.t. its input.  accumulate != 0: dx += result. */
 int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
                           cudaStream_t stream);

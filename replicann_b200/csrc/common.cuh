@@ -41,6 +41,9 @@ void rnn_set_last_error(const char* file, int line, cudaError_t e);
 void rnn_set_last_message(const char* file, int line, const char* msg);
 int rnn_num_sms();
 void rnn_count_launch();
+int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, float count, const float* gamma,
+                             const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                             float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream);
 
 typedef __nv_bfloat16 bf16;
 

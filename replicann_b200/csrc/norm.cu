@@ -114,24 +114,28 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
 
 // Sum the per-block partials: one WARP per channel (8 channels per 256-thread block); the 32 lanes stride
 // over the partial rows and a shuffle tree combines them in a fixed order (deterministic).
+// Partial layout: [C / blk][nparts][2][blk] -- blk == C for the row-block partials of bn_reduce_kernel, blk = the
+// N tile of the convolution when the statistics come out of its epilogue (one partial row per epilogue warp).
 __device__ __forceinline__ void sum_partials_warp(const float* __restrict__ partials, int nparts, int C, int c,
-                                                  float& s, float& ss) {
+                                                  float& s, float& ss, int blk) {
   const int lane = threadIdx.x & 31;
   float a = 0.f, b = 0.f;
   if (c < C) {
+    const float* base = partials + (long long)(c / blk) * nparts * 2 * blk + (c % blk);
+    const long long rs = 2ll * blk;
     // four independent row loads in flight per lane: the loop is latency-bound (partials sit in L2)
     int p = lane;
     for (; p + 96 < nparts; p += 128) {
-      float a0 = partials[(long long)p * 2 * C + c], b0 = partials[(long long)p * 2 * C + C + c];
-      float a1 = partials[(long long)(p + 32) * 2 * C + c], b1 = partials[(long long)(p + 32) * 2 * C + C + c];
-      float a2 = partials[(long long)(p + 64) * 2 * C + c], b2 = partials[(long long)(p + 64) * 2 * C + C + c];
-      float a3 = partials[(long long)(p + 96) * 2 * C + c], b3 = partials[(long long)(p + 96) * 2 * C + C + c];
+      float a0 = base[p * rs], b0 = base[p * rs + blk];
+      float a1 = base[(p + 32) * rs], b1 = base[(p + 32) * rs + blk];
+      float a2 = base[(p + 64) * rs], b2 = base[(p + 64) * rs + blk];
+      float a3 = base[(p + 96) * rs], b3 = base[(p + 96) * rs + blk];
       a += (a0 + a1) + (a2 + a3);
       b += (b0 + b1) + (b2 + b3);
     }
     for (; p < nparts; p += 32) {
-      a += partials[(long long)p * 2 * C + c];
-      b += partials[(long long)p * 2 * C + C + c];
+      a += base[p * rs];
+      b += base[p * rs + blk];
     }
   }
   s = warp_sum(a);
@@ -143,10 +147,10 @@ bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, 
                          const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                          float momentum, float* running_mean, float* running_var,
                          float* __restrict__ mean, float* __restrict__ invstd,
-                         float* __restrict__ scale, float* __restrict__ shift) {
+                         float* __restrict__ scale, float* __restrict__ shift, int blk) {
   const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
   float s, ss;
-  sum_partials_warp(partials, nparts, C, c, s, ss);
+  sum_partials_warp(partials, nparts, C, c, s, ss, blk);
   if ((threadIdx.x & 31) != 0 || c >= C) return;
   const float m = s / count;
   float var = ss / count - m * m;
@@ -184,7 +188,7 @@ bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
                        const float* __restrict__ gamma, float inv_count, float* __restrict__ coef /* [3][C] */) {
   const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
   float s, ss;
-  sum_partials_warp(partials, nparts, C, c, s, ss);
+  sum_partials_warp(partials, nparts, C, c, s, ss, C);
   if ((threadIdx.x & 31) != 0 || c >= C) return;
   sum_dy[c] = s;
   sum_dy_xhat[c] = ss;
@@ -494,6 +498,17 @@ int bn_static_scratch_address(float** out) {
 }
 }  // namespace
 
+// Finalize BatchNorm statistics from partial sums produced elsewhere (the convolution epilogue): used by
+// tc_gemm.cu.  `blk` = columns per partial block (see sum_partials_warp).
+int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, float count, const float* gamma,
+                             const float* beta, float eps, float momentum, float* running_mean, float* running_var,
+                             float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
+  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>(partials, nparts, C, count, gamma, beta, eps, momentum,
+                                                                running_mean, running_var, mean, invstd, scale, shift, blk);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
 extern "C" {
 
 size_t rnn_bn_workspace(long long M, int C) { return (size_t)bn_row_blocks(M, C) * 2 * C * sizeof(float); }
@@ -510,7 +525,7 @@ int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, con
   RNN_CHECK_LAUNCH();
   bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
-                                                                   scale, shift);
+                                                                   scale, shift, C);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
@@ -554,7 +569,7 @@ int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gam
   RNN_CHECK_LAUNCH();
   bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
-                                                                   scale, shift);
+                                                                   scale, shift, C);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

@@ -56,6 +56,9 @@ struct TcParams {
   int relu;
   int tma_store;        // epilogue writes through the third tensor map (dense row mapping only)
   int reduce_add;       // TMA stores add into D instead of overwriting it (gradient accumulation)
+  float* stat_partials; // STATS: per-epilogue-warp column sums / sums of squares [n_nblk][stat_rows][2][BN]
+  int stat_rows;        // = (gridDim.x / n_nblk) * 4
+  int force_grid;       // launch exactly this many CTAs (STATS needs gridDim.x % n_nblk == 0)
   TapDesc taps[MAX_TAPS];
 };
 
@@ -72,7 +75,9 @@ struct Cfg {
 
 // FUSED = the bf16 epilogue applies scale / shift / residual / ReLU; the plain variant (most convolutions of
 // a BatchNorm network, every dgrad) compiles to convert + store only.
-template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED>
+// STATS = the epilogue also accumulates, per output channel, the sum and the sum of squares of the bf16 values it
+// stores (BatchNorm batch statistics without a second pass over the activation).
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmD, const __grid_constant__ TcParams p) {
@@ -252,6 +257,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     uint8_t* stage_w = staging + q * 8192;  // two 4 KB buffers
     int sbuf = 0;
+    float st[STATS ? BN / 64 : 1][4];       // STATS: {sum, sum} {sumsq, sumsq} of columns 2*lane, 2*lane+1 per chunk
+#pragma unroll
+    for (int c = 0; c < (STATS ? BN / 64 : 1); ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -284,10 +292,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       // the chunk inside the row, valid16 = number of 16-byte pieces of the chunk that are inside D
       // TMA-store variant: the swizzled staging buffer is exactly the SWIZZLE_128B box the output tensor map
       // expects; one lane hands it to the TMA engine, which also clips rows/columns outside D.
+      const uint8_t* last_buf = stage_w;
       auto flush_tma = [&](const uint4* v, int col0, int row0) {
         if (lane == 0) tc::tma_store_wait_read<1>();  // the store issued two chunks ago has drained its buffer
         __syncwarp();
         uint8_t* buf = stage_w + sbuf * 4096;
+        last_buf = buf;
         uint4* srow = reinterpret_cast<uint4*>(buf + lane * 128);
 #pragma unroll
         for (int j = 0; j < 8; ++j) srow[j ^ (lane & 7)] = v[j];
@@ -331,8 +341,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         }
       } else {
         // bf16 output with the fused epilogue: 64 columns = 128 bytes per row per chunk
-#pragma unroll 1
-        for (int chunk = 0; chunk < BN / 64; ++chunk) {
+        auto do_chunk = [&](const int chunk) {
           uint32_t r[64];
           __syncwarp();
           tc::tmem_ld32(t_acc + (uint32_t)(chunk * 64), r);
@@ -377,6 +386,28 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           valid16 = valid16 < 0 ? 0 : (valid16 > 8 ? 8 : valid16);
           if (p.tma_store) flush_tma(out, c_first, mblk * BM + q * 32);
           else flush(out, chunk * 128, valid16);
+          if constexpr (STATS) {
+            // column sums over this warp's 32 rows, read back from the swizzled staging tile: lane owns the
+            // 4-byte word holding columns 2*lane, 2*lane+1 (conflict-free: 32 distinct words per row)
+            float a0 = 0.f, a1 = 0.f, q0 = 0.f, q1 = 0.f;
+#pragma unroll 8
+            for (int rr = 0; rr < 32; ++rr) {
+              const uint32_t wv = *reinterpret_cast<const uint32_t*>(
+                  last_buf + rr * 128 + ((((lane >> 2) ^ (rr & 7)) << 4) | ((lane & 3) << 2)));
+              const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv));
+              a0 += f.x; a1 += f.y;
+              q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
+            }
+            st[STATS ? chunk : 0][0] += a0; st[STATS ? chunk : 0][1] += a1;
+            st[STATS ? chunk : 0][2] += q0; st[STATS ? chunk : 0][3] += q1;
+          }
+        };
+        if constexpr (STATS) {
+#pragma unroll
+          for (int chunk = 0; chunk < BN / 64; ++chunk) do_chunk(chunk);
+        } else {
+#pragma unroll 1
+          for (int chunk = 0; chunk < BN / 64; ++chunk) do_chunk(chunk);
         }
       }
       tc::tc_fence_before();
@@ -385,6 +416,16 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (p.tma_store && lane == 0) tc::tma_store_wait<0>();
+    if constexpr (STATS) {
+      const int nb = blockIdx.x % p.n_nblk;  // gridDim.x is a multiple of n_nblk: every tile of this CTA has this n-block
+      const int prow = (blockIdx.x / p.n_nblk) * 4 + q;
+      float* base = p.stat_partials + ((long long)(nb * p.stat_rows + prow) * 2) * BN;
+#pragma unroll
+      for (int c = 0; c < BN / 64; ++c) {
+        *reinterpret_cast<float2*>(base + c * 64 + 2 * lane) = make_float2(st[c][0], st[c][1]);
+        *reinterpret_cast<float2*>(base + BN + c * 64 + 2 * lane) = make_float2(st[c][2], st[c][3]);
+      }
+    }
   }
 
   tc::tc_fence_before();
@@ -529,7 +570,7 @@ int make_tmap_out(CUtensorMap* m, TcParams* p) {
   return RNN_OK;
 }
 
-template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED>
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS = false>
 int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
   TcParams p = p_in;
   CUtensorMap td;
@@ -538,13 +579,14 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     if (rc != RNN_OK) return rc;
   }
   static bool attr_set = false;
-  auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED>;
+  auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED, STATS>;
   if (!attr_set) {
     RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
     attr_set = true;
   }
   const int tiles = p.n_mblk * p.n_nblk * p.splits;
-  const int grid = tiles < rnn_num_sms() ? tiles : rnn_num_sms();
+  int grid = tiles < rnn_num_sms() ? tiles : rnn_num_sms();
+  if (p.force_grid > 0) grid = p.force_grid;
   kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, td, p);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
@@ -552,6 +594,9 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
 
 template <int BN, int KIND, bool A_MN, bool B_MN>
 int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
+  if constexpr (KIND == KIND_CONV && !A_MN && !B_MN && BN != 192) {
+    if (p.stat_partials != nullptr) return launch_inst2<BN, KIND, A_MN, B_MN, false, true>(ta, tb, p, stream);
+  }
   // wgrad and the MN-major-A GEMM (Linear wgrad) never carry a fused epilogue
   if constexpr (KIND != KIND_WGRAD && !A_MN) {
     if (p.ws == nullptr && (p.scale || p.shift || p.residual || p.relu))
@@ -728,9 +773,9 @@ static int check_conv_desc(const rnn_conv_desc* d) {
   return RNN_OK;
 }
 
-// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); optional per-channel scale/shift, residual add, ReLU.
-int rnn_conv2d_fprop_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
-                          const float* shift, const void* residual, int relu, cudaStream_t stream) {
+static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
+                           const float* shift, const void* residual, int relu, float* stat_partials, int* stat_rows,
+                           cudaStream_t stream) {
   int rc = check_conv_desc(d);
   if (rc != RNN_OK) return rc;
   rc = load_driver_entry_points();
@@ -760,12 +805,55 @@ int rnn_conv2d_fprop_bf16(const rnn_conv_desc* d, const void* x, const void* w, 
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
   p.ldd = d->K;
   p.D = y; p.scale = scale; p.shift = shift; p.residual = reinterpret_cast<const bf16*>(residual); p.relu = relu;
+  if (stat_partials != nullptr) {
+    RNN_REQUIRE(d->K % BN == 0, RNN_ERR_SHAPE);  // statistics need whole N tiles
+    const int sms = rnn_num_sms();
+    RNN_REQUIRE(p.n_nblk <= sms, RNN_ERR_SHAPE);
+    p.force_grid = (sms / p.n_nblk) * p.n_nblk;  // every CTA keeps one n-block for all of its tiles
+    p.stat_rows = (p.force_grid / p.n_nblk) * 4;
+    p.stat_partials = stat_partials;
+    *stat_rows = p.stat_rows;
+  }
   for (int r = 0; r < d->R; ++r)
     for (int s = 0; s < d->S; ++s) {
       TapDesc& t = p.taps[r * d->S + s];
       t.ow = (int16_t)s; t.oh = (int16_t)r; t.bcol = (r * d->S + s) * d->C;
     }
   return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);
+}
+
+// y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); optional per-channel scale/shift, residual add, ReLU.
+int rnn_conv2d_fprop_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
+                          const float* shift, const void* residual, int relu, cudaStream_t stream) {
+  return conv_fprop_impl(d, x, w, y, scale, shift, residual, relu, nullptr, nullptr, stream);
+}
+
+// Convolution + BatchNorm batch statistics of its output in one pass: the epilogue accumulates per-channel sums
+// of the bf16 values it stores, a finalize kernel turns them into mean / invstd / scale / shift and updates the
+// running statistics (torch.nn.BatchNorm2d training semantics).  ws: rnn_conv2d_fprop_bn_stats_workspace() bytes.
+size_t rnn_conv2d_fprop_bn_stats_workspace(const rnn_conv_desc* d) {
+  if (d == nullptr || d->K <= 0) return 0;
+  const int BN = pick_bn(d->K);
+  const int n_nblk = ceil_div_i(d->K, BN);
+  const int sms = rnn_num_sms();
+  if (n_nblk > sms) return 0;
+  const int grid = (sms / n_nblk) * n_nblk;
+  return (size_t)n_nblk * ((grid / n_nblk) * 4) * 2 * BN * sizeof(float);
+}
+
+int rnn_conv2d_fprop_bn_stats_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* gamma,
+                                   const float* beta, float eps, float momentum, float* running_mean,
+                                   float* running_var, float* mean, float* invstd, float* scale, float* shift,
+                                   void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(d != nullptr, RNN_ERR_SHAPE);
+  const size_t need = rnn_conv2d_fprop_bn_stats_workspace(d);
+  RNN_REQUIRE(need > 0 && ws != nullptr && ws_bytes >= need, RNN_ERR_WORKSPACE);
+  int rows = 0;
+  int rc = conv_fprop_impl(d, x, w, y, nullptr, nullptr, nullptr, 0, reinterpret_cast<float*>(ws), &rows, stream);
+  if (rc != RNN_OK) return rc;
+  const long long M = (long long)d->N * d->P * d->Q;
+  return rnn_internal_bn_finalize(reinterpret_cast<const float*>(ws), rows, d->K, pick_bn(d->K), (float)M, gamma, beta,
+                                  eps, momentum, running_mean, running_var, mean, invstd, scale, shift, stream);
 }
 
 // dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w[K,R,S,C]).  Strided convolutions are decomposed

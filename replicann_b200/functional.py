@@ -127,6 +127,24 @@ def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None
     return y
 
 
+def conv2d_fprop_bn_stats(x, w, gamma, beta, eps, momentum, running_mean, running_var, *, stride=1, pad=0):
+    """Convolution whose epilogue also produces the BatchNorm batch statistics of its output.
+    Returns (y, mean, invstd, scale, shift); updates the running statistics in place."""
+    lib = _lib.load()
+    _req(x, torch.bfloat16, "x"); _req(w, torch.bfloat16, "w")
+    d = _cdesc(x.shape, w.shape, stride, pad)
+    y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x.device)
+    st = torch.empty((4, d.K), dtype=torch.float32, device=x.device)
+    nbytes = lib.rnn_conv2d_fprop_bn_stats_workspace(d)
+    ws = workspace(nbytes, x.device)
+    with _span("tc_conv_fprop", _conv_flops(d), "stats " + _conv_tag(d)):
+        check(lib.rnn_conv2d_fprop_bn_stats_bf16(d, ptr(x), ptr(w), ptr(y), ptr(gamma), ptr(beta), float(eps),
+                                                 float(momentum), ptr(running_mean), ptr(running_var), ptr(st[0]),
+                                                 ptr(st[1]), ptr(st[2]), ptr(st[3]), ptr(ws), nbytes, cur_stream()),
+              "rnn_conv2d_fprop_bn_stats_bf16")
+    return y, st[0], st[1], st[2], st[3]
+
+
 # ---- first layer (C <= 8): packed-pixel layout -------------------------------------------------------
 def first_conv_geometry(d):
     import ctypes as C

