@@ -14,6 +14,7 @@
 // warps 2..5 = epilogue (TMEM -> registers -> global).  Three mbarrier rings: smem full/empty
 // between producer and MMA, TMEM full/empty between MMA and epilogue (two accumulator buffers so
 // the epilogue of tile i overlaps the main loop of tile i+1).
+#include <stdlib.h>
 #include <string.h>
 
 #include "tc_ptx.cuh"
@@ -59,12 +60,16 @@ struct TcParams {
   float* stat_partials; // STATS: per-epilogue-warp column sums / sums of squares [n_nblk][stat_rows][2][BN]
   int stat_rows;        // = (gridDim.x / n_nblk) * 4
   int force_grid;       // launch exactly this many CTAs (STATS needs gridDim.x % n_nblk == 0)
+  int cg;               // host only: 2 = launch as CTA pairs (cta_group::2), else single CTAs
   TapDesc taps[MAX_TAPS];
 };
 
-template <int BN>
+// CG = CTAs per MMA (cta_group): 1, or 2 = a CTA pair computing a 256 x BN tile with each CTA staging its own
+// 128 rows of A and HALF of B (the pair's tensor cores read both halves), which halves the operand bytes every
+// SM pulls through L2 per FLOP and deepens the pipeline.
+template <int BN, int CG = 1>
 struct Cfg {
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2 / CG;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BN == 192 ? 256 : BN;  // TMEM columns between the two accumulators
@@ -77,11 +82,15 @@ struct Cfg {
 // a BatchNorm network, every dgrad) compiles to convert + store only.
 // STATS = the epilogue also accumulates, per output channel, the sum and the sum of squares of the bf16 values it
 // stores (BatchNorm batch statistics without a second pass over the activation).
-template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS>
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmD, const __grid_constant__ TcParams p) {
-  using C = Cfg<BN>;
+  using C = Cfg<BN, CG>;
+  static_assert(CG == 1 || (BN % 128 == 0), "a CTA pair splits B in halves of whole 64-wide blocks");
+  const int cta_rank = CG == 2 ? (int)tc::cluster_ctarank() : 0;   // 0 = the CTA that issues the MMAs
+  const int cluster_id = blockIdx.x / CG, num_clusters = gridDim.x / CG;
+  const int n_pm = (p.n_mblk + CG - 1) / CG;                       // M tiles of 128*CG rows
   extern __shared__ uint8_t smem_raw[];
   const uint32_t raw_addr = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
@@ -95,7 +104,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.n_mblk * p.n_nblk * p.splits;
+  const int num_tiles = n_pm * p.n_nblk * p.splits;
 
   if (warp == 0 && lane == 0) {
     tc::prefetch_tmap(&tmA);
@@ -107,16 +116,17 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
     for (int a = 0; a < 2; ++a) {
       tc::mbar_init(&tfull_bar[a], 1);
-      tc::mbar_init(&tempty_bar[a], 4);  // one arrive per epilogue warp
+      tc::mbar_init(&tempty_bar[a], 4 * CG);  // one arrive per epilogue warp (of every CTA of the pair)
     }
     tc::fence_barrier_init();
   }
   if (warp == 1) {
-    tc::tmem_alloc(tmem_slot, C::TMEM_COLS);
-    tc::tmem_relinquish();
+    if (CG == 2) { tc::tmem_alloc_pair(tmem_slot, C::TMEM_COLS); tc::tmem_relinquish_pair(); }
+    else { tc::tmem_alloc(tmem_slot, C::TMEM_COLS); tc::tmem_relinquish(); }
   }
   tc::tc_fence_before();
-  __syncthreads();
+  if (CG == 2) tc::cluster_sync_all();  // barriers of both CTAs initialised before any remote arrive / TMA
+  else __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -125,11 +135,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      constexpr int NB_LOCAL = BN / 64 / CG;   // 64-wide B blocks staged by this CTA (MN-major B)
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int t = tile;
         const int nblk = t % p.n_nblk; t /= p.n_nblk;
-        const int mblk = t % p.n_mblk;
-        const int split = t / p.n_mblk;
+        const int mblk = (t % n_pm) * CG + cta_rank;
+        const int split = t / n_pm;
         const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
         const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         const int m0 = mblk * BM;
@@ -163,52 +174,63 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             sb_oh[j] = (uint16_t)p.taps[tap].oh;
           }
         }
+        // loads of a pair credit the even CTA's barrier; it alone announces the bytes of BOTH CTAs
+        auto ld2 = [&](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
+          if (CG == 2) tc::tma_load_2d_pair(dst, m, bar, c0, c1);
+          else tc::tma_load_2d(dst, m, bar, c0, c1);
+        };
+        auto ldi = [&](void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n, uint16_t ow,
+                       uint16_t oh) {
+          if (CG == 2) tc::tma_load_im2col_4d_pair(dst, m, bar, c, w, h, n, ow, oh);
+          else tc::tma_load_im2col_4d(dst, m, bar, c, w, h, n, ow, oh);
+        };
+        const int jb0 = cta_rank * NB_LOCAL;     // first 64-wide B block this CTA stages
         for (int it = k_lo; it < k_hi; ++it) {
           tc::mbar_wait(&empty_bar[stage], phase ^ 1u);
           uint8_t* sA = smem + stage * C::STAGE_BYTES;
           uint8_t* sB = sA + A_BYTES;
-          tc::mbar_expect_tx(&full_bar[stage],
-                             KIND == KIND_WGRAD ? (uint32_t)(A_BYTES + nsb_valid * 8192) : (uint32_t)C::STAGE_BYTES);
+          if (cta_rank == 0)
+            tc::mbar_expect_tx(&full_bar[stage], KIND == KIND_WGRAD ? (uint32_t)(CG * A_BYTES + nsb_valid * 8192)
+                                                                    : (uint32_t)(CG * C::STAGE_BYTES));
           if (KIND == KIND_GEMM) {
             const int kc = it * BK;
             if (!A_MN) {
-              tc::tma_load_2d(sA, &tmA, &full_bar[stage], kc, m0);
+              ld2(sA, &tmA, &full_bar[stage], kc, m0);
             } else {
-              tc::tma_load_2d(sA, &tmA, &full_bar[stage], m0, kc);
-              tc::tma_load_2d(sA + 8192, &tmA, &full_bar[stage], m0 + 64, kc);
+              ld2(sA, &tmA, &full_bar[stage], m0, kc);
+              ld2(sA + 8192, &tmA, &full_bar[stage], m0 + 64, kc);
             }
             if (!B_MN) {
-              tc::tma_load_2d(sB, &tmB, &full_bar[stage], kc, n0);
+              ld2(sB, &tmB, &full_bar[stage], kc, n0 + cta_rank * (BN / CG));   // box rows = BN / CG
             } else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tc::tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], n0 + j * 64, kc);
+              for (int j = 0; j < NB_LOCAL; ++j)
+                ld2(sB + j * 8192, &tmB, &full_bar[stage], n0 + (jb0 + j) * 64, kc);
             }
           } else if (KIND == KIND_CONV) {
             const int tap = it / p.cchunks;
             const int cc = it - tap * p.cchunks;
             const TapDesc td = p.taps[tap];
-            tc::tma_load_im2col_4d(sA, &tmA, &full_bar[stage], cc * BK, w0, h0, img0, (uint16_t)td.ow,
-                                   (uint16_t)td.oh);
+            ldi(sA, &tmA, &full_bar[stage], cc * BK, w0, h0, img0, (uint16_t)td.ow, (uint16_t)td.oh);
             if (!B_MN) {
-              tc::tma_load_2d(sB, &tmB, &full_bar[stage], td.bcol + cc * BK, n0);
+              ld2(sB, &tmB, &full_bar[stage], td.bcol + cc * BK, n0 + cta_rank * (BN / CG));
             } else {
 #pragma unroll
-              for (int j = 0; j < BN / 64; ++j)
-                tc::tma_load_2d(sB + j * 8192, &tmB, &full_bar[stage], td.bcol + n0 + j * 64, cc * BK);
+              for (int j = 0; j < NB_LOCAL; ++j)
+                ld2(sB + j * 8192, &tmB, &full_bar[stage], td.bcol + n0 + (jb0 + j) * 64, cc * BK);
             }
           } else {  // KIND_WGRAD: reduction over pixels
             const int pix0 = it * BK;
             const int img = pix0 / p.HoWo;
             const int rem = pix0 - img * p.HoWo;
             const int i = rem / p.Wo, j2 = rem - i * p.Wo;
-            tc::tma_load_2d(sA, &tmA, &full_bar[stage], m0, pix0);
-            tc::tma_load_2d(sA + 8192, &tmA, &full_bar[stage], m0 + 64, pix0);
+            ld2(sA, &tmA, &full_bar[stage], m0, pix0);
+            ld2(sA + 8192, &tmA, &full_bar[stage], m0 + 64, pix0);
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j) {
-              if (j < nsb_valid)
-                tc::tma_load_im2col_4d(sB + j * 8192, &tmB, &full_bar[stage], sb_c0[j], j2 * p.ts_w + p.lo_w,
-                                       i * p.ts_h + p.lo_h, img, sb_ow[j], sb_oh[j]);
+              if (j >= jb0 && j < jb0 + NB_LOCAL && j < nsb_valid)
+                ldi(sB + (j - jb0) * 8192, &tmB, &full_bar[stage], sb_c0[j], j2 * p.ts_w + p.lo_w,
+                    i * p.ts_h + p.lo_h, img, sb_ow[j], sb_oh[j]);
             }
           }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
@@ -217,14 +239,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
-    if (lane == 0) {
-      constexpr uint32_t idesc = tc::make_idesc_bf16(BM, BN, A_MN, B_MN);
+    if (lane == 0 && cta_rank == 0) {
+      constexpr uint32_t idesc = tc::make_idesc_bf16(BM * CG, BN, A_MN, B_MN);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int split = tile / (p.n_nblk * p.n_mblk);
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        const int split = tile / (p.n_nblk * n_pm);
         const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
         const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
@@ -241,12 +263,15 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
                                         : tc::make_smem_desc(sA + k * 32, 16, 1024);
             const uint64_t bdesc = B_MN ? tc::make_smem_desc(sB + k * 2048, 8192, 1024)
                                         : tc::make_smem_desc(sB + k * 32, 16, 1024);
-            tc::umma_bf16(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
+            if (CG == 2) tc::umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
+            else tc::umma_bf16(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
           }
-          tc::umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          // frees the smem slot (in both CTAs of a pair) once these MMAs retire
+          if (CG == 2) tc::umma_commit_pair(&empty_bar[stage]); else tc::umma_commit(&empty_bar[stage]);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
-        tc::umma_commit(&tfull_bar[acc]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue warps (of both CTAs)
+        if (CG == 2) tc::umma_commit_pair(&tfull_bar[acc]); else tc::umma_commit(&tfull_bar[acc]);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
@@ -262,11 +287,11 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     for (int c = 0; c < (STATS ? BN / 64 : 1); ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int t = tile;
       const int nblk = t % p.n_nblk; t /= p.n_nblk;
-      const int mblk = t % p.n_mblk;
-      const int split = t / p.n_mblk;
+      const int mblk = (t % n_pm) * CG + cta_rank;
+      const int split = t / n_pm;
       const int row = mblk * BM + q * 32 + lane;
       const bool row_ok = row < p.M;
       const int col_base = nblk * BN;
@@ -412,13 +437,17 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       }
       tc::tc_fence_before();
       __syncwarp();
-      if (lane == 0) tc::mbar_arrive(&tempty_bar[acc]);
+      if (lane == 0) {  // the accumulator buffer may be overwritten once every epilogue warp of the pair has drained it
+        if (CG == 2 && cta_rank != 0) tc::mbar_arrive_remote(&tempty_bar[acc], 0);
+        else tc::mbar_arrive(&tempty_bar[acc]);
+      }
       if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (p.tma_store && lane == 0) tc::tma_store_wait<0>();
     if constexpr (STATS) {
-      const int nb = blockIdx.x % p.n_nblk;  // gridDim.x is a multiple of n_nblk: every tile of this CTA has this n-block
-      const int prow = (blockIdx.x / p.n_nblk) * 4 + q;
+      // the number of clusters is a multiple of n_nblk: every tile of this CTA has the same n-block
+      const int nb = cluster_id % p.n_nblk;
+      const int prow = ((cluster_id / p.n_nblk) * CG + cta_rank) * 4 + q;
       float* base = p.stat_partials + ((long long)(nb * p.stat_rows + prow) * 2) * BN;
 #pragma unroll
       for (int c = 0; c < BN / 64; ++c) {
@@ -429,10 +458,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   }
 
   tc::tc_fence_before();
-  __syncthreads();
+  if (CG == 2) tc::cluster_sync_all();  // the peer may still be reading this CTA's smem / signalling its barriers
+  else __syncthreads();
   if (warp == 1) {
     tc::tc_fence_after();
-    tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
+    if (CG == 2) tc::tmem_dealloc_pair(tmem_base, C::TMEM_COLS);
+    else tc::tmem_dealloc(tmem_base, C::TMEM_COLS);
   }
 }
 
@@ -570,7 +601,32 @@ int make_tmap_out(CUtensorMap* m, TcParams* p) {
   return RNN_OK;
 }
 
-template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS = false>
+// Whether a launch runs as CTA pairs.  A pair owns a 256-row M tile, so the M tiles must come in twos (or be
+// many enough that one idle half tile is noise) and B must split into whole 64-wide halves.  Pairs cut the
+// operand bytes each SM pulls through L2 by a third (BN = 256), which is what bounds the long-K tiles
+// (measured: 3x3 and C >= 512 layers +5..20 %); tiles with few K steps are bound by their epilogue and lose
+// 20-30 % to the cross-CTA hand-offs, so they stay single.  RNN_TC_PAIR=0 turns pairs off, =2 forces them
+// wherever the shape allows (A/B timing and tests of both launch forms).
+int pick_cg(int BN, int n_mblk, int k_iters) {
+  static const int mode = [] {
+    const char* e = getenv("RNN_TC_PAIR");
+    return e == nullptr ? 1 : atoi(e);
+  }();
+  if (mode == 0 || BN % 128 != 0) return 1;
+  if (!(n_mblk % 2 == 0 || n_mblk >= 16)) return 1;
+  return (mode == 2 || k_iters >= 8) ? 2 : 1;
+}
+
+// STATS launches: every CTA (pair) keeps one n-block for all of its tiles, so the number of CTAs (pairs) is a
+// multiple of n_nblk.  Partial-sum rows: 4 per CTA.
+void plan_stats_grid(TcParams* p) {
+  const int cg = p->cg == 2 ? 2 : 1;
+  const int units = rnn_num_sms() / cg;
+  p->force_grid = (units / p->n_nblk) * p->n_nblk * cg;
+  p->stat_rows = (p->force_grid / p->n_nblk) * 4;
+}
+
+template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS = false, int CG = 1>
 int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p_in, cudaStream_t stream) {
   TcParams p = p_in;
   CUtensorMap td;
@@ -579,34 +635,58 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     if (rc != RNN_OK) return rc;
   }
   static bool attr_set = false;
-  auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED, STATS>;
+  auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED, STATS, CG>;
+  constexpr int smem = Cfg<BN, CG>::SMEM_BYTES;
   if (!attr_set) {
-    RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BN>::SMEM_BYTES));
+    RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;
   }
-  const int tiles = p.n_mblk * p.n_nblk * p.splits;
-  int grid = tiles < rnn_num_sms() ? tiles : rnn_num_sms();
+  const int units = rnn_num_sms() / CG;   // CTAs, or CTA pairs
+  const int tiles = ceil_div_i(p.n_mblk, CG) * p.n_nblk * p.splits;
+  int grid = (tiles < units ? tiles : units) * CG;
   if (p.force_grid > 0) grid = p.force_grid;
-  kern<<<grid, NUM_THREADS, Cfg<BN>::SMEM_BYTES, stream>>>(ta, tb, td, p);
+  if (CG == 1) {
+    kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, td, p);
+  } else {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr;
+    attr.id = cudaLaunchAttributeClusterDimension;
+    attr.val.clusterDim.x = CG; attr.val.clusterDim.y = 1; attr.val.clusterDim.z = 1;
+    cfg.attrs = &attr;
+    cfg.numAttrs = 1;
+    RNN_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, td, p));
+  }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }
 
-template <int BN, int KIND, bool A_MN, bool B_MN>
+template <int BN, int KIND, bool A_MN, bool B_MN, int CG = 1>
 int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t stream) {
   if constexpr (KIND == KIND_CONV && !A_MN && !B_MN && BN != 192) {
-    if (p.stat_partials != nullptr) return launch_inst2<BN, KIND, A_MN, B_MN, false, true>(ta, tb, p, stream);
+    if (p.stat_partials != nullptr) return launch_inst2<BN, KIND, A_MN, B_MN, false, true, CG>(ta, tb, p, stream);
   }
   // wgrad and the MN-major-A GEMM (Linear wgrad) never carry a fused epilogue
   if constexpr (KIND != KIND_WGRAD && !A_MN) {
     if (p.ws == nullptr && (p.scale || p.shift || p.residual || p.relu))
-      return launch_inst2<BN, KIND, A_MN, B_MN, true>(ta, tb, p, stream);
+      return launch_inst2<BN, KIND, A_MN, B_MN, true, false, CG>(ta, tb, p, stream);
   }
-  return launch_inst2<BN, KIND, A_MN, B_MN, false>(ta, tb, p, stream);
+  return launch_inst2<BN, KIND, A_MN, B_MN, false, false, CG>(ta, tb, p, stream);
 }
 
 template <int KIND, bool A_MN, bool B_MN>
 int launch_bn(int BN, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t s) {
+  if (p.cg == 2) {
+    switch (BN) {
+      case 128: return launch_inst<128, KIND, A_MN, B_MN, 2>(ta, tb, p, s);
+      case 256: return launch_inst<256, KIND, A_MN, B_MN, 2>(ta, tb, p, s);
+    }
+    return RNN_ERR_SHAPE;
+  }
   switch (BN) {
     case 64: return launch_inst<64, KIND, A_MN, B_MN>(ta, tb, p, s);
     case 128: return launch_inst<128, KIND, A_MN, B_MN>(ta, tb, p, s);
@@ -672,6 +752,10 @@ int pick_splits(int base, int k_iters) {
 
 // Tile width (in columns of the [K, taps*C] gradient matrix) for `nsb` 64-wide sub-blocks.
 int wgrad_bn(int nsb) {
+  if (const char* e = getenv("RNN_WGRAD_BN")) {  // tuning experiments only
+    const int v = atoi(e);
+    if (v == 64 || v == 128 || v == 192 || v == 256) return v;
+  }
   if (nsb % 4 == 0) return 256;
   if (nsb % 3 == 0) return 192;
   if (nsb % 2 == 0) return nsb > 8 ? 256 : 128;
@@ -721,17 +805,19 @@ int rnn_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, in
   if (rc != RNN_OK) return rc;
 
   const int BN = pick_bn(N);
+  const int cg = gemm_splits(M, N, K, BN) > 1 ? 1 : pick_cg(BN, ceil_div_i(M, BM), ceil_div_i(K, BK));
   CUtensorMap ta, tb;
   if (!a_mn) rc = make_tmap_2d(&ta, A, M, K, K, BM);   // A[M,K], box {64 k, 128 m}
   else       rc = make_tmap_2d(&ta, A, K, M, M, 64);   // A stored [K,M], box {64 m, 64 k}
   if (rc != RNN_OK) return rc;
-  if (!b_mn) rc = make_tmap_2d(&tb, B, N, K, K, BN);   // B[N,K], box {64 k, BN n}
+  if (!b_mn) rc = make_tmap_2d(&tb, B, N, K, K, BN / cg);   // B[N,K], box {64 k, BN n} (half per CTA of a pair)
   else       rc = make_tmap_2d(&tb, B, K, N, N, 64);   // B stored [K,N], box {64 n, 64 k}
   if (rc != RNN_OK) return rc;
 
   TcParams p;
   memset(&p, 0, sizeof(p));
   p.M = M; p.N = N;
+  p.cg = cg;
   p.k_iters = ceil_div_i(K, BK);
   p.splits = gemm_splits(M, N, K, BN);
   p.n_mblk = ceil_div_i(M, BM);
@@ -787,14 +873,16 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
                         d->pad_h - (d->R - 1), d->stride_w, d->stride_h, BM);
   if (rc != RNN_OK) return rc;
   const long long rsc = (long long)d->R * d->S * d->C;
-  rc = make_tmap_2d(&tb, w, d->K, rsc, rsc, BN);
+  const long long M = (long long)d->N * d->P * d->Q;
+  RNN_REQUIRE(M < (1ll << 31), RNN_ERR_SHAPE);
+  const int cg = pick_cg(BN, ceil_div_i(M, BM), d->R * d->S * (d->C / 64));
+  rc = make_tmap_2d(&tb, w, d->K, rsc, rsc, BN / cg);
   if (rc != RNN_OK) return rc;
 
   TcParams p;
   memset(&p, 0, sizeof(p));
-  const long long M = (long long)d->N * d->P * d->Q;
-  RNN_REQUIRE(M < (1ll << 31), RNN_ERR_SHAPE);
   p.M = (int)M; p.N = d->K;
+  p.cg = cg;
   p.cchunks = d->C / 64;
   p.ntaps = d->R * d->S;
   p.k_iters = p.ntaps * p.cchunks;
@@ -807,10 +895,8 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
   p.D = y; p.scale = scale; p.shift = shift; p.residual = reinterpret_cast<const bf16*>(residual); p.relu = relu;
   if (stat_partials != nullptr) {
     RNN_REQUIRE(d->K % BN == 0, RNN_ERR_SHAPE);  // statistics need whole N tiles
-    const int sms = rnn_num_sms();
-    RNN_REQUIRE(p.n_nblk <= sms, RNN_ERR_SHAPE);
-    p.force_grid = (sms / p.n_nblk) * p.n_nblk;  // every CTA keeps one n-block for all of its tiles
-    p.stat_rows = (p.force_grid / p.n_nblk) * 4;
+    RNN_REQUIRE(p.n_nblk <= rnn_num_sms() / 2, RNN_ERR_SHAPE);
+    plan_stats_grid(&p);
     p.stat_partials = stat_partials;
     *stat_rows = p.stat_rows;
   }
@@ -918,6 +1004,7 @@ int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w,
       p.splits = 1;
       p.n_mblk = ceil_div_i(M, BM);
       p.n_nblk = ceil_div_i(d->C, BN);
+      p.cg = pick_cg(BN, p.n_mblk, p.k_iters);
       p.Wo = Wc; p.HoWo = Hc * Wc;
       p.ts_w = 1; p.ts_h = 1; p.lo_w = lo_w; p.lo_h = lo_h;
       p.ldd = d->C;
@@ -975,6 +1062,7 @@ int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy,
   p.ncblk = d->C / 64;                    // 64-channel sub-blocks per tap
   p.n_mblk = w.n_mblk;
   p.n_nblk = w.ncblk;
+  p.cg = 1;   // pairs measured neutral for wgrad (it is bound by the pixel-major operand loads, not by L2 bytes)
   p.Wo = d->Q; p.HoWo = d->P * d->Q;
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
   p.ws = reinterpret_cast<float*>(ws);

@@ -1,0 +1,22 @@
+"""The tensor-core kernels have two launch forms: single CTAs and CTA pairs (cta_group::2, a 256-row tile whose
+B operand is split between the two CTAs).  The library picks per shape; RNN_TC_PAIR=2 / 0 force one form wherever
+the shape allows, so the whole tensor-core parity file is re-run under each in a child process (the switch is read
+once per process)."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+ROOT = Path(__file__).resolve().parents[1]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode", ["2", "0"])
+def test_tc_parity_under_forced_launch_form(mode):
+    env = dict(os.environ, RNN_TC_PAIR=mode)
+    r = subprocess.run([sys.executable, "-m", "pytest", str(ROOT / "tests" / "test_tc_kernels.py"), "-m", "gpu", "-q",
+                        "-x", "--timeout", "600", "-p", "no:cacheprovider"],
+                       cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
