@@ -112,24 +112,28 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
   }
 }
 
-// Sum the per-block partials: one WARP per channel (8 channels per 256-thread block); the 32 lanes stride
-// over the partial rows and a shuffle tree combines them in a fixed order (deterministic).
+// Sum the per-block partials.  A 1024-thread block owns 32 channels: warp w walks partial rows w, w+32, ... with
+// its 32 lanes on 32 consecutive channels (one coalesced 128-byte load per row and quantity), then lane-columns
+// are combined through shared memory in a fixed order (deterministic).  With ~600 partial rows every thread has
+// all of its ~19 loads in flight at once, so the kernel costs about two L2 round trips instead of a chain of them.
 // Partial layout: [C / blk][nparts][2][blk] -- blk == C for the row-block partials of bn_reduce_kernel, blk = the
 // N tile of the convolution when the statistics come out of its epilogue (one partial row per epilogue warp).
-__device__ __forceinline__ void sum_partials_warp(const float* __restrict__ partials, int nparts, int C, int c,
-                                                  float& s, float& ss, int blk) {
-  const int lane = threadIdx.x & 31;
+// Returns true in the threads of warp 0 that hold a finished channel (c < C); s / ss are valid only there.
+constexpr int FIN_THREADS = 1024, FIN_CH = 32;
+__device__ __forceinline__ bool sum_partials_block(const float* __restrict__ partials, int nparts, int C, int c,
+                                                   float& s, float& ss, int blk) {
+  __shared__ float sm[2][32][FIN_CH + 1];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
   float a = 0.f, b = 0.f;
   if (c < C) {
     const float* base = partials + (long long)(c / blk) * nparts * 2 * blk + (c % blk);
     const long long rs = 2ll * blk;
-    // four independent row loads in flight per lane: the loop is latency-bound (partials sit in L2)
-    int p = lane;
+    int p = w;
     for (; p + 96 < nparts; p += 128) {
-      float a0 = base[p * rs], b0 = base[p * rs + blk];
-      float a1 = base[(p + 32) * rs], b1 = base[(p + 32) * rs + blk];
-      float a2 = base[(p + 64) * rs], b2 = base[(p + 64) * rs + blk];
-      float a3 = base[(p + 96) * rs], b3 = base[(p + 96) * rs + blk];
+      const float a0 = base[p * rs], b0 = base[p * rs + blk];
+      const float a1 = base[(p + 32) * rs], b1 = base[(p + 32) * rs + blk];
+      const float a2 = base[(p + 64) * rs], b2 = base[(p + 64) * rs + blk];
+      const float a3 = base[(p + 96) * rs], b3 = base[(p + 96) * rs + blk];
       a += (a0 + a1) + (a2 + a3);
       b += (b0 + b1) + (b2 + b3);
     }
@@ -138,20 +142,26 @@ __device__ __forceinline__ void sum_partials_warp(const float* __restrict__ part
       b += base[p * rs + blk];
     }
   }
-  s = warp_sum(a);
-  ss = warp_sum(b);
+  sm[0][w][lane] = a;
+  sm[1][w][lane] = b;
+  __syncthreads();
+  if (w != 0) return false;
+  a = 0.f; b = 0.f;
+#pragma unroll
+  for (int i = 0; i < 32; ++i) { a += sm[0][i][lane]; b += sm[1][i][lane]; }
+  s = a; ss = b;
+  return c < C;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(FIN_THREADS)
 bn_stats_finalize_kernel(const float* __restrict__ partials, int nparts, int C, float count,
                          const float* __restrict__ gamma, const float* __restrict__ beta, float eps,
                          float momentum, float* running_mean, float* running_var,
                          float* __restrict__ mean, float* __restrict__ invstd,
                          float* __restrict__ scale, float* __restrict__ shift, int blk) {
-  const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int c = blockIdx.x * FIN_CH + (threadIdx.x & 31);
   float s, ss;
-  sum_partials_warp(partials, nparts, C, c, s, ss, blk);
-  if ((threadIdx.x & 31) != 0 || c >= C) return;
+  if (!sum_partials_block(partials, nparts, C, c, s, ss, blk)) return;
   const float m = s / count;
   float var = ss / count - m * m;
   var = var < 0.f ? 0.f : var;
@@ -180,16 +190,15 @@ __global__ void bn_eval_prepare_kernel(const float* __restrict__ gamma, const fl
   shift[c] = b - rm[c] * g * is;
 }
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(FIN_THREADS)
 bn_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int C,
                        float* __restrict__ sum_dy, float* __restrict__ sum_dy_xhat,
                        void* dgamma, void* dbeta, int grads_f32, int accumulate,
                        const float* __restrict__ mean, const float* __restrict__ invstd,
                        const float* __restrict__ gamma, float inv_count, float* __restrict__ coef /* [3][C] */) {
-  const int c = blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int c = blockIdx.x * FIN_CH + (threadIdx.x & 31);
   float s, ss;
-  sum_partials_warp(partials, nparts, C, c, s, ss, C);
-  if ((threadIdx.x & 31) != 0 || c >= C) return;
+  if (!sum_partials_block(partials, nparts, C, c, s, ss, C)) return;
   sum_dy[c] = s;
   sum_dy_xhat[c] = ss;
   {
@@ -499,11 +508,11 @@ int bn_static_scratch_address(float** out) {
 }  // namespace
 
 // Finalize BatchNorm statistics from partial sums produced elsewhere (the convolution epilogue): used by
-// tc_gemm.cu.  `blk` = columns per partial block (see sum_partials_warp).
+// tc_gemm.cu.  `blk` = columns per partial block (see sum_partials_block).
 int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, float count, const float* gamma,
                              const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                              float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>(partials, nparts, C, count, gamma, beta, eps, momentum,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>(partials, nparts, C, count, gamma, beta, eps, momentum,
                                                                 running_mean, running_var, mean, invstd, scale, shift, blk);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
@@ -523,7 +532,7 @@ int rnn_bn_stats_bf16(const void* x, long long M, int C, const float* gamma, con
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            (float*)ws);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift, C);
   RNN_CHECK_LAUNCH();
@@ -567,7 +576,7 @@ int rnn_bn_stats_bf16_static(const void* x, long long M, int C, const float* gam
   bn_reduce_kernel<false><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, nullptr, nullptr, nullptr, nullptr, M, C,
                                                            scratch);
   RNN_CHECK_LAUNCH();
-  bn_stats_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
+  bn_stats_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>(scratch, gy, C, (float)M, gamma, beta, eps,
                                                                    momentum, running_mean, running_var, mean, invstd,
                                                                    scale, shift, C);
   RNN_CHECK_LAUNCH();
@@ -614,7 +623,7 @@ int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable
   bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
                                                           invstd, M, C, (float*)ws, fwd_scale, fwd_shift, relu_mask);
   RNN_CHECK_LAUNCH();
-  bn_bwd_finalize_kernel<<<ceil_div_i(C, 8), 256, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
+  bn_bwd_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
                                                                 dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
                                                                 1.f / (float)M, coef);
   RNN_CHECK_LAUNCH();

@@ -48,7 +48,11 @@ def main():
             P = (H + 2 * pad - R) // stride + 1
             dy = torch.randn(N, P, P, K, device="cuda").to(torch.bfloat16)
             fl = 2.0 * N * P * P * K * C * R * R
+            g = torch.ones(K, device="cuda"); b0 = torch.zeros(K, device="cuda")
+            rm = torch.zeros(K, device="cuda"); rv = torch.ones(K, device="cuda")
             for name, fn in (("fprop", lambda: RF.conv2d_fprop(x, w, stride=stride, pad=pad)),
+                             ("fprop+bnstats", lambda: RF.conv2d_fprop_bn_stats(x, w, g, b0, 1e-5, 0.1, rm, rv,
+                                                                                stride=stride, pad=pad)),
                              ("dgrad", lambda: RF.conv2d_dgrad(dy, w, tuple(x.shape), stride=stride, pad=pad)),
                              ("wgrad", lambda: RF.conv2d_wgrad(x, dy, tuple(w.shape), stride=stride, pad=pad))):
                 ms = time_it(fn)
