@@ -67,11 +67,15 @@ struct TcParams {
 // CG = CTAs per MMA (cta_group): 1, or 2 = a CTA pair computing a 256 x BN tile with each CTA staging its own
 // 128 rows of A and HALF of B (the pair's tensor cores read both halves), which halves the operand bytes every
 // SM pulls through L2 per FLOP and deepens the pipeline.
+#ifndef RNN_TC_STAGE_BUDGET
+#define RNN_TC_STAGE_BUDGET 196608
+#endif
+constexpr int kStageBudget = RNN_TC_STAGE_BUDGET;  // bytes of shared memory given to the operand ring
 template <int BN, int CG = 1>
 struct Cfg {
   static constexpr int B_BYTES = BN * BK * 2 / CG;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (196608 / STAGE_BYTES) > 8 ? 8 : (196608 / STAGE_BYTES);
+  static constexpr int STAGES = (kStageBudget / STAGE_BYTES) > 8 ? 8 : (kStageBudget / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BN == 192 ? 256 : BN;  // TMEM columns between the two accumulators
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;         // 128 / 256 / 512: powers of two
   static constexpr int STAGING_BYTES = 4 * 2 * 4096;       // per epilogue warp: 2 x (32 rows x 128 B)

@@ -5,12 +5,17 @@ activations NHWC, filters KRSC, everything contiguous.  No function here compute
 """
 from __future__ import annotations
 
+import contextlib
+import os
+import threading
+
 import torch
 
 from . import _lib
 from ._lib import check, conv_desc, cur_stream, ptr
 
-_workspaces: dict[int, torch.Tensor] = {}
+_workspaces: dict[tuple[int, int], torch.Tensor] = {}
+_tls = threading.local()
 
 # Optional per-call device timing used by bench.py: when `_profile` is a list, every instrumented wrapper
 # appends (kind, algorithmic_bytes_or_None, start_event, end_event) recorded on the launching stream.
@@ -47,15 +52,102 @@ def launch_count() -> int:
 
 
 def workspace(nbytes: int, device) -> torch.Tensor | None:
-    """Grow-only per-device scratch buffer (torch caching allocator owns the memory)."""
+    """Grow-only per-device scratch buffer (torch caching allocator owns the memory).  Kernels enqueued inside
+    `side_stream()` get a buffer of their own: they run concurrently with the main stream's kernels."""
     if nbytes <= 0:
         return None
-    idx = torch.device(device).index or 0
-    ws = _workspaces.get(idx)
+    key = (torch.device(device).index or 0, getattr(_tls, "slot", 0))
+    ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
-        _workspaces[idx] = ws
+        _workspaces[key] = ws
     return ws
+
+
+# ------------------------------------------------------------------------------------------- side stream
+# Backward has two independent consumers of every convolution's output gradient: dgrad (on the critical path to
+# the next layer) and wgrad (needed only by the optimizer).  The weight-gradient kernels are tensor-core work, the
+# BatchNorm backward kernels that follow dgrad on the critical path are HBM streaming work; issued on two streams
+# they share the SMs instead of taking turns.  RNN_SIDE_STREAM=0 keeps everything on one stream.
+class _Side:
+    def __init__(self, device):
+        self.stream = torch.cuda.Stream(device=device)
+        self.pending: list = []        # [(event after the group's last kernel, tensors kept alive, on_join)]
+        self.callback_queued = False
+
+
+_sides: dict[int, _Side] = {}
+_side_enabled = os.environ.get("RNN_SIDE_STREAM", "1") != "0"
+
+
+def side_enabled() -> bool:
+    return _side_enabled and _profile is None   # per-kernel event timing needs one stream
+
+
+def _side(device) -> _Side:
+    idx = torch.device(device).index
+    if idx is None:
+        idx = torch.cuda.current_device()
+    st = _sides.get(idx)
+    if st is None:
+        st = _sides[idx] = _Side(torch.device("cuda", idx))
+    return st
+
+
+@contextlib.contextmanager
+def side_stream(device):
+    """Enqueue the enclosed kernels on the device's side stream, ordered after everything enqueued so far on the
+    current stream.  Follow with side_commit(); the work is joined back by side_join()."""
+    st = _side(device)
+    ev = torch.cuda.Event()
+    ev.record()
+    st.stream.wait_event(ev)
+    prev = getattr(_tls, "slot", 0)
+    _tls.slot = 1
+    try:
+        with torch.cuda.stream(st.stream):
+            yield st
+    finally:
+        _tls.slot = prev
+
+
+def side_commit(device, keepalive, on_join=None) -> None:
+    """Close a group of side-stream kernels.  `keepalive`: every tensor those kernels read or write that could
+    otherwise be freed (and its memory reused by the main stream) before the group is joined."""
+    st = _side(device)
+    ev = torch.cuda.Event()
+    ev.record(st.stream)
+    st.pending.append((ev, keepalive, on_join))
+
+
+def side_join(device=None, keep: int = 0) -> None:
+    """Make the current stream wait for all but the newest `keep` committed groups, then run their on_join
+    callbacks (gradient-ready notifications) and drop the tensors they kept alive."""
+    for idx, st in list(_sides.items()):
+        if device is not None and (torch.device(device).index or 0) != idx:
+            continue
+        while len(st.pending) > keep:
+            ev, _keep, cb = st.pending.pop(0)
+            torch.cuda.current_stream(torch.device("cuda", idx)).wait_event(ev)
+            if cb is not None:
+                cb()
+
+
+def side_join_at_end_of_backward(device) -> None:
+    """Queue (once per backward pass) an autograd-engine callback that joins every outstanding group, so that
+    whatever runs after `.backward()` -- optimizer, all-reduce, the end of a CUDA-graph capture -- sees them."""
+    st = _side(device)
+    if st.callback_queued:
+        return
+    st.callback_queued = True
+    dev = torch.device(device)
+
+    def _cb():
+        st.callback_queued = False
+        with torch.cuda.device(dev):
+            side_join(dev)
+
+    torch.autograd.Variable._execution_engine.queue_callback(_cb)
 
 
 def _req(t: torch.Tensor, dtype, name: str):

@@ -579,10 +579,22 @@ class BottleneckFn(Function):
             _notify(gamma); _notify(beta)
             return dx2.reshape(y4.shape), (dres2.reshape(y4.shape) if dres2 is not None else None)
 
+        dev = dout.device
+        use_side = RF.side_enabled()
+        side_group: list = []   # (param, operands) of the weight-gradient kernels issued on the side stream
+
         def wgrad(w, xin, dy, s, p):
             kshape = tuple(nhwc(w).shape)
-            _write_param_grad(w, lambda o, acc: RF.conv2d_wgrad(xin, dy, kshape, stride=s, pad=p,
-                                                                out=nhwc_param_view(o), accumulate=acc))
+            if not (use_side and w.is_leaf):
+                _write_param_grad(w, lambda o, acc: RF.conv2d_wgrad(xin, dy, kshape, stride=s, pad=p,
+                                                                    out=nhwc_param_view(o), accumulate=acc))
+                return
+            # off the critical path: nothing in this backward pass reads dW, so the kernel goes to the side stream
+            # where it overlaps the HBM-bound BatchNorm kernels of the main chain
+            tgt, acc = grad_target(w)
+            with RF.side_stream(dev):
+                RF.conv2d_wgrad(xin, dy, kshape, stride=s, pad=p, out=nhwc_param_view(tgt), accumulate=acc)
+            side_group.append((w, xin, dy, tgt))
 
         # bn3 (+ residual, ReLU): gradient of conv3's output and of the identity branch
         dy3, dres = bn_b(dout_h, y3, s3, g3, b3, omask, True, False)
@@ -605,4 +617,10 @@ class BottleneckFn(Function):
         elif need_dx:
             # identity shortcut: dres already IS d(out)/d(x) through the skip; conv1's dgrad accumulates into it
             dx = RF.conv2d_dgrad(dy1, k1, tuple(xh.shape), out=dres, accumulate=True)
+        if side_group:
+            params = [g[0] for g in side_group]
+            RF.side_commit(dev, side_group, lambda: [_notify(p_) for p_ in params])
+            # join with a lag of one block: this block's weight gradients overlap the next block's main chain
+            RF.side_join(dev, keep=1)
+            RF.side_join_at_end_of_backward(dev)
         return (nchw(dx) if dx is not None else None,) + (None,) * (15 + (8 if ctx.has_down else 6))

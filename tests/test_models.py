@@ -216,3 +216,31 @@ def test_fused_bottleneck_matches_layerwise_path():
         assert torch.allclose(res[True][2][k], res[False][2][k], rtol=2e-2, atol=2e-3), k
     for n, gr in res[True][1].items():
         assert cosine(gr, res[False][1][n]) > 0.99, n   # rounding-order noise only (see noise-floor note)
+
+
+def test_side_stream_weight_gradients_are_bitwise_the_same(monkeypatch):
+    """The bottleneck backward issues its weight-gradient kernels on a side stream (joined with a lag of one
+    block and at the end of backward).  Same kernels, same inputs: gradients must match the one-stream run
+    bit for bit, over several steps so that a missed join (a race) would show."""
+    from replicann_b200 import functional as RF
+    from replicann_b200.arch.resnet import ResNet
+    g = torch.Generator().manual_seed(11)
+    x = torch.randn(16, 3, 64, 64, generator=g).cuda()
+    y = torch.randint(0, 16, (16,), generator=g).cuda()
+    res = {}
+    for side in (True, False):
+        monkeypatch.setattr(RF, "_side_enabled", side)
+        torch.manual_seed(3)
+        m = ResNet((2, 2), bottleneck=True, n_classes=16).cuda().to(torch.bfloat16)
+        grads = []
+        for _ in range(3):
+            for p in m.parameters():
+                p.grad = None
+            F.cross_entropy(m(x).float(), y).backward()
+            grads.append({n: p.grad.clone() for n, p in m.named_parameters()})
+        torch.cuda.synchronize()
+        assert not any(st.pending for st in RF._sides.values())   # everything joined when backward returned
+        res[side] = grads
+    for a, b in zip(res[True], res[False]):
+        for n in a:
+            assert torch.equal(a[n], b[n]), n
