@@ -67,15 +67,16 @@ struct TcParams {
 // CG = CTAs per MMA (cta_group): 1, or 2 = a CTA pair computing a 256 x BN tile with each CTA staging its own
 // 128 rows of A and HALF of B (the pair's tensor cores read both halves), which halves the operand bytes every
 // SM pulls through L2 per FLOP and deepens the pipeline.
-#ifndef RNN_TC_STAGE_BUDGET
-#define RNN_TC_STAGE_BUDGET 196608
-#endif
-constexpr int kStageBudget = RNN_TC_STAGE_BUDGET;  // bytes of shared memory given to the operand ring
-template <int BN, int CG = 1>
+// Shared memory given to the operand ring.  The weight-gradient kernels take less: they run on a side stream
+// beside the BatchNorm backward kernels of the main stream, whose blocks need 16 KB each to be co-resident.
+constexpr int kStageBudget = 196608;
+constexpr int kStageBudgetWgrad = 163840;
+template <int BN, int CG = 1, int KIND = KIND_GEMM>
 struct Cfg {
+  static constexpr int BUDGET = KIND == KIND_WGRAD ? kStageBudgetWgrad : kStageBudget;
   static constexpr int B_BYTES = BN * BK * 2 / CG;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (kStageBudget / STAGE_BYTES) > 8 ? 8 : (kStageBudget / STAGE_BYTES);
+  static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BN == 192 ? 256 : BN;  // TMEM columns between the two accumulators
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;         // 128 / 256 / 512: powers of two
   static constexpr int STAGING_BYTES = 4 * 2 * 4096;       // per epilogue warp: 2 x (32 rows x 128 B)
@@ -90,7 +91,7 @@ template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS, int CG
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
           const __grid_constant__ CUtensorMap tmD, const __grid_constant__ TcParams p) {
-  using C = Cfg<BN, CG>;
+  using C = Cfg<BN, CG, KIND>;
   static_assert(CG == 1 || (BN % 128 == 0), "a CTA pair splits B in halves of whole 64-wide blocks");
   const int cta_rank = CG == 2 ? (int)tc::cluster_ctarank() : 0;   // 0 = the CTA that issues the MMAs
   const int cluster_id = blockIdx.x / CG, num_clusters = gridDim.x / CG;
@@ -640,7 +641,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   }
   static bool attr_set = false;
   auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED, STATS, CG>;
-  constexpr int smem = Cfg<BN, CG>::SMEM_BYTES;
+  constexpr int smem = Cfg<BN, CG, KIND>::SMEM_BYTES;
   if (!attr_set) {
     RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     attr_set = true;

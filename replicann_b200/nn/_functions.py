@@ -597,26 +597,29 @@ class BottleneckFn(Function):
             side_group.append((w, xin, dy, tgt))
 
         # bn3 (+ residual, ReLU): gradient of conv3's output and of the identity branch
+        # Order of issue: each wgrad is enqueued AFTER the dgrad of the same layer, so on the side stream it starts
+        # once that dgrad has finished and runs beside the BatchNorm backward kernels that follow on the main
+        # stream (tensor-core work next to HBM streaming work) instead of contending with the dgrad for the SMs.
         dy3, dres = bn_b(dout_h, y3, s3, g3, b3, omask, True, False)
-        wgrad(w3, z2, dy3, 1, 0)
         dz2 = RF.conv2d_dgrad(dy3, k3, tuple(z2.shape))
+        wgrad(w3, z2, dy3, 1, 0)
         dy2, _ = bn_b(dz2, y2, s2, g2, b2, None, False, True)
-        wgrad(w2, z1, dy2, stride, 1)
         dz1 = RF.conv2d_dgrad(dy2, k2, tuple(z1.shape), stride=stride, pad=1)
+        wgrad(w2, z1, dy2, stride, 1)
         dy1, _ = bn_b(dz1, y1, s1, g1, b1, None, False, True)
-        wgrad(w1, xh, dy1, 1, 0)
         need_dx = ctx.needs_input_grad[0]
         dx = None
         if ctx.has_down:
             kd = nhwc(wd)
             dyd, _ = bn_b(dres, yd, sd, gd, bd, None, False, False)
-            wgrad(wd, xh, dyd, stride, 0)
             if need_dx:
                 dx = RF.conv2d_dgrad(dyd, kd, tuple(xh.shape), stride=stride)
                 RF.conv2d_dgrad(dy1, k1, tuple(xh.shape), out=dx, accumulate=True)
+            wgrad(wd, xh, dyd, stride, 0)
         elif need_dx:
             # identity shortcut: dres already IS d(out)/d(x) through the skip; conv1's dgrad accumulates into it
             dx = RF.conv2d_dgrad(dy1, k1, tuple(xh.shape), out=dres, accumulate=True)
+        wgrad(w1, xh, dy1, 1, 0)
         if side_group:
             params = [g[0] for g in side_group]
             RF.side_commit(dev, side_group, lambda: [_notify(p_) for p_ in params])
