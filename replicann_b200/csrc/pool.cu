@@ -36,6 +36,47 @@ struct PoolGeom {
   int N, H, W, C, R, S, sh, sw, ph, pw, P, Q;
 };
 
+// Element-group index -> (n, a, b, cg) for a [N, A, B, cgs] iteration space.  32-bit arithmetic whenever the
+// space fits (64-bit integer division costs ~10x more and these kernels decode one index per 16 bytes moved).
+template <typename I>
+__device__ __forceinline__ void decode4(long long i, int cgs, int B, int A, int& n, int& a, int& b, int& cg) {
+  I t = (I)i;
+  cg = (int)(t % (I)cgs); t /= (I)cgs;
+  b = (int)(t % (I)B); t /= (I)B;
+  a = (int)(t % (I)A);
+  n = (int)(t / (I)A);
+}
+
+// window position (1 byte per element) packed VW to a word
+template <int VW> struct WIdx;
+template <> struct WIdx<1> {
+  __device__ static void store(unsigned char* p, const int* l) { p[0] = (unsigned char)l[0]; }
+  __device__ static void load(const unsigned char* p, int* l) { l[0] = p[0]; }
+};
+template <> struct WIdx<4> {
+  __device__ static void store(unsigned char* p, const int* l) {
+    *reinterpret_cast<unsigned*>(p) = (unsigned)l[0] | ((unsigned)l[1] << 8) | ((unsigned)l[2] << 16) | ((unsigned)l[3] << 24);
+  }
+  __device__ static void load(const unsigned char* p, int* l) {
+    const unsigned v = *reinterpret_cast<const unsigned*>(p);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) l[e] = (v >> (8 * e)) & 0xffu;
+  }
+};
+template <> struct WIdx<8> {
+  __device__ static void store(unsigned char* p, const int* l) {
+    uint2 v;
+    v.x = (unsigned)l[0] | ((unsigned)l[1] << 8) | ((unsigned)l[2] << 16) | ((unsigned)l[3] << 24);
+    v.y = (unsigned)l[4] | ((unsigned)l[5] << 8) | ((unsigned)l[6] << 16) | ((unsigned)l[7] << 24);
+    *reinterpret_cast<uint2*>(p) = v;
+  }
+  __device__ static void load(const unsigned char* p, int* l) {
+    const uint2 v = *reinterpret_cast<const uint2*>(p);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) { l[e] = (v.x >> (8 * e)) & 0xffu; l[4 + e] = (v.y >> (8 * e)) & 0xffu; }
+  }
+};
+
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx,
@@ -43,40 +84,37 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.P * g.Q * cgs;
+  const bool small = total < (1ll << 31);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % cgs);
-    long long t = i / cgs;
-    const int q = (int)(t % g.Q); t /= g.Q;
-    const int p = (int)(t % g.P);
-    const int n = (int)(t / g.P);
+    int n, p, q, cg;
+    if (small) decode4<unsigned>(i, cgs, g.Q, g.P, n, p, q, cg);
+    else decode4<long long>(i, cgs, g.Q, g.P, n, p, q, cg);
     float best[VW];
-    int bi[VW];
+    int bl[VW];   // argmax as the position inside the (unclipped) R x S window
     const int h0 = p * g.sh - g.ph, w0 = q * g.sw - g.pw;
     const int hs = h0 < 0 ? 0 : h0, ws = w0 < 0 ? 0 : w0;
     const int he = min(h0 + g.R, g.H), we = min(w0 + g.S, g.W);
 #pragma unroll
-    for (int e = 0; e < VW; ++e) { best[e] = -INFINITY; bi[e] = hs * g.W + ws; }
+    for (int e = 0; e < VW; ++e) { best[e] = -INFINITY; bl[e] = (hs - h0) * g.S + (ws - w0); }
     for (int h = hs; h < he; ++h)
       for (int w = ws; w < we; ++w) {
         float v[VW];
         PV<T, VEC>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
+        const int local = (h - h0) * g.S + (w - w0);
 #pragma unroll
         for (int e = 0; e < VW; ++e)
-          if (v[e] > best[e] || v[e] != v[e]) { best[e] = v[e]; bi[e] = h * g.W + w; }
+          if (v[e] > best[e] || v[e] != v[e]) { best[e] = v[e]; bl[e] = local; }
       }
     const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
     PV<T, VEC>::store(y + o, best);
-    if (idx) {
-#pragma unroll
-      for (int e = 0; e < VW; ++e) idx[o + e] = bi[e];
-    }
-    if (widx) {  // position inside the (unclipped) window: 1 byte instead of 4 for the backward pass
+    if (idx) {  // torch's flat index h * W + w inside the input plane
 #pragma unroll
       for (int e = 0; e < VW; ++e) {
-        const int bh = bi[e] / g.W, bw = bi[e] - bh * g.W;
-        widx[o + e] = (unsigned char)((bh - h0) * g.S + (bw - w0));
+        const int lh = bl[e] / g.S, lw = bl[e] - lh * g.S;
+        idx[o + e] = (h0 + lh) * g.W + (w0 + lw);
       }
     }
+    if (widx) WIdx<VW>::store(widx + o, bl);  // 1 byte instead of 4 for the backward pass
   }
 }
 
@@ -88,12 +126,11 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
   const long long total = (long long)g.N * g.H * g.W * cgs;
+  const bool small = total < (1ll << 31);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int cg = (int)(i % cgs);
-    long long t = i / cgs;
-    const int w = (int)(t % g.W); t /= g.W;
-    const int h = (int)(t % g.H);
-    const int n = (int)(t / g.H);
+    int n, h, w, cg;
+    if (small) decode4<unsigned>(i, cgs, g.W, g.H, n, h, w, cg);
+    else decode4<long long>(i, cgs, g.W, g.H, n, h, w, cg);
     const int me = h * g.W + w;
     float acc[VW];
 #pragma unroll
@@ -110,9 +147,11 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
         PV<T, VEC>::load(dy + o, d);
         if (widx) {
           const int local = (h - (p * g.sh - g.ph)) * g.S + (w - (q * g.sw - g.pw));
+          int l[VW];
+          WIdx<VW>::load(widx + o, l);
 #pragma unroll
           for (int e = 0; e < VW; ++e)
-            if ((int)widx[o + e] == local) acc[e] += d[e];
+            if (l[e] == local) acc[e] += d[e];
         } else {
 #pragma unroll
           for (int e = 0; e < VW; ++e)
