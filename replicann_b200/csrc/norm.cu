@@ -237,8 +237,7 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
                 unsigned char* __restrict__ relu_mask) {
   const long long stride = (long long)gridDim.x * blockDim.x;
   const uint4 z = make_uint4(0, 0, 0, 0);
-  auto finish = [&](long long i, const uint4& ux, const uint4& ur) {
-    const int cg = (int)(i % cgs);
+  auto finish = [&](long long i, int cg, const uint4& ux, const uint4& ur) {
     float v[8];
     unpack8(ux, v);
     const float4 a0 = __ldg(reinterpret_cast<const float4*>(scale + cg * 8));
@@ -269,17 +268,24 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
     }
   };
   constexpr int U = APPLY_UNROLL;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  // channel group of each vector without a 64-bit modulo per trip: it advances by (stride mod cgs), wrapped
+  int cg = (int)(i0 % cgs);
+  const int dcg = (int)(stride % cgs);
+  for (long long i = i0; i < nvec; i += U * stride) {
     uint4 xs[U], rs[U];
+    int cgu[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long j = i + u * stride;
       xs[u] = j < nvec ? ld_stream(x + j * 8) : z;
       rs[u] = (j < nvec && residual) ? ld_stream(residual + j * 8) : z;
+      cgu[u] = cg;
+      cg += dcg; cg -= cg >= cgs ? cgs : 0;
     }
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      if (i + u * stride < nvec) finish(i + u * stride, xs[u], rs[u]);
+      if (i + u * stride < nvec) finish(i + u * stride, cgu[u], xs[u], rs[u]);
   }
 }
 
@@ -291,8 +297,8 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
   const int C = cgs * 8;
   const long long stride = (long long)gridDim.x * blockDim.x;
   const uint4 z = make_uint4(0, 0, 0, 0);
-  auto finish = [&](long long i, const uint4& ug, const uint4& ux, const uint4& uo, unsigned mbits) {
-    const int c0 = (int)(i % cgs) * 8;
+  auto finish = [&](long long i, int cg, const uint4& ug, const uint4& ux, const uint4& uo, unsigned mbits) {
+    const int c0 = cg * 8;
     float g[8], v[8];
     unpack8(ug, g);
     unpack8(ux, v);
@@ -326,9 +332,13 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
     st_stream(dx + i * 8, pack8(r));
   };
   constexpr int U = APPLY_UNROLL;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += U * stride) {
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  int cg = (int)(i0 % cgs);
+  const int dcg = (int)(stride % cgs);
+  for (long long i = i0; i < nvec; i += U * stride) {
     uint4 gs[U], xs[U], os[U];
     unsigned ms[U];
+    int cgu[U];
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const long long j = i + u * stride;
@@ -337,10 +347,12 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
       xs[u] = ok ? ld_stream(x + j * 8) : z;
       os[u] = (ok && yout) ? ld_stream(yout + j * 8) : z;
       ms[u] = (ok && bitmask) ? bitmask[j] : 0u;
+      cgu[u] = cg;
+      cg += dcg; cg -= cg >= cgs ? cgs : 0;
     }
 #pragma unroll
     for (int u = 0; u < U; ++u)
-      if (i + u * stride < nvec) finish(i + u * stride, gs[u], xs[u], os[u], ms[u]);
+      if (i + u * stride < nvec) finish(i + u * stride, cgu[u], gs[u], xs[u], os[u], ms[u]);
   }
 }
 

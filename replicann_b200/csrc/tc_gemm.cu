@@ -107,7 +107,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint64_t* tempty_bar = tfull_bar + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
 
-  const int warp = threadIdx.x >> 5;
+  // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role loops' state
+  // (stage counters, barrier addresses, TMA coordinates, MMA descriptors) in uniform registers
+  const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
   const int num_tiles = n_pm * p.n_nblk * p.splits;
 
@@ -135,12 +137,19 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
+  const uint32_t smem_a0 = tc::smem_u32(smem);              // stage s: A at smem_a0 + s * STAGE_BYTES, B after it
+  const uint32_t full0 = tc::smem_u32(full_bar), empty0 = tc::smem_u32(empty_bar);
+
   if (warp == 0) {
     // ===================================================================== TMA producer
-    if (lane == 0) {
+    // One elected thread.  Everything that does not change from one K step to the next is computed per tile; a
+    // K step costs a barrier wait, the expect_tx arrive and the TMA instructions (the step rate of this thread,
+    // not the memory system, bounded the narrow-N tiles before: ~800 cycles per step).
+    if (tc::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
       constexpr int NB_LOCAL = BN / 64 / CG;   // 64-wide B blocks staged by this CTA (MN-major B)
+      const int jb0 = cta_rank * NB_LOCAL;     // first 64-wide B block this CTA stages
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int t = tile;
         const int nblk = t % p.n_nblk; t /= p.n_nblk;
@@ -149,7 +158,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
         const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         const int m0 = mblk * BM;
-        int n0 = nblk * BN;
+        const int n0 = nblk * BN;
         // CONV: base pixel of this M tile
         int img0 = 0, w0 = 0, h0 = 0;
         if (KIND == KIND_CONV) {
@@ -180,72 +189,89 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           }
         }
         // loads of a pair credit the even CTA's barrier; it alone announces the bytes of BOTH CTAs
-        auto ld2 = [&](void* dst, const CUtensorMap* m, uint64_t* bar, int c0, int c1) {
-          if (CG == 2) tc::tma_load_2d_pair(dst, m, bar, c0, c1);
-          else tc::tma_load_2d(dst, m, bar, c0, c1);
-        };
-        auto ldi = [&](void* dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n, uint16_t ow,
-                       uint16_t oh) {
-          if (CG == 2) tc::tma_load_im2col_4d_pair(dst, m, bar, c, w, h, n, ow, oh);
-          else tc::tma_load_im2col_4d(dst, m, bar, c, w, h, n, ow, oh);
-        };
-        const int jb0 = cta_rank * NB_LOCAL;     // first 64-wide B block this CTA stages
+        const uint32_t tx_bytes = KIND == KIND_WGRAD ? (uint32_t)(CG * A_BYTES + nsb_valid * 8192)
+                                                     : (uint32_t)(CG * C::STAGE_BYTES);
+        // CONV: (tap, channel chunk) of the K step, advanced without divisions
+        int tap = 0, cc = 0;
+        TapDesc td = p.taps[0];
+        if (KIND == KIND_CONV) {
+          tap = k_lo / p.cchunks;
+          cc = k_lo - tap * p.cchunks;
+          td = p.taps[tap];
+        }
+        // WGRAD: pixel coordinates of the K step, advanced by 64 pixels per step
+        int wg_img = 0, wg_i = 0, wg_j = 0;
+        const int wg_ho = KIND == KIND_WGRAD ? p.HoWo / p.Wo : 1;
+        if (KIND == KIND_WGRAD) {
+          const int pix0 = k_lo * BK;
+          wg_img = pix0 / p.HoWo;
+          const int rem = pix0 - wg_img * p.HoWo;
+          wg_i = rem / p.Wo;
+          wg_j = rem - wg_i * p.Wo;
+        }
         for (int it = k_lo; it < k_hi; ++it) {
-          tc::mbar_wait(&empty_bar[stage], phase ^ 1u);
-          uint8_t* sA = smem + stage * C::STAGE_BYTES;
-          uint8_t* sB = sA + A_BYTES;
-          if (cta_rank == 0)
-            tc::mbar_expect_tx(&full_bar[stage], KIND == KIND_WGRAD ? (uint32_t)(CG * A_BYTES + nsb_valid * 8192)
-                                                                    : (uint32_t)(CG * C::STAGE_BYTES));
+          const uint32_t fb = full0 + stage * 8;
+          const uint32_t sA = smem_a0 + stage * C::STAGE_BYTES;
+          const uint32_t sB = sA + A_BYTES;
+          tc::mbar_wait(empty0 + stage * 8, phase ^ 1u);
+          if (cta_rank == 0) tc::mbar_expect_tx(fb, tx_bytes);
           if (KIND == KIND_GEMM) {
             const int kc = it * BK;
             if (!A_MN) {
-              ld2(sA, &tmA, &full_bar[stage], kc, m0);
+              tc::tma_ld2<CG>(sA, &tmA, fb, kc, m0);
             } else {
-              ld2(sA, &tmA, &full_bar[stage], m0, kc);
-              ld2(sA + 8192, &tmA, &full_bar[stage], m0 + 64, kc);
+              tc::tma_ld2<CG>(sA, &tmA, fb, m0, kc);
+              tc::tma_ld2<CG>(sA + 8192, &tmA, fb, m0 + 64, kc);
             }
             if (!B_MN) {
-              ld2(sB, &tmB, &full_bar[stage], kc, n0 + cta_rank * (BN / CG));   // box rows = BN / CG
+              tc::tma_ld2<CG>(sB, &tmB, fb, kc, n0 + cta_rank * (BN / CG));   // box rows = BN / CG
             } else {
 #pragma unroll
-              for (int j = 0; j < NB_LOCAL; ++j)
-                ld2(sB + j * 8192, &tmB, &full_bar[stage], n0 + (jb0 + j) * 64, kc);
+              for (int j = 0; j < NB_LOCAL; ++j) tc::tma_ld2<CG>(sB + j * 8192, &tmB, fb, n0 + (jb0 + j) * 64, kc);
             }
           } else if (KIND == KIND_CONV) {
-            const int tap = it / p.cchunks;
-            const int cc = it - tap * p.cchunks;
-            const TapDesc td = p.taps[tap];
-            ldi(sA, &tmA, &full_bar[stage], cc * BK, w0, h0, img0, (uint16_t)td.ow, (uint16_t)td.oh);
+            tc::tma_ldi<CG>(sA, &tmA, fb, cc * BK, w0, h0, img0, (uint16_t)td.ow, (uint16_t)td.oh);
             if (!B_MN) {
-              ld2(sB, &tmB, &full_bar[stage], td.bcol + cc * BK, n0 + cta_rank * (BN / CG));
+              tc::tma_ld2<CG>(sB, &tmB, fb, td.bcol + cc * BK, n0 + cta_rank * (BN / CG));
             } else {
 #pragma unroll
               for (int j = 0; j < NB_LOCAL; ++j)
-                ld2(sB + j * 8192, &tmB, &full_bar[stage], td.bcol + n0 + (jb0 + j) * 64, cc * BK);
+                tc::tma_ld2<CG>(sB + j * 8192, &tmB, fb, td.bcol + n0 + (jb0 + j) * 64, cc * BK);
+            }
+            if (++cc == p.cchunks) {
+              cc = 0;
+              ++tap;
+              td = p.taps[tap < MAX_TAPS ? tap : 0];
             }
           } else {  // KIND_WGRAD: reduction over pixels
             const int pix0 = it * BK;
-            const int img = pix0 / p.HoWo;
-            const int rem = pix0 - img * p.HoWo;
-            const int i = rem / p.Wo, j2 = rem - i * p.Wo;
-            ld2(sA, &tmA, &full_bar[stage], m0, pix0);
-            ld2(sA + 8192, &tmA, &full_bar[stage], m0 + 64, pix0);
+            tc::tma_ld2<CG>(sA, &tmA, fb, m0, pix0);
+            tc::tma_ld2<CG>(sA + 8192, &tmA, fb, m0 + 64, pix0);
+            const int cw = wg_j * p.ts_w + p.lo_w, ch = wg_i * p.ts_h + p.lo_h;
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j) {
               if (j >= jb0 && j < jb0 + NB_LOCAL && j < nsb_valid)
-                ldi(sB + (j - jb0) * 8192, &tmB, &full_bar[stage], sb_c0[j], j2 * p.ts_w + p.lo_w,
-                    i * p.ts_h + p.lo_h, img, sb_ow[j], sb_oh[j]);
+                tc::tma_ldi<CG>(sB + (j - jb0) * 8192, &tmB, fb, sb_c0[j], cw, ch, wg_img, sb_ow[j], sb_oh[j]);
             }
+            // next step starts 64 pixels further: carry into rows and images without dividing
+            wg_j += BK;
+            while (wg_j >= p.Wo) { wg_j -= p.Wo; if (++wg_i == wg_ho) { wg_i = 0; ++wg_img; } }
           }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
       }
     }
+    __syncwarp();
   } else if (warp == 1) {
     // ===================================================================== MMA issuer
-    if (lane == 0 && cta_rank == 0) {
+    if (cta_rank == 0 && tc::elect_one()) {
       constexpr uint32_t idesc = tc::make_idesc_bf16(BM * CG, BN, A_MN, B_MN);
+      // descriptors of stage 0; a stage adds STAGE_BYTES >> 4 and a 16-wide K slice adds KADV to the address field
+      const uint64_t adesc0 = A_MN ? tc::make_smem_desc(smem_a0, 8192, 1024) : tc::make_smem_desc(smem_a0, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? tc::make_smem_desc(smem_a0 + A_BYTES, 8192, 1024)
+                                   : tc::make_smem_desc(smem_a0 + A_BYTES, 16, 1024);
+      constexpr uint32_t A_KADV = (A_MN ? 2048 : 32) >> 4, B_KADV = (B_MN ? 2048 : 32) >> 4;
+      const uint32_t tfull0 = tc::smem_u32(tfull_bar), tempty0 = tc::smem_u32(tempty_bar);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -254,32 +280,31 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int split = tile / (p.n_nblk * n_pm);
         const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
         const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
-        tc::mbar_wait(&tempty_bar[acc], acc_phase ^ 1u);
+        tc::mbar_wait(tempty0 + acc * 8, acc_phase ^ 1u);
         tc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * C::ACC_STRIDE);
+        uint32_t accumulate = 0;
         for (int it = k_lo; it < k_hi; ++it) {
-          tc::mbar_wait(&full_bar[stage], phase);
+          tc::mbar_wait(full0 + stage * 8, phase);
           tc::tc_fence_after();
-          const uint32_t sA = tc::smem_u32(smem + stage * C::STAGE_BYTES);
-          const uint32_t sB = sA + A_BYTES;
+          const uint64_t ad = adesc0 + (uint64_t)(stage * (C::STAGE_BYTES >> 4));
+          const uint64_t bd = bdesc0 + (uint64_t)(stage * (C::STAGE_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t adesc = A_MN ? tc::make_smem_desc(sA + k * 2048, 8192, 1024)
-                                        : tc::make_smem_desc(sA + k * 32, 16, 1024);
-            const uint64_t bdesc = B_MN ? tc::make_smem_desc(sB + k * 2048, 8192, 1024)
-                                        : tc::make_smem_desc(sB + k * 32, 16, 1024);
-            if (CG == 2) tc::umma_bf16_pair(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
-            else tc::umma_bf16(d_tmem, adesc, bdesc, idesc, (it > k_lo || k > 0) ? 1u : 0u);
+            if (CG == 2) tc::umma_bf16_pair(d_tmem, ad + k * A_KADV, bd + k * B_KADV, idesc, accumulate);
+            else tc::umma_bf16(d_tmem, ad + k * A_KADV, bd + k * B_KADV, idesc, accumulate);
+            accumulate = 1;
           }
           // frees the smem slot (in both CTAs of a pair) once these MMAs retire
-          if (CG == 2) tc::umma_commit_pair(&empty_bar[stage]); else tc::umma_commit(&empty_bar[stage]);
+          tc::umma_commit_u32<CG>(empty0 + stage * 8);
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
         }
         // accumulator complete -> epilogue warps (of both CTAs)
-        if (CG == 2) tc::umma_commit_pair(&tfull_bar[acc]); else tc::umma_commit(&tfull_bar[acc]);
+        tc::umma_commit_u32<CG>(tfull0 + acc * 8);
         if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
       }
     }
+    __syncwarp();
   } else {
     // ===================================================================== epilogue (warps 2..5)
     // TMEM -> registers (one row per thread) -> per-warp smem staging (XOR-swizzled 16-byte pieces) ->

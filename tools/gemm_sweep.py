@@ -25,7 +25,10 @@ def time_it(fn, iters=10):
 
 def main():
     print("M\tN\tK\ta_mn\tb_mn\tus\tTFLOP/s")
-    for M, N, K in ((4096, 4096, 4096), (8192, 8192, 2048), (256, 2304, 50176), (2048, 2048, 12544), (16384, 256, 2304)):
+    shapes = ((4096, 4096, 4096), (8192, 8192, 2048), (256, 2304, 50176), (2048, 2048, 12544), (16384, 256, 2304))
+    if len(sys.argv) > 1 and sys.argv[1] == "conv":  # GEMMs with the shapes of ResNet convolutions (tiled TMA instead of im2col TMA)
+        shapes = ((50176, 512, 1024), (802816, 64, 576), (200704, 128, 1152), (50176, 256, 2304), (12544, 512, 4608))
+    for M, N, K in shapes:
         for a_mn, b_mn in ((0, 0), (0, 1), (1, 1)):
             a = torch.randn((K, M) if a_mn else (M, K), device="cuda").to(torch.bfloat16)
             b = torch.randn((K, N) if b_mn else (N, K), device="cuda").to(torch.bfloat16)
