@@ -24,7 +24,8 @@ namespace {
 constexpr int BM = 128;       // UMMA M (cta_group::1)
 constexpr int BK = 64;        // 64 bf16 = one 128-byte swizzle row
 constexpr int A_BYTES = BM * BK * 2;
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;        // TMA producer warp, MMA warp, 2 groups of 4 epilogue warps
+constexpr int NUM_THREADS_NARROW = 192; // ... or 1 group: the launch decides (see launch_inst2)
 constexpr int MAX_TAPS = 128;
 
 enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
@@ -58,7 +59,7 @@ struct TcParams {
   int tma_store;        // epilogue writes through the third tensor map (dense row mapping only)
   int reduce_add;       // TMA stores add into D instead of overwriting it (gradient accumulation)
   float* stat_partials; // STATS: per-epilogue-warp column sums / sums of squares [n_nblk][stat_rows][2][BN]
-  int stat_rows;        // = (gridDim.x / n_nblk) * 4
+  int stat_rows;        // = (gridDim.x / n_nblk) * 8
   int force_grid;       // launch exactly this many CTAs (STATS needs gridDim.x % n_nblk == 0)
   int cg;               // host only: 2 = launch as CTA pairs (cta_group::2), else single CTAs
   TapDesc taps[MAX_TAPS];
@@ -79,7 +80,7 @@ struct Cfg {
   static constexpr int STAGES = (BUDGET / STAGE_BYTES) > 8 ? 8 : (BUDGET / STAGE_BYTES);
   static constexpr int ACC_STRIDE = BN == 192 ? 256 : BN;  // TMEM columns between the two accumulators
   static constexpr int TMEM_COLS = 2 * ACC_STRIDE;         // 128 / 256 / 512: powers of two
-  static constexpr int STAGING_BYTES = 4 * 2 * 4096;       // per epilogue warp: 2 x (32 rows x 128 B)
+  static constexpr int STAGING_BYTES = 8 * 4096;           // per epilogue warp: 32 rows x 128 B
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + STAGING_BYTES + 1024 /*align*/ + 256 /*barriers*/;
 };
 
@@ -306,18 +307,23 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     }
     __syncwarp();
   } else {
-    // ===================================================================== epilogue (warps 2..5)
+    // ===================================================================== epilogue (warps 2..9)
+    // One or two groups of four warps (blockDim.x = 192 or 320).  With two, group g drains every other tile of
+    // this CTA, so the epilogues of two consecutive tiles overlap (memory-bound layers spend longer here than in
+    // their MMAs); the side-stream weight-gradient launches use one group to stay small next to other kernels.
     // TMEM -> registers (one row per thread) -> per-warp smem staging (XOR-swizzled 16-byte pieces) ->
-    // coalesced 128-bit global stores: each store instruction writes 4 rows x 128 contiguous bytes.
-    const int q = warp & 3;  // TMEM lane quarter this warp may read
-    uint8_t* stage_w = staging + q * 8192;  // two 4 KB buffers
-    int sbuf = 0;
+    // TMA store, or coalesced 128-bit global stores: each store instruction writes 4 rows x 128 contiguous bytes.
+    const int q = warp & 3;          // TMEM lane quarter this warp may read
+    const int grp = (warp - 2) >> 2; // accumulator buffer this warp's group owns
+    uint8_t* stage_w = staging + (grp * 4 + q) * 4096;
     float st[STATS ? BN / 64 : 1][4];       // STATS: {sum, sum} {sumsq, sumsq} of columns 2*lane, 2*lane+1 per chunk
 #pragma unroll
     for (int c = 0; c < (STATS ? BN / 64 : 1); ++c) st[c][0] = st[c][1] = st[c][2] = st[c][3] = 0.f;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+    const int ngrp = blockDim.x >= NUM_THREADS ? 2 : 1;
+    int ti = grp;   // index of the tile in this CTA's sequence: accumulator buffer ti & 1, barrier phase (ti >> 1) & 1
+    for (int tile = cluster_id + grp * num_clusters; tile < num_tiles; tile += ngrp * num_clusters, ti += ngrp) {
+      const int acc = ti & 1;
+      const uint32_t acc_phase = (uint32_t)(ti >> 1) & 1u;
       int t = tile;
       const int nblk = t % p.n_nblk; t /= p.n_nblk;
       const int mblk = (t % n_pm) * CG + cta_rank;
@@ -347,12 +353,10 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       // the chunk inside the row, valid16 = number of 16-byte pieces of the chunk that are inside D
       // TMA-store variant: the swizzled staging buffer is exactly the SWIZZLE_128B box the output tensor map
       // expects; one lane hands it to the TMA engine, which also clips rows/columns outside D.
-      const uint8_t* last_buf = stage_w;
       auto flush_tma = [&](const uint4* v, int col0, int row0) {
-        if (lane == 0) tc::tma_store_wait_read<1>();  // the store issued two chunks ago has drained its buffer
+        if (lane == 0) tc::tma_store_wait_read<0>();  // this warp's previous store has drained the buffer
         __syncwarp();
-        uint8_t* buf = stage_w + sbuf * 4096;
-        last_buf = buf;
+        uint8_t* buf = stage_w;
         uint4* srow = reinterpret_cast<uint4*>(buf + lane * 128);
 #pragma unroll
         for (int j = 0; j < 8; ++j) srow[j ^ (lane & 7)] = v[j];
@@ -364,7 +368,6 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           else tc::tma_store_2d(&tmD, buf, col0, row0);
           tc::tma_store_commit();
         }
-        sbuf ^= 1;
       };
       auto flush = [&](const uint4* v, int chunk_byte0, int valid16) {
         uint4* srow = reinterpret_cast<uint4*>(stage_w + lane * 128);
@@ -448,7 +451,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll 8
             for (int rr = 0; rr < 32; ++rr) {
               const uint32_t wv = *reinterpret_cast<const uint32_t*>(
-                  last_buf + rr * 128 + ((((lane >> 2) ^ (rr & 7)) << 4) | ((lane & 3) << 2)));
+                  stage_w + rr * 128 + ((((lane >> 2) ^ (rr & 7)) << 4) | ((lane & 3) << 2)));
               const float2 f = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wv));
               a0 += f.x; a1 += f.y;
               q0 = fmaf(f.x, f.x, q0); q1 = fmaf(f.y, f.y, q1);
@@ -471,13 +474,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         if (CG == 2 && cta_rank != 0) tc::mbar_arrive_remote(&tempty_bar[acc], 0);
         else tc::mbar_arrive(&tempty_bar[acc]);
       }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1u; }
     }
     if (p.tma_store && lane == 0) tc::tma_store_wait<0>();
     if constexpr (STATS) {
       // the number of clusters is a multiple of n_nblk: every tile of this CTA has the same n-block
       const int nb = cluster_id % p.n_nblk;
-      const int prow = ((cluster_id / p.n_nblk) * CG + cta_rank) * 4 + q;
+      const int prow = ((cluster_id / p.n_nblk) * CG + cta_rank) * 8 + grp * 4 + q;
       float* base = p.stat_partials + ((long long)(nb * p.stat_rows + prow) * 2) * BN;
 #pragma unroll
       for (int c = 0; c < BN / 64; ++c) {
@@ -648,12 +650,12 @@ int pick_cg(int BN, int n_mblk, int k_iters) {
 }
 
 // STATS launches: every CTA (pair) keeps one n-block for all of its tiles, so the number of CTAs (pairs) is a
-// multiple of n_nblk.  Partial-sum rows: 4 per CTA.
+// multiple of n_nblk.  Partial-sum rows: one per epilogue warp, 8 per CTA.
 void plan_stats_grid(TcParams* p) {
   const int cg = p->cg == 2 ? 2 : 1;
   const int units = rnn_num_sms() / cg;
   p->force_grid = (units / p->n_nblk) * p->n_nblk * cg;
-  p->stat_rows = (p->force_grid / p->n_nblk) * 4;
+  p->stat_rows = (p->force_grid / p->n_nblk) * 8;
 }
 
 template <int BN, int KIND, bool A_MN, bool B_MN, bool FUSED, bool STATS = false, int CG = 1>
@@ -675,13 +677,15 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   const int tiles = ceil_div_i(p.n_mblk, CG) * p.n_nblk * p.splits;
   int grid = (tiles < units ? tiles : units) * CG;
   if (p.force_grid > 0) grid = p.force_grid;
+  // weight-gradient kernels run on a side stream next to other kernels: one epilogue group keeps them small
+  const int threads = (KIND == KIND_WGRAD && !STATS) ? NUM_THREADS_NARROW : NUM_THREADS;
   if (CG == 1) {
-    kern<<<grid, NUM_THREADS, smem, stream>>>(ta, tb, td, p);
+    kern<<<grid, threads, smem, stream>>>(ta, tb, td, p);
   } else {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
     cfg.gridDim = dim3(grid);
-    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.blockDim = dim3(threads);
     cfg.dynamicSmemBytes = smem;
     cfg.stream = stream;
     cudaLaunchAttribute attr;
@@ -954,7 +958,7 @@ size_t rnn_conv2d_fprop_bn_stats_workspace(const rnn_conv_desc* d) {
   const int sms = rnn_num_sms();
   if (n_nblk > sms) return 0;
   const int grid = (sms / n_nblk) * n_nblk;
-  return (size_t)n_nblk * ((grid / n_nblk) * 4) * 2 * BN * sizeof(float);
+  return (size_t)n_nblk * ((grid / n_nblk) * 8) * 2 * BN * sizeof(float);
 }
 
 int rnn_conv2d_fprop_bn_stats_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* gamma,
