@@ -293,6 +293,11 @@ def run_gpu(args) -> None:
                     "sample": "1 ResNet-50 fp32 training step of 8 images (numpy oracle, multi-threaded BLAS)"}
 
     if rank == 0:
+        # DRAM bytes per tc_kernel launch: from the committed ncu pass over one step (tools/step_profile.py)
+        try:
+            traffic = json.loads((ROOT / "profiles" / "r01_traffic.json").read_text())
+        except (OSError, ValueError):
+            traffic = {}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
             "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -307,7 +312,9 @@ def run_gpu(args) -> None:
             "clocks": clk,
             "roofline": {"bound": "tensor", "kernel": "tc_kernel (tcgen05 implicit-GEMM conv fprop/dgrad/wgrad + Linear GEMM)",
                          "achieved": tc_tflops, "peak": peak_tf, "unit": "TFLOP/s", "frac": tc_tflops / peak_tf,
-                         "peak_source": f"{peaks['source']} bf16_tflops_sustained", "traffic": None,
+                         "peak_source": f"{peaks['source']} bf16_tflops_sustained",
+                         "traffic": traffic.get("tc_kernel_dram_bytes_per_launch"),
+                         "traffic_source": traffic.get("source", "no ncu capture committed"),
                          "frac_of_nominal_2250": tc_tflops / 2250.0,
                          "launches_per_step": tc_calls / args.steps, "share_of_step": tc_ms / prof_ms,
                          "timed_in": "eager pass of the same K steps (graph replay has no launch boundaries)"
