@@ -90,7 +90,8 @@ def load(path: os.PathLike | None = None):
     global _lib
     if _lib is not None:
         return _lib
-    p = Path(path) if path else LIB_PATH
+    # RNN_B200_LIB: load another build of the same ABI (A/B timing of two builds on one box)
+    p = Path(path) if path else Path(os.environ.get("RNN_B200_LIB") or LIB_PATH)
     if not p.exists():
         raise RnnError(
             f"{p} not found: build it with `python -m replicann_b200.build` (nvcc, sm_100a). "

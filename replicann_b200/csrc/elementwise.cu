@@ -37,28 +37,54 @@ __global__ void nchw_f32_to_nhwc_bf16_kernel(const float* __restrict__ x, bf16* 
   }
 }
 
-// Same conversion into a spatially zero-padded buffer [N, Hp, Wp, Cp]: block (hp, n) writes one padded row;
-// border rows/columns and padded channels are written as zeros, so no separate memset is needed.
-__global__ void nchw_f32_to_nhwc_bf16_padded_kernel(const float* __restrict__ x, bf16* __restrict__ y, int C, int H,
-                                                    int W, int Cp, int pad_h, int pad_w, int Hp, int Wp) {
+// Same conversion into a spatially zero-padded buffer [N, Hp, Wp, Cp]: block (hp group, n) writes ROWS_PER_BLOCK
+// padded rows; border rows/columns and padded channels are written as zeros, so no separate memset is needed.
+// Cp == 8 (the packed-pixel first layer): one thread builds one whole pixel and stores it as 16 bytes.
+constexpr int PAD_ROWS_PER_BLOCK = 4;
+__global__ void __launch_bounds__(256)
+nchw_f32_to_nhwc_bf16_padded_kernel(const float* __restrict__ x, bf16* __restrict__ y, int C, int H, int W, int Cp,
+                                    int pad_h, int pad_w, int Hp, int Wp) {
   extern __shared__ float tile[];  // [C][W+1]
-  const int n = blockIdx.y, hp = blockIdx.x;
-  const int h = hp - pad_h;
-  const bool inside = h >= 0 && h < H;
-  if (inside) {
-    const float* src = x + ((long long)n * C * H + h) * W;
-    for (int i = threadIdx.x; i < C * W; i += blockDim.x) {
-      const int c = i / W, w = i - c * W;
-      tile[c * (W + 1) + w] = src[(long long)c * H * W + w];
+  const int n = blockIdx.y;
+  for (int hp = blockIdx.x * PAD_ROWS_PER_BLOCK; hp < min((int)(blockIdx.x + 1) * PAD_ROWS_PER_BLOCK, Hp); ++hp) {
+    const int h = hp - pad_h;
+    const bool inside = h >= 0 && h < H;
+    __syncthreads();   // the previous row's readers are done with the tile
+    if (inside) {
+      const float* src = x + ((long long)n * C * H + h) * W;
+      if ((W & 3) == 0) {   // rows are 16-byte aligned: 128-bit loads
+        const int w4 = W >> 2;
+        for (int i = threadIdx.x; i < C * w4; i += blockDim.x) {
+          const int c = i / w4, j = i - c * w4;
+          const float4 v = *reinterpret_cast<const float4*>(src + (long long)c * H * W + 4 * j);
+          float* t = tile + c * (W + 1) + 4 * j;
+          t[0] = v.x; t[1] = v.y; t[2] = v.z; t[3] = v.w;
+        }
+      } else {
+        for (int i = threadIdx.x; i < C * W; i += blockDim.x) {
+          const int c = i / W, w = i - c * W;
+          tile[c * (W + 1) + w] = src[(long long)c * H * W + w];
+        }
+      }
     }
-  }
-  __syncthreads();
-  bf16* dst = y + ((long long)n * Hp + hp) * Wp * Cp;
-  for (int i = threadIdx.x; i < Wp * Cp; i += blockDim.x) {
-    const int wp = i / Cp, c = i - wp * Cp;
-    const int w = wp - pad_w;
-    const bool ok = inside && w >= 0 && w < W && c < C;
-    dst[i] = __float2bfloat16(ok ? tile[c * (W + 1) + w] : 0.f);
+    __syncthreads();
+    bf16* dst = y + ((long long)n * Hp + hp) * Wp * Cp;
+    if (Cp == 8) {
+      for (int wp = threadIdx.x; wp < Wp; wp += blockDim.x) {
+        const int w = wp - pad_w;
+        float v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[c] = (inside && w >= 0 && w < W && c < C) ? tile[c * (W + 1) + w] : 0.f;
+        *reinterpret_cast<uint4*>(dst + wp * 8) = pack8(v);
+      }
+    } else {
+      for (int i = threadIdx.x; i < Wp * Cp; i += blockDim.x) {
+        const int wp = i / Cp, c = i - wp * Cp;
+        const int w = wp - pad_w;
+        const bool ok = inside && w >= 0 && w < W && c < C;
+        dst[i] = __float2bfloat16(ok ? tile[c * (W + 1) + w] : 0.f);
+      }
+    }
   }
 }
 
@@ -229,7 +255,7 @@ int rnn_nchw_f32_to_nhwc_bf16_padded(const float* x, void* y, int N, int C, int 
   RNN_REQUIRE(pad_h >= 0 && pad_w >= 0 && Hp >= H + pad_h && Wp >= W + pad_w, RNN_ERR_SHAPE);
   const size_t smem = (size_t)C * (W + 1) * sizeof(float);
   RNN_REQUIRE(smem <= 48 * 1024, RNN_ERR_SHAPE);
-  nchw_f32_to_nhwc_bf16_padded_kernel<<<dim3(Hp, N), 256, smem, stream>>>(x, reinterpret_cast<bf16*>(y), C, H, W, Cpad,
+  nchw_f32_to_nhwc_bf16_padded_kernel<<<dim3(ceil_div_i(Hp, PAD_ROWS_PER_BLOCK), N), 256, smem, stream>>>(x, reinterpret_cast<bf16*>(y), C, H, W, Cpad,
                                                                           pad_h, pad_w, Hp, Wp);
   RNN_CHECK_LAUNCH();
   return RNN_OK;

@@ -77,89 +77,89 @@ template <> struct WIdx<8> {
   }
 };
 
+// Max pooling runs one grid row per output (fwd) / input (bwd) image row: blockIdx.y = row, blockIdx.z = image,
+// so a thread decodes only (column, channel group) -- the flat-index version spent ~250 instructions per 16 bytes
+// on integer divisions and was instruction-bound at 1 TB/s.
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx,
-                   unsigned char* __restrict__ widx, PoolGeom g) {
+                   unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift) {
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
-  const long long total = (long long)g.N * g.P * g.Q * cgs;
-  const bool small = total < (1ll << 31);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    int n, p, q, cg;
-    if (small) decode4<unsigned>(i, cgs, g.Q, g.P, n, p, q, cg);
-    else decode4<long long>(i, cgs, g.Q, g.P, n, p, q, cg);
-    float best[VW];
-    int bl[VW];   // argmax as the position inside the (unclipped) R x S window
-    const int h0 = p * g.sh - g.ph, w0 = q * g.sw - g.pw;
-    const int hs = h0 < 0 ? 0 : h0, ws = w0 < 0 ? 0 : w0;
-    const int he = min(h0 + g.R, g.H), we = min(w0 + g.S, g.W);
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= g.Q * cgs) return;
+  const int q = cgs_shift >= 0 ? (e >> cgs_shift) : (int)((unsigned)e / (unsigned)cgs);
+  const int cg = e - q * cgs;
+  const int p = blockIdx.y, n = blockIdx.z;
+  float best[VW];
+  int bl[VW];   // argmax as the position inside the (unclipped) R x S window
+  const int h0 = p * g.sh - g.ph, w0 = q * g.sw - g.pw;
+  const int hs = h0 < 0 ? 0 : h0, ws = w0 < 0 ? 0 : w0;
+  const int he = min(h0 + g.R, g.H), we = min(w0 + g.S, g.W);
 #pragma unroll
-    for (int e = 0; e < VW; ++e) { best[e] = -INFINITY; bl[e] = (hs - h0) * g.S + (ws - w0); }
-    for (int h = hs; h < he; ++h)
-      for (int w = ws; w < we; ++w) {
-        float v[VW];
-        PV<T, VEC>::load(x + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, v);
-        const int local = (h - h0) * g.S + (w - w0);
+  for (int e2 = 0; e2 < VW; ++e2) { best[e2] = -INFINITY; bl[e2] = (hs - h0) * g.S + (ws - w0); }
+  const T* xn = x + (long long)n * g.H * g.W * g.C + cg * VW;
+  for (int h = hs; h < he; ++h)
+    for (int w = ws; w < we; ++w) {
+      float v[VW];
+      PV<T, VEC>::load(xn + ((long long)h * g.W + w) * g.C, v);
+      const int local = (h - h0) * g.S + (w - w0);
 #pragma unroll
-        for (int e = 0; e < VW; ++e)
-          if (v[e] > best[e] || v[e] != v[e]) { best[e] = v[e]; bl[e] = local; }
-      }
-    const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
-    PV<T, VEC>::store(y + o, best);
-    if (idx) {  // torch's flat index h * W + w inside the input plane
-#pragma unroll
-      for (int e = 0; e < VW; ++e) {
-        const int lh = bl[e] / g.S, lw = bl[e] - lh * g.S;
-        idx[o + e] = (h0 + lh) * g.W + (w0 + lw);
-      }
+      for (int e2 = 0; e2 < VW; ++e2)
+        if (v[e2] > best[e2] || v[e2] != v[e2]) { best[e2] = v[e2]; bl[e2] = local; }
     }
-    if (widx) WIdx<VW>::store(widx + o, bl);  // 1 byte instead of 4 for the backward pass
+  const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
+  PV<T, VEC>::store(y + o, best);
+  if (idx) {  // torch's flat index h * W + w inside the input plane
+#pragma unroll
+    for (int e2 = 0; e2 < VW; ++e2) {
+      const int lh = bl[e2] / g.S, lw = bl[e2] - lh * g.S;
+      idx[o + e2] = (h0 + lh) * g.W + (w0 + lw);
+    }
   }
+  if (widx) WIdx<VW>::store(widx + o, bl);  // 1 byte instead of 4 for the backward pass
 }
 
 // Gather form of the backward pass: every input element sums the dy of the windows whose argmax it is.
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const unsigned char* __restrict__ widx,
-                   T* __restrict__ dx, PoolGeom g) {
+                   T* __restrict__ dx, PoolGeom g, int cgs_shift) {
   constexpr int VW = PV<T, VEC>::W;
   const int cgs = g.C / VW;
-  const long long total = (long long)g.N * g.H * g.W * cgs;
-  const bool small = total < (1ll << 31);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    int n, h, w, cg;
-    if (small) decode4<unsigned>(i, cgs, g.W, g.H, n, h, w, cg);
-    else decode4<long long>(i, cgs, g.W, g.H, n, h, w, cg);
-    const int me = h * g.W + w;
-    float acc[VW];
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= g.W * cgs) return;
+  const int w = cgs_shift >= 0 ? (e >> cgs_shift) : (int)((unsigned)e / (unsigned)cgs);
+  const int cg = e - w * cgs;
+  const int h = blockIdx.y, n = blockIdx.z;
+  const int me = h * g.W + w;
+  float acc[VW];
 #pragma unroll
-    for (int e = 0; e < VW; ++e) acc[e] = 0.f;
-    // windows p with p*sh - ph <= h < p*sh - ph + R
-    int p_lo = (h + g.ph - g.R + g.sh) / g.sh; if (h + g.ph - g.R + 1 <= 0) p_lo = 0;
-    int p_hi = (h + g.ph) / g.sh; if (p_hi > g.P - 1) p_hi = g.P - 1;
-    int q_lo = (w + g.pw - g.S + g.sw) / g.sw; if (w + g.pw - g.S + 1 <= 0) q_lo = 0;
-    int q_hi = (w + g.pw) / g.sw; if (q_hi > g.Q - 1) q_hi = g.Q - 1;
-    for (int p = p_lo; p <= p_hi; ++p)
-      for (int q = q_lo; q <= q_hi; ++q) {
-        const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
-        float d[VW];
-        PV<T, VEC>::load(dy + o, d);
-        if (widx) {
-          const int local = (h - (p * g.sh - g.ph)) * g.S + (w - (q * g.sw - g.pw));
-          int l[VW];
-          WIdx<VW>::load(widx + o, l);
+  for (int e2 = 0; e2 < VW; ++e2) acc[e2] = 0.f;
+  // windows p with p*sh - ph <= h < p*sh - ph + R (the row bounds are the same for the whole block)
+  int p_lo = (h + g.ph - g.R + g.sh) / g.sh; if (h + g.ph - g.R + 1 <= 0) p_lo = 0;
+  int p_hi = (h + g.ph) / g.sh; if (p_hi > g.P - 1) p_hi = g.P - 1;
+  int q_lo = (w + g.pw - g.S + g.sw) / g.sw; if (w + g.pw - g.S + 1 <= 0) q_lo = 0;
+  int q_hi = (w + g.pw) / g.sw; if (q_hi > g.Q - 1) q_hi = g.Q - 1;
+  for (int p = p_lo; p <= p_hi; ++p)
+    for (int q = q_lo; q <= q_hi; ++q) {
+      const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
+      float d[VW];
+      PV<T, VEC>::load(dy + o, d);
+      if (widx) {
+        const int local = (h - (p * g.sh - g.ph)) * g.S + (w - (q * g.sw - g.pw));
+        int l[VW];
+        WIdx<VW>::load(widx + o, l);
 #pragma unroll
-          for (int e = 0; e < VW; ++e)
-            if (l[e] == local) acc[e] += d[e];
-        } else {
+        for (int e2 = 0; e2 < VW; ++e2)
+          if (l[e2] == local) acc[e2] += d[e2];
+      } else {
 #pragma unroll
-          for (int e = 0; e < VW; ++e)
-            if (idx[o + e] == me) acc[e] += d[e];
-        }
+        for (int e2 = 0; e2 < VW; ++e2)
+          if (idx[o + e2] == me) acc[e2] += d[e2];
       }
-    PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
-  }
+    }
+  PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
 }
 
 // count_include_pad = True, ceil_mode = False (torch defaults): divisor is always R*S.
@@ -281,6 +281,14 @@ global_avgpool_bwd_kernel(const T* __restrict__ dy, T* __restrict__ dx, int HW, 
   }
 }
 
+// log2(v) when v is a power of two, else -1 (the kernels then divide)
+int pow2_shift(int v) {
+  if (v <= 0 || (v & (v - 1)) != 0) return -1;
+  int s = 0;
+  while ((1 << s) < v) ++s;
+  return s;
+}
+
 int pgrid(long long total) {
   long long b = (total + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * 16;
@@ -310,13 +318,16 @@ int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* windo
   const bool vec = C % vw == 0;
   int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * g.P * g.Q * (vec ? C / vw : C);
+  RNN_REQUIRE(g.P <= 65535 && N <= 65535, RNN_ERR_SHAPE);
+  const int cgs = vec ? C / vw : C;
+  const int sh_ = pow2_shift(cgs);
+  const dim3 grid(ceil_div_i((long long)g.Q * cgs, 256), g.P, N);
   if (is_f32) {
-    if (vec) maxpool_fwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g);
-    else maxpool_fwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g);
+    if (vec) maxpool_fwd_kernel<float, true><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
+    else maxpool_fwd_kernel<float, false><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
   } else {
-    if (vec) maxpool_fwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g);
-    else maxpool_fwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g);
+    if (vec) maxpool_fwd_kernel<bf16, true><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
+    else maxpool_fwd_kernel<bf16, false><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
@@ -329,13 +340,16 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
   const bool vec = C % vw == 0;
   int rc = make_geom(&g, N, H, W, C, R, S, sh, sw, ph, pw, vw);
   if (rc != RNN_OK) return rc;
-  const long long total = (long long)N * H * W * (vec ? C / vw : C);
+  RNN_REQUIRE(H <= 65535 && N <= 65535, RNN_ERR_SHAPE);
+  const int cgs = vec ? C / vw : C;
+  const int sh_ = pow2_shift(cgs);
+  const dim3 grid(ceil_div_i((long long)W * cgs, 256), H, N);
   if (is_f32) {
-    if (vec) maxpool_bwd_kernel<float, true><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g);
-    else maxpool_bwd_kernel<float, false><<<pgrid(total), 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g);
+    if (vec) maxpool_bwd_kernel<float, true><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
+    else maxpool_bwd_kernel<float, false><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
   } else {
-    if (vec) maxpool_bwd_kernel<bf16, true><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g);
-    else maxpool_bwd_kernel<bf16, false><<<pgrid(total), 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g);
+    if (vec) maxpool_bwd_kernel<bf16, true><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
+    else maxpool_bwd_kernel<bf16, false><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
