@@ -212,6 +212,24 @@ int rnn_softmax_ce(const void* logits, const long long* target, long long rows, 
 /* torch.argmax(x, dim=-1): first maximum wins. */
 int rnn_argmax(const void* x, long long* out, long long rows, int cols, int is_f32, cudaStream_t stream);
 
+/* ---- batched GEMM (attention contractions on the tensor cores) -------------------------------------- */
+/* D_z = A_z . B_z^T, bf16 in, fp32 accumulate, for z = b * heads + h.  No counterpart in the reference: it is the
+ * two torch.bmm-shaped `@` products of _AttentionHead._attention (nn/attention.py:37,47) and their autograd, for
+ * all heads of a multi-head module at once.  Operand X in {a, b, d} is a 3-D tensor of row-major slabs
+ * (x_ld elements between rows, x_bstride between slabs).  x_per_head = 0: problem z owns slab z.
+ * x_per_head = 1: the heads of batch b share slab b and head h's columns start at h * x_hoff -- the layout of a
+ * packed projection [B][T][H*hs] (x_hoff = hs; hs and the extents along a shared row must be multiples of 64).
+ * a_mn / b_mn: the operand is stored [K][M] / [K][N] (transposed use of the same buffer, no copy).
+ * out_f32: D is fp32, one dense [M][N] slab per problem. */
+typedef struct {
+  int M, N, K, batches, heads;
+  int a_mn, b_mn, out_f32;
+  long long a_ld, a_bstride; int a_per_head, a_hoff;
+  long long b_ld, b_bstride; int b_per_head, b_hoff;
+  long long d_ld, d_bstride; int d_per_head, d_hoff;
+} rnn_bgemm_desc;
+int rnn_gemm_batched_bf16(const rnn_bgemm_desc* d, const void* A, const void* B, void* D, cudaStream_t stream);
+
 /* ---- fused attention ------------------------------------------------------------------------------- */
 /* All heads of one multi-head module in one launch.  q/k/v/z/dz are addressed as
  * base + b*bs + row*rs + head*hs + d (elements): the packed projection output and the reference's
@@ -234,6 +252,21 @@ int rnn_attention_fwd(const rnn_attn_desc* d, const void* q, const void* k, cons
 int rnn_attention_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
                       const void* z, const void* dz, const float* lse, float* delta, void* dq, void* dk, void* dv,
                       int is_f32, cudaStream_t stream);
+
+/* Tensor-core form of the same attention (bf16; head size a multiple of 64, T and Tk multiples of 8, strides
+ * multiples of 8 elements -- rnn_attention_tc_supported() says whether a descriptor qualifies).  The contractions
+ * (nn/attention.py:37,47 and their autograd) run as batched tcgen05 GEMMs over all heads, the softmax / mask /
+ * dropout step (:38-46) as one row-wise kernel in between.  `saved` (rnn_attention_tc_saved_bytes) holds the
+ * probabilities from forward to backward; `ws` (rnn_attention_tc_workspace) is scratch for either direction.
+ * dq / dk / dv use the strides of q / k / v. */
+int rnn_attention_tc_supported(const rnn_attn_desc* d);
+size_t rnn_attention_tc_saved_bytes(const rnn_attn_desc* d);
+size_t rnn_attention_tc_workspace(const rnn_attn_desc* d);
+int rnn_attention_tc_fwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                         void* z, void* saved, void* ws, size_t ws_bytes, cudaStream_t stream);
+int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* saved,
+                         const void* dz, void* dq, void* dk, void* dv, void* ws, size_t ws_bytes,
+                         cudaStream_t stream);
 
 /* ---- fused optimizers over flat buckets ---------------------------------------------------------- */
 /* torch.optim.SGD (momentum, dampening, nesterov, weight_decay) on an fp32 master copy. */

@@ -38,11 +38,12 @@ constexpr int KC = 64;     // keys (or queries, in the dk/dv kernel) per shared-
 constexpr int ROWS = 16;   // rows handled per CTA (4 warps x 4)
 constexpr int MAXD = 4;    // head size <= 32 * MAXD = 128
 
-__device__ __forceinline__ uint32_t philox_first(unsigned long long seed, unsigned long long offset,
-                                                 unsigned long long idx) {
+// Philox-4x32-10: one call yields four 32-bit words.  Attention-weight element `idx` uses word (idx & 3) of the
+// block with counter (idx >> 2), so a kernel that walks four consecutive elements pays for one call.
+__device__ __forceinline__ uint4 philox4(unsigned long long seed, unsigned long long offset, unsigned long long ctr) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
-  uint32_t c0 = (uint32_t)idx, c1 = (uint32_t)(idx >> 32), c2 = (uint32_t)offset, c3 = (uint32_t)(offset >> 32);
+  uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = (uint32_t)offset, c3 = (uint32_t)(offset >> 32);
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
     const uint32_t hi0 = __umulhi(M0, c0), lo0 = M0 * c0, hi1 = __umulhi(M1, c2), lo1 = M1 * c2;
@@ -50,13 +51,19 @@ __device__ __forceinline__ uint32_t philox_first(unsigned long long seed, unsign
     c0 = n0; c1 = lo1; c2 = n2; c3 = lo0;
     k0 += W0; k1 += W1;
   }
-  return c0;
+  return make_uint4(c0, c1, c2, c3);
+}
+__device__ __forceinline__ uint32_t philox_word(unsigned long long seed, unsigned long long offset,
+                                                unsigned long long idx) {
+  const uint4 r = philox4(seed, offset, idx >> 2);
+  const int w = (int)(idx & 3);
+  return w == 0 ? r.x : w == 1 ? r.y : w == 2 ? r.z : r.w;
 }
 
 __device__ __forceinline__ float keep_scale(const AttnParams& p, int bh, int i, int j) {
   if (p.p_drop <= 0.f) return 1.f;
   const unsigned long long idx = ((unsigned long long)bh * p.T + i) * p.Tk + j;
-  const uint32_t r = philox_first(p.seed, p.offset, idx);
+  const uint32_t r = philox_word(p.seed, p.offset, idx);
   return r >= (uint32_t)(p.p_drop * 4294967296.0) ? 1.f / (1.f - p.p_drop) : 0.f;
 }
 
@@ -392,6 +399,150 @@ int set_smem(K kern, size_t bytes) {
   return RNN_OK;
 }
 
+
+// ---------------------------------------------------------------------------------------------------------------
+// Tensor-core form (bf16, head size a multiple of 64): the two contractions of the forward pass and the four of
+// the backward pass are batched tcgen05 GEMMs over all (batch, head) problems (rnn_gemm_batched_bf16, operands read
+// in place from the packed projections); the row-wise softmax / mask / dropout step between them runs here.  The
+// scores are kept in fp32 between the QK^T GEMM and the softmax; the probabilities are stored in bf16 because
+// they are tensor-core operands next.
+// ---------------------------------------------------------------------------------------------------------------
+struct SmaxParams {
+  int H, T, Tk;
+  float scale;
+  const void* mask;
+  int mask_kind;
+  long long mask_bs, mask_rs;
+  float p_drop;
+  unsigned long long seed, offset;
+};
+
+__device__ __forceinline__ float smax_score(const SmaxParams& p, float raw, int b, int i, int j) {
+  const float s = raw * p.scale;
+  if (p.mask_kind == 1) {
+    const uint8_t m = reinterpret_cast<const uint8_t*>(p.mask)[b * p.mask_bs + i * p.mask_rs + j];
+    return m ? -INFINITY : s;
+  }
+  if (p.mask_kind == 2) return s + reinterpret_cast<const float*>(p.mask)[b * p.mask_bs + i * p.mask_rs + j];
+  return s;
+}
+
+// One warp per score row: P = softmax(S * scale (+ mask)), Pd = dropout(P).  Lanes walk the row four elements at a
+// time (Tk is a multiple of 8 here): 128-bit loads of the scores, one Philox call per four probabilities, 64-bit
+// stores.  Three passes over a row of a few KB (served by L1 after the first); same Philox word per element as
+// the fused kernel (keep_scale above).
+__global__ void __launch_bounds__(128)
+attn_softmax_fwd_kernel(const float* __restrict__ S, bf16* __restrict__ P, bf16* __restrict__ Pd, long long rows,
+                        SmaxParams p) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const int bh = (int)(r / p.T), i = (int)(r - (long long)bh * p.T), b = bh / p.H;
+  const float4* srow = reinterpret_cast<const float4*>(S + r * p.Tk);
+  const int n4 = p.Tk >> 2;
+  auto score4 = [&](int j4, float* s) {
+    const float4 raw = srow[j4];
+    s[0] = smax_score(p, raw.x, b, i, 4 * j4 + 0); s[1] = smax_score(p, raw.y, b, i, 4 * j4 + 1);
+    s[2] = smax_score(p, raw.z, b, i, 4 * j4 + 2); s[3] = smax_score(p, raw.w, b, i, 4 * j4 + 3);
+  };
+  float m = -INFINITY;
+  for (int j4 = lane; j4 < n4; j4 += 32) {
+    float s[4];
+    score4(j4, s);
+    m = fmaxf(fmaxf(m, fmaxf(s[0], s[1])), fmaxf(s[2], s[3]));
+  }
+  m = warp_max(m);
+  float l = 0.f;
+  for (int j4 = lane; j4 < n4; j4 += 32) {
+    float s[4];
+    score4(j4, s);
+    l += (__expf(s[0] - m) + __expf(s[1] - m)) + (__expf(s[2] - m) + __expf(s[3] - m));
+  }
+  l = warp_sum(l);
+  const float inv = 1.f / l;
+  const float keep = 1.f / (1.f - p.p_drop);
+  const uint32_t thresh = (uint32_t)(p.p_drop * 4294967296.0);
+  const unsigned long long row_idx = ((unsigned long long)bh * p.T + i) * p.Tk;   // multiple of 4
+  for (int j4 = lane; j4 < n4; j4 += 32) {
+    float s[4], pv[4];
+    score4(j4, s);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) pv[e] = __expf(s[e] - m) * inv;
+    __nv_bfloat162 lo = __floats2bfloat162_rn(pv[0], pv[1]), hi = __floats2bfloat162_rn(pv[2], pv[3]);
+    uint2 out;
+    out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(P + r * p.Tk + 4 * j4) = out;
+    if (Pd != P) {
+      const uint4 rnd = philox4(p.seed, p.offset, (row_idx >> 2) + j4);
+      lo = __floats2bfloat162_rn(rnd.x >= thresh ? pv[0] * keep : 0.f, rnd.y >= thresh ? pv[1] * keep : 0.f);
+      hi = __floats2bfloat162_rn(rnd.z >= thresh ? pv[2] * keep : 0.f, rnd.w >= thresh ? pv[3] * keep : 0.f);
+      out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(Pd + r * p.Tk + 4 * j4) = out;
+    }
+  }
+}
+
+// dS = scale * P * (dPd * keep - delta), delta_i = sum_j dPd_ij * Pd_ij (= dz_i . z_i).  `keep` is read off the
+// stored pair: an element with P != 0 and Pd == 0 was dropped (P == 0 contributes nothing either way).
+__global__ void __launch_bounds__(128)
+attn_softmax_bwd_kernel(const bf16* __restrict__ P, const bf16* __restrict__ Pd, const float* __restrict__ dPd,
+                        bf16* __restrict__ dS, long long rows, int Tk, float scale, float p_drop) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (r >= rows) return;
+  const uint2* prow = reinterpret_cast<const uint2*>(P + r * Tk);      // four bf16 per step (Tk % 8 == 0)
+  const uint2* pdrow = reinterpret_cast<const uint2*>(Pd + r * Tk);
+  const float4* grow = reinterpret_cast<const float4*>(dPd + r * Tk);
+  const int n4 = Tk >> 2;
+  auto unpack4 = [](const uint2& u, float* f) {
+    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+  };
+  float delta = 0.f;
+  for (int j4 = lane; j4 < n4; j4 += 32) {
+    float pd[4];
+    unpack4(pdrow[j4], pd);
+    const float4 g = grow[j4];
+    delta += (g.x * pd[0] + g.y * pd[1]) + (g.z * pd[2] + g.w * pd[3]);
+  }
+  delta = warp_sum(delta);
+  const float keep = 1.f / (1.f - p_drop);
+  for (int j4 = lane; j4 < n4; j4 += 32) {
+    float pv[4], pd[4];
+    unpack4(prow[j4], pv);
+    const float4 g4 = grow[j4];
+    float g[4] = {g4.x, g4.y, g4.z, g4.w};
+    if (Pd != P) {
+      unpack4(pdrow[j4], pd);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) g[e] = pd[e] != 0.f ? g[e] * keep : 0.f;
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(scale * pv[0] * (g[0] - delta), scale * pv[1] * (g[1] - delta));
+    __nv_bfloat162 hi = __floats2bfloat162_rn(scale * pv[2] * (g[2] - delta), scale * pv[3] * (g[3] - delta));
+    uint2 out;
+    out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(dS + r * Tk + 4 * j4) = out;
+  }
+}
+
+int tc_check(const rnn_attn_desc* d) {
+  int rc = check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(d->hs % 64 == 0 && d->T % 8 == 0 && d->Tk % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->q_rs % 8 == 0 && d->k_rs % 8 == 0 && d->v_rs % 8 == 0 && d->z_rs % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->q_bs % 8 == 0 && d->k_bs % 8 == 0 && d->v_bs % 8 == 0 && d->z_bs % 8 == 0, RNN_ERR_SHAPE);
+  return RNN_OK;
+}
+
+// operand specs of the batched GEMMs
+void spec_heads(long long& ld, long long& bstride, int& per_head, int& hoff, long long rs, long long bs, int hs) {
+  ld = rs; bstride = bs; per_head = 1; hoff = hs;
+}
+void spec_slab(long long& ld, long long& bstride, int& per_head, int& hoff, int rows, int cols) {
+  ld = cols; bstride = (long long)rows * cols; per_head = 0; hoff = 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -446,4 +597,114 @@ int rnn_attention_bwd(const rnn_attn_desc* d, const void* q, const void* k, cons
   return RNN_OK;
 }
 
+
+int rnn_attention_tc_supported(const rnn_attn_desc* d) {
+  if (d == nullptr || d->hs <= 0) return 0;
+  return d->hs % 64 == 0 && d->T % 8 == 0 && d->Tk % 8 == 0 && d->q_rs % 8 == 0 && d->k_rs % 8 == 0 &&
+         d->v_rs % 8 == 0 && d->z_rs % 8 == 0 && d->q_bs % 8 == 0 && d->k_bs % 8 == 0 && d->v_bs % 8 == 0 &&
+         d->z_bs % 8 == 0;
+}
+// probabilities kept from forward to backward: P, and dropout(P) when dropout is active (both bf16 [B*H][T][Tk])
+size_t rnn_attention_tc_saved_bytes(const rnn_attn_desc* d) {
+  if (d == nullptr) return 0;
+  const size_t one = (size_t)d->B * d->H * d->T * d->Tk * sizeof(bf16);
+  return d->p_drop > 0.f ? 2 * one : one;
+}
+// scratch of either direction: fp32 scores (forward), fp32 d(probabilities) + bf16 d(scores) (backward)
+size_t rnn_attention_tc_workspace(const rnn_attn_desc* d) {
+  if (d == nullptr) return 0;
+  const size_t n = (size_t)d->B * d->H * d->T * d->Tk;
+  return n * sizeof(float) + n * sizeof(bf16);
+}
+
+int rnn_attention_tc_fwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                         void* z, void* saved, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  int rc = tc_check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE((d->mask_kind == 0) == (mask == nullptr), RNN_ERR_DTYPE);
+  RNN_REQUIRE(saved != nullptr && ws != nullptr && ws_bytes >= rnn_attention_tc_workspace(d), RNN_ERR_WORKSPACE);
+  const long long n = (long long)d->B * d->H * d->T * d->Tk;
+  float* S = reinterpret_cast<float*>(ws);
+  bf16* P = reinterpret_cast<bf16*>(saved);
+  bf16* Pd = d->p_drop > 0.f ? P + n : P;
+  rnn_bgemm_desc g;
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  // S = q k^T  (nn/attention.py:37)
+  g.M = d->T; g.N = d->Tk; g.K = d->hs; g.out_f32 = 1;
+  spec_heads(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->q_rs, d->q_bs, d->hs);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->k_rs, d->k_bs, d->hs);
+  spec_slab(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->T, d->Tk);
+  rc = rnn_gemm_batched_bf16(&g, q, k, S, stream);
+  if (rc != RNN_OK) return rc;
+  // scale, mask, softmax, dropout (:38-46)
+  SmaxParams sp;
+  sp.H = d->H; sp.T = d->T; sp.Tk = d->Tk; sp.scale = d->scale; sp.mask = mask; sp.mask_kind = d->mask_kind;
+  sp.mask_bs = d->mask_bs; sp.mask_rs = d->mask_rs; sp.p_drop = d->p_drop; sp.seed = d->seed; sp.offset = d->offset;
+  const long long rows = (long long)d->B * d->H * d->T;
+  attn_softmax_fwd_kernel<<<ceil_div_i(rows, 4), 128, 0, stream>>>(S, P, Pd, rows, sp);
+  RNN_CHECK_LAUNCH();
+  // z = w v  (:47), written straight into the concatenated-heads layout
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  g.M = d->T; g.N = d->hs; g.K = d->Tk; g.b_mn = 1;
+  spec_slab(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->T, d->Tk);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->v_rs, d->v_bs, d->hs);
+  spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->z_rs, d->z_bs, d->hs);
+  return rnn_gemm_batched_bf16(&g, Pd, v, z, stream);
+}
+
+int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* saved,
+                         const void* dz, void* dq, void* dk, void* dv, void* ws, size_t ws_bytes,
+                         cudaStream_t stream) {
+  int rc = tc_check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(d->dz_rs % 8 == 0 && d->dz_bs % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(saved != nullptr && ws != nullptr && ws_bytes >= rnn_attention_tc_workspace(d), RNN_ERR_WORKSPACE);
+  const long long n = (long long)d->B * d->H * d->T * d->Tk;
+  float* dPd = reinterpret_cast<float*>(ws);
+  bf16* dS = reinterpret_cast<bf16*>(dPd + n);
+  const bf16* P = reinterpret_cast<const bf16*>(saved);
+  const bf16* Pd = d->p_drop > 0.f ? P + n : P;
+  rnn_bgemm_desc g;
+  // d(dropout(w)) = dz v^T
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  g.M = d->T; g.N = d->Tk; g.K = d->hs; g.out_f32 = 1;
+  spec_heads(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->dz_rs, d->dz_bs, d->hs);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->v_rs, d->v_bs, d->hs);
+  spec_slab(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->T, d->Tk);
+  rc = rnn_gemm_batched_bf16(&g, dz, v, dPd, stream);
+  if (rc != RNN_OK) return rc;
+  // dv = dropout(w)^T dz
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  g.M = d->Tk; g.N = d->hs; g.K = d->T; g.a_mn = 1; g.b_mn = 1;
+  spec_slab(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->T, d->Tk);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->dz_rs, d->dz_bs, d->hs);
+  spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->v_rs, d->v_bs, d->hs);
+  rc = rnn_gemm_batched_bf16(&g, Pd, dz, dv, stream);
+  if (rc != RNN_OK) return rc;
+  // softmax / dropout / scale backward
+  const long long rows = (long long)d->B * d->H * d->T;
+  attn_softmax_bwd_kernel<<<ceil_div_i(rows, 4), 128, 0, stream>>>(P, Pd, dPd, dS, rows, d->Tk, d->scale, d->p_drop);
+  RNN_CHECK_LAUNCH();
+  // dq = ds k
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  g.M = d->T; g.N = d->hs; g.K = d->Tk; g.b_mn = 1;
+  spec_slab(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->T, d->Tk);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->k_rs, d->k_bs, d->hs);
+  spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->q_rs, d->q_bs, d->hs);
+  rc = rnn_gemm_batched_bf16(&g, dS, k, dq, stream);
+  if (rc != RNN_OK) return rc;
+  // dk = ds^T q
+  memset(&g, 0, sizeof(g));
+  g.batches = d->B; g.heads = d->H;
+  g.M = d->Tk; g.N = d->hs; g.K = d->T; g.a_mn = 1; g.b_mn = 1;
+  spec_slab(g.a_ld, g.a_bstride, g.a_per_head, g.a_hoff, d->T, d->Tk);
+  spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->q_rs, d->q_bs, d->hs);
+  spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->k_rs, d->k_bs, d->hs);
+  return rnn_gemm_batched_bf16(&g, dS, q, dk, stream);
+}
 }  // extern "C"

@@ -519,12 +519,12 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ xin, const 
 }
 
 template <typename T>
-__global__ void layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int E, T* dgamma,
-                                              T* dbeta, int accumulate) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= E) return;
-  float a = 0.f, b = 0.f;
-  for (int p = 0; p < nparts; ++p) { a += partials[(long long)p * 2 * E + c]; b += partials[(long long)p * 2 * E + E + c]; }
+__global__ void __launch_bounds__(FIN_THREADS)
+layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int E, T* dgamma, T* dbeta,
+                              int accumulate) {
+  const int c = blockIdx.x * FIN_CH + (threadIdx.x & 31);
+  float a, b;
+  if (!sum_partials_block(partials, nparts, E, c, a, b, E)) return;   // partials: [nparts][2][E]
   if (accumulate) { a += (float)dgamma[c]; b += (float)dbeta[c]; }
   dgamma[c] = (T)a;
   dbeta[c] = (T)b;
@@ -729,14 +729,14 @@ int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const 
     layernorm_bwd_kernel<float><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
                                                                mean, rstd, (float*)dx, (float*)ws, M, E);
     RNN_CHECK_LAUNCH();
-    layernorm_bwd_finalize_kernel<float><<<ceil_div_i(E, 128), 128, 0, stream>>>((const float*)ws, blocks, E,
+    layernorm_bwd_finalize_kernel<float><<<ceil_div_i(E, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, blocks, E,
                                                                                 (float*)dgamma, (float*)dbeta,
                                                                                 accumulate_grads);
   } else {
     layernorm_bwd_kernel<bf16><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
                                                               mean, rstd, (bf16*)dx, (float*)ws, M, E);
     RNN_CHECK_LAUNCH();
-    layernorm_bwd_finalize_kernel<bf16><<<ceil_div_i(E, 128), 128, 0, stream>>>((const float*)ws, blocks, E,
+    layernorm_bwd_finalize_kernel<bf16><<<ceil_div_i(E, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, blocks, E,
                                                                                (bf16*)dgamma, (bf16*)dbeta,
                                                                                accumulate_grads);
   }

@@ -28,7 +28,7 @@ constexpr int NUM_THREADS = 320;        // TMA producer warp, MMA warp, 2 groups
 constexpr int NUM_THREADS_NARROW = 192; // ... or 1 group: the launch decides (see launch_inst2)
 constexpr int MAX_TAPS = 128;
 
-enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2 };
+enum { KIND_GEMM = 0, KIND_CONV = 1, KIND_WGRAD = 2, KIND_BGEMM = 3 };
 
 struct TapDesc {
   int16_t ow, oh;  // filter-tap offsets handed to the im2col TMA
@@ -62,6 +62,14 @@ struct TcParams {
   int stat_rows;        // = (gridDim.x / n_nblk) * 8
   int force_grid;       // launch exactly this many CTAs (STATS needs gridDim.x % n_nblk == 0)
   int cg;               // host only: 2 = launch as CTA pairs (cta_group::2), else single CTAs
+  // BGEMM: `splits` independent problems z = b * bg_heads + h, each with the full K range.  Operand X lives in a
+  // 3-D tensor; its slab index is b (x_zdiv = 1: heads of a batch share rows, head h starts x_hoff * h elements
+  // into the inner dimension) or z (x_zdiv = 0).
+  int bg_heads;
+  int a_zdiv, b_zdiv, d_zdiv;
+  int a_hoff, b_hoff, d_hoff;
+  long long d_bstride;  // elements between slabs of a bf16 D
+  int d_slabs, d_inner; // extents of the bf16 D tensor map (slabs, inner elements)
   TapDesc taps[MAX_TAPS];
 };
 
@@ -157,10 +165,17 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         const int nblk = t % p.n_nblk; t /= p.n_nblk;
         const int mblk = (t % n_pm) * CG + cta_rank;
         const int split = t / n_pm;
-        const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
-        const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
+        const int k_lo = KIND == KIND_BGEMM ? 0 : (int)(((long long)p.k_iters * split) / p.splits);
+        const int k_hi = KIND == KIND_BGEMM ? p.k_iters : (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         const int m0 = mblk * BM;
         const int n0 = nblk * BN;
+        // BGEMM: slab and inner offset of this problem's operands
+        int za = 0, zb = 0, a_off = 0, b_off = 0;
+        if (KIND == KIND_BGEMM) {
+          const int bb = split / p.bg_heads, hh = split - bb * p.bg_heads;
+          za = p.a_zdiv ? bb : split; zb = p.b_zdiv ? bb : split;
+          a_off = hh * p.a_hoff; b_off = hh * p.b_hoff;
+        }
         // CONV: base pixel of this M tile
         int img0 = 0, w0 = 0, h0 = 0;
         if (KIND == KIND_CONV) {
@@ -231,6 +246,20 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
               for (int j = 0; j < NB_LOCAL; ++j) tc::tma_ld2<CG>(sB + j * 8192, &tmB, fb, n0 + (jb0 + j) * 64, kc);
             }
+          } else if (KIND == KIND_BGEMM) {
+            const int kc = it * BK;
+            if (!A_MN) {
+              tc::tma_ld3(sA, &tmA, fb, kc + a_off, m0, za);
+            } else {
+              tc::tma_ld3(sA, &tmA, fb, m0 + a_off, kc, za);
+              tc::tma_ld3(sA + 8192, &tmA, fb, m0 + 64 + a_off, kc, za);
+            }
+            if (!B_MN) {
+              tc::tma_ld3(sB, &tmB, fb, kc + b_off, n0, zb);
+            } else {
+#pragma unroll
+              for (int j = 0; j < NB_LOCAL; ++j) tc::tma_ld3(sB + j * 8192, &tmB, fb, n0 + j * 64 + b_off, kc, zb);
+            }
           } else if (KIND == KIND_CONV) {
             tc::tma_ldi<CG>(sA, &tmA, fb, cc * BK, w0, h0, img0, (uint16_t)td.ow, (uint16_t)td.oh);
             if (!B_MN) {
@@ -280,8 +309,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       uint32_t acc_phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         const int split = tile / (p.n_nblk * n_pm);
-        const int k_lo = (int)(((long long)p.k_iters * split) / p.splits);
-        const int k_hi = (int)(((long long)p.k_iters * (split + 1)) / p.splits);
+        const int k_lo = KIND == KIND_BGEMM ? 0 : (int)(((long long)p.k_iters * split) / p.splits);
+        const int k_hi = KIND == KIND_BGEMM ? p.k_iters : (int)(((long long)p.k_iters * (split + 1)) / p.splits);
         tc::mbar_wait(tempty0 + acc * 8, acc_phase ^ 1u);
         tc::tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)(acc * C::ACC_STRIDE);
@@ -365,6 +394,10 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         __syncwarp();
         if (lane == 0) {
           if (p.ws != nullptr) tc::tma_store_3d(&tmD, buf, col0, row0, split);
+          else if (KIND == KIND_BGEMM) {
+            const int bb = split / p.bg_heads, hh = split - bb * p.bg_heads;
+            tc::tma_store_3d(&tmD, buf, col0 + hh * p.d_hoff, row0, p.d_zdiv ? bb : split);
+          }
           else if (p.reduce_add) tc::tma_reduce_add_2d(&tmD, buf, col0, row0);
           else tc::tma_store_2d(&tmD, buf, col0, row0);
           tc::tma_store_commit();
@@ -580,6 +613,22 @@ int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols
   return RNN_OK;
 }
 
+// bf16 tensor [slabs][rows][inner] (row pitch ld, slab pitch bstride, elements); box = {64 inner, box_rows, 1}.
+int make_tmap_3d(CUtensorMap* m, const void* ptr, long long slabs, long long rows, long long inner, long long ld,
+                 long long bstride, int box_rows) {
+  cuuint64_t gdim[3] = {(cuuint64_t)inner, (cuuint64_t)rows, (cuuint64_t)slabs};
+  cuuint64_t gstr[2] = {(cuuint64_t)ld * 2, (cuuint64_t)bstride * 2};
+  cuuint32_t box[3] = {64u, (cuuint32_t)box_rows, 1u};
+  cuuint32_t estr[3] = {1u, 1u, 1u};
+  RNN_REQUIRE((ld * 2) % 16 == 0 && (bstride * 2) % 16 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15u) == 0, RNN_ERR_ALIGN);
+  CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim, gstr, box,
+                              estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  RNN_REQUIRE(r == CUDA_SUCCESS, RNN_ERR_TENSORMAP);
+  return RNN_OK;
+}
+
 // NHWC bf16 activation tensor seen as (C, W, H, N) for im2col-mode TMA.  Strides are explicit so
 // that callers may describe virtual (overlapping) views.
 int make_tmap_im2col(CUtensorMap* m, const void* ptr, int C, int W, int H, int N, long long str_w,
@@ -617,6 +666,14 @@ int make_tmap_out(CUtensorMap* m, TcParams* p) {
     cuuint64_t gstr[2] = {(cuuint64_t)p->ldw * 4, (cuuint64_t)p->ldw * 4 * (cuuint64_t)p->M};
     cuuint32_t box[3] = {32u, 32u, 1u};
     r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, p->ws, gdim, gstr, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else if (p->bg_heads > 0) {
+    if ((p->ldd * 2) % 16 != 0 || (p->d_bstride * 2) % 16 != 0 || (reinterpret_cast<uintptr_t>(p->D) & 15u)) return RNN_OK;
+    cuuint64_t gdim[3] = {(cuuint64_t)p->d_inner, (cuuint64_t)p->M, (cuuint64_t)p->d_slabs};
+    cuuint64_t gstr[2] = {(cuuint64_t)p->ldd * 2, (cuuint64_t)p->d_bstride * 2};
+    cuuint32_t box[3] = {64u, 32u, 1u};
+    r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, p->D, gdim, gstr, box, estr,
                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   } else {
@@ -731,6 +788,17 @@ int launch_bn(int BN, const CUtensorMap& ta, const CUtensorMap& tb, const TcPara
   return RNN_ERR_SHAPE;
 }
 
+// batched GEMMs always launch single CTAs (their tiles have 1-8 K steps)
+template <bool A_MN, bool B_MN>
+int launch_bgemm(int BN, const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p, cudaStream_t s) {
+  switch (BN) {
+    case 64: return launch_inst2<64, KIND_BGEMM, A_MN, B_MN, false>(ta, tb, p, s);
+    case 128: return launch_inst2<128, KIND_BGEMM, A_MN, B_MN, false>(ta, tb, p, s);
+    case 256: return launch_inst2<256, KIND_BGEMM, A_MN, B_MN, false>(ta, tb, p, s);
+  }
+  return RNN_ERR_SHAPE;
+}
+
 int launch_reduce(const float* ws, int splits, long long slab, int ncols, const float* shift, int relu,
                   int accumulate, void* out, int out_f32, cudaStream_t stream) {
   RNN_REQUIRE(slab % 4 == 0 && ncols % 4 == 0, RNN_ERR_SHAPE);
@@ -821,6 +889,67 @@ WgradPlan plan_wgrad(const rnn_conv_desc* d) {
 // C ABI
 // =============================================================================================
 extern "C" {
+
+// Batched D_z = A_z . B_z^T for z = b * heads + h (see rnn_bgemm_desc in the header): the attention contractions
+// of all heads of a multi-head module in one launch, operands addressed in place inside the packed projections.
+int rnn_gemm_batched_bf16(const rnn_bgemm_desc* d, const void* A, const void* B, void* D, cudaStream_t stream) {
+  RNN_REQUIRE(d != nullptr && d->M > 0 && d->N > 0 && d->K > 0 && d->batches > 0 && d->heads > 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(!(d->a_mn && !d->b_mn), RNN_ERR_SHAPE);  // (MN,K) combination is not instantiated
+  // a head's slice of a shared row must be whole 64-wide blocks, or a tile would read / write its neighbour
+  if (d->a_per_head) RNN_REQUIRE(d->a_hoff % 64 == 0 && (d->a_mn ? d->M : d->K) % 64 == 0, RNN_ERR_SHAPE);
+  if (d->b_per_head) RNN_REQUIRE(d->b_hoff % 64 == 0 && (d->b_mn ? d->N : d->K) % 64 == 0, RNN_ERR_SHAPE);
+  if (d->d_per_head) RNN_REQUIRE(d->d_hoff % 64 == 0 && d->N % 64 == 0, RNN_ERR_SHAPE);
+  int rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  const long long nz = (long long)d->batches * d->heads;
+  RNN_REQUIRE(nz < (1 << 24), RNN_ERR_SHAPE);
+  const int BN = pick_bn(d->N);
+  CUtensorMap ta, tb;
+  {
+    const long long slabs = d->a_per_head ? d->batches : nz;
+    const long long rows = d->a_mn ? d->K : d->M;
+    const long long inner = d->a_per_head ? (long long)d->heads * d->a_hoff : (d->a_mn ? d->M : d->K);
+    rc = make_tmap_3d(&ta, A, slabs, rows, inner, d->a_ld, d->a_bstride, d->a_mn ? 64 : BM);
+    if (rc != RNN_OK) return rc;
+  }
+  {
+    const long long slabs = d->b_per_head ? d->batches : nz;
+    const long long rows = d->b_mn ? d->K : d->N;
+    const long long inner = d->b_per_head ? (long long)d->heads * d->b_hoff : (d->b_mn ? d->N : d->K);
+    rc = make_tmap_3d(&tb, B, slabs, rows, inner, d->b_ld, d->b_bstride, d->b_mn ? 64 : BN);
+    if (rc != RNN_OK) return rc;
+  }
+  TcParams p;
+  memset(&p, 0, sizeof(p));
+  p.M = d->M; p.N = d->N;
+  p.k_iters = ceil_div_i(d->K, BK);
+  p.splits = (int)nz;
+  p.n_mblk = ceil_div_i(d->M, BM);
+  p.n_nblk = ceil_div_i(d->N, BN);
+  p.cg = 1;
+  p.bg_heads = d->heads;
+  p.a_zdiv = d->a_per_head; p.b_zdiv = d->b_per_head; p.d_zdiv = d->d_per_head;
+  p.a_hoff = d->a_per_head ? d->a_hoff : 0; p.b_hoff = d->b_per_head ? d->b_hoff : 0;
+  p.d_hoff = d->d_per_head ? d->d_hoff : 0;
+  if (d->out_f32) {
+    // fp32 D is always one dense slab per problem: [z][M][N]
+    RNN_REQUIRE(!d->d_per_head && d->d_ld == d->N && d->d_bstride == (long long)d->M * d->N, RNN_ERR_SHAPE);
+    RNN_REQUIRE(d->N % 4 == 0 && (reinterpret_cast<uintptr_t>(D) & 15u) == 0, RNN_ERR_ALIGN);
+    p.ws = reinterpret_cast<float*>(D);
+    p.ldw = d->N;
+  } else {
+    p.D = D;
+    p.ldd = d->d_ld;
+    p.d_bstride = d->d_bstride;
+    p.d_slabs = (int)(d->d_per_head ? d->batches : nz);
+    p.d_inner = (int)(d->d_per_head ? (long long)d->heads * d->d_hoff : d->N);
+    RNN_REQUIRE((d->d_ld * 2) % 16 == 0 && (d->d_bstride * 2) % 16 == 0, RNN_ERR_SHAPE);
+    RNN_REQUIRE((reinterpret_cast<uintptr_t>(D) & 15u) == 0, RNN_ERR_ALIGN);
+  }
+  if (!d->a_mn && !d->b_mn) return launch_bgemm<false, false>(BN, ta, tb, p, stream);
+  if (!d->a_mn && d->b_mn) return launch_bgemm<false, true>(BN, ta, tb, p, stream);
+  return launch_bgemm<true, true>(BN, ta, tb, p, stream);
+}
 
 size_t rnn_gemm_bf16_workspace(int M, int N, int K, int out_f32, int has_epilogue) {
   const int BN = pick_bn(N);

@@ -145,6 +145,15 @@ __device__ __forceinline__ void tma_ldi(uint32_t dst, const CUtensorMap* m, uint
         : "memory");
 }
 
+// 3-D tiled load (inner, row, slab): the batched GEMMs address one problem's operand as a slab of a 3-D tensor,
+// so rows past the problem's extent are zero-filled instead of running into the next problem.
+__device__ __forceinline__ void tma_ld3(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(m)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+
 // TMA stores (shared -> global), tracked by the issuing thread's bulk async-group.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(

@@ -699,6 +699,11 @@ def _attn_desc(B, H, T, Tk, hs, q, k, v, z, dz, scale, mask, p_drop, seed, offse
     return d
 
 
+def _req_dtype(t, dtype, name):
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+
+
 def _check_qkv(t, name):
     if t.dim() != 3 or t.stride(2) != 1:
         raise ValueError(f"{name} must be [B, T, H*hs] with unit stride in the last dimension")
@@ -717,6 +722,55 @@ def attention_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, of
     check(lib.rnn_attention_fwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(lse), _is_f32(q), cur_stream()),
           "rnn_attention_fwd")
     return z, lse
+
+
+_attn_tc_enabled = os.environ.get("RNN_ATTN_TC", "1") != "0"
+
+
+def attention_tc_ok(q, k, v, n_heads, hs) -> bool:
+    """Whether the tensor-core attention pipeline takes these operands (bf16, head size % 64, T % 8, aligned strides)."""
+    if not _attn_tc_enabled or q.dtype != torch.bfloat16:
+        return False
+    B, T, _ = q.shape
+    z_rs, z_bs = n_heads * hs, T * n_heads * hs
+    return (hs % 64 == 0 and T % 8 == 0 and k.shape[1] % 8 == 0 and z_rs % 8 == 0 and z_bs % 8 == 0
+            and all(t.stride(0) % 8 == 0 and t.stride(1) % 8 == 0 and t.data_ptr() % 16 == 0 for t in (q, k, v)))
+
+
+def attention_tc_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, offset=0):
+    """Tensor-core attention forward: returns z [B,T,H*hs] and the saved probabilities (opaque uint8 buffer)."""
+    lib = _lib.load(); _cuda(q, k, v, mask)
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _check_qkv(t, n)
+        _req_dtype(t, torch.bfloat16, n)
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    z = torch.empty((B, T, n_heads * hs), dtype=q.dtype, device=q.device)
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, None, scale, mask, p_drop, seed, offset)
+    saved = torch.empty(lib.rnn_attention_tc_saved_bytes(d), dtype=torch.uint8, device=q.device)
+    nbytes = lib.rnn_attention_tc_workspace(d)
+    ws = workspace(nbytes, q.device)
+    with _span("attention_tc", 4.0 * B * n_heads * T * Tk * hs, f"fwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_tc_fwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(saved), ptr(ws), nbytes,
+                                       cur_stream()), "rnn_attention_tc_fwd")
+    return z, saved
+
+
+def attention_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):
+    lib = _lib.load(); _cuda(q, k, v, dz)
+    _check_qkv(dz, "dz")
+    for a, b, n in ((dq, q, "dq"), (dk, k, "dk"), (dv, v, "dv")):
+        if a.stride() != b.stride() or a.shape != b.shape:
+            raise ValueError(f"{n} must have the shape and strides of its forward tensor")
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, dz, dz, scale, mask, p_drop, seed, offset)
+    d.z_bs, d.z_rs = T * n_heads * hs, n_heads * hs
+    nbytes = lib.rnn_attention_tc_workspace(d)
+    ws = workspace(nbytes, q.device)
+    with _span("attention_tc", 8.0 * B * n_heads * T * Tk * hs, f"bwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_tc_bwd(d, ptr(q), ptr(k), ptr(v), ptr(saved), ptr(dz), ptr(dq), ptr(dk), ptr(dv),
+                                       ptr(ws), nbytes, cur_stream()), "rnn_attention_tc_bwd")
 
 
 def attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):

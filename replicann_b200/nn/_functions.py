@@ -484,15 +484,25 @@ class AttentionFn(Function):
             q = q_or_qkv if q_or_qkv.stride(-1) == 1 else q_or_qkv.contiguous()
             k = k if k.stride(-1) == 1 else k.contiguous()
             v = v if v.stride(-1) == 1 else v.contiguous()
-        z, lse = RF.attention_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
+        # bf16 with a 64-multiple head size: contractions on the tensor cores (batched tcgen05 GEMMs over all heads);
+        # anything else: the fused fp32-FMA kernel
+        ctx.tc = RF.attention_tc_ok(q, k, v, n_heads, hs)
         ctx.cfg = (scale, p_drop, n_heads, hs, seed, offset, packed)
+        if ctx.tc:
+            z, saved = RF.attention_tc_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
+            ctx.save_for_backward(q, k, v, saved, mask)
+            return z
+        z, lse = RF.attention_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
         ctx.save_for_backward(q, k, v, z, lse, mask)
         return z
 
     @staticmethod
     def backward(ctx, dz):
-        q, k, v, z, lse, mask = ctx.saved_tensors
         scale, p_drop, n_heads, hs, seed, offset, packed = ctx.cfg
+        if ctx.tc:
+            q, k, v, saved, mask = ctx.saved_tensors
+        else:
+            q, k, v, z, lse, mask = ctx.saved_tensors
         dz = dz if dz.stride(-1) == 1 else dz.contiguous()
         Hh = n_heads * hs
         if packed:
@@ -502,7 +512,12 @@ class AttentionFn(Function):
             dq = torch.empty_strided(q.shape, q.stride(), dtype=q.dtype, device=q.device)
             dk = torch.empty_strided(k.shape, k.stride(), dtype=k.dtype, device=k.device)
             dv = torch.empty_strided(v.shape, v.stride(), dtype=v.dtype, device=v.device)
-        RF.attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
+        if ctx.tc:
+            if dz.stride(0) % 8 or dz.stride(1) % 8 or dz.data_ptr() % 16:
+                dz = dz.contiguous()
+            RF.attention_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
+        else:
+            RF.attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
         if packed:
             return dqkv, None, None, None, None, None, None, None, None, None, None
         return dq, dk, dv, None, None, None, None, None, None, None, None
