@@ -518,6 +518,76 @@ layernorm_bwd_kernel(const T* __restrict__ dy, const T* __restrict__ xin, const 
   for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) p[i] = acc[i];
 }
 
+// Same computation for rows of at most 32 * W * NV elements: each lane owns NV fixed W-wide column groups, keeps
+// the row it is working on in registers (one global read of dy and x instead of two) and accumulates its share of
+// dgamma / dbeta in registers across all of its rows; shared memory sees one add per column per WARP at the end
+// instead of two atomics per element per row.
+template <typename T, int NV>
+__global__ void __launch_bounds__(256)
+layernorm_bwd_reg_kernel(const T* __restrict__ dy, const T* __restrict__ xin, const T* __restrict__ gamma,
+                         const float* __restrict__ mean, const float* __restrict__ rstd, T* __restrict__ dx,
+                         float* __restrict__ partials, long long M, int E) {
+  constexpr int W = Vec<T>::W;
+  extern __shared__ float acc[];  // [2][E] block accumulators
+  for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) acc[i] = 0.f;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  float gam[NV][W], dgam[NV][W], dbet[NV][W];
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = (k * 32 + lane) * W;
+#pragma unroll
+    for (int e = 0; e < W; ++e) { gam[k][e] = 0.f; dgam[k][e] = 0.f; dbet[k][e] = 0.f; }
+    if (c < E) Vec<T>::load(gamma + c, gam[k]);
+  }
+  for (long long row = (long long)blockIdx.x * nw + wid; row < M; row += (long long)gridDim.x * nw) {
+    const float mu = mean[row], rs = rstd[row];
+    float d[NV][W], xh[NV][W];
+    float sg = 0.f, sgx = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * W;
+      if (c < E) {
+        float v[W];
+        Vec<T>::load(dy + row * E + c, d[k]);
+        Vec<T>::load(xin + row * E + c, v);
+#pragma unroll
+        for (int e = 0; e < W; ++e) {
+          xh[k][e] = (v[e] - mu) * rs;
+          const float gg = d[k][e] * gam[k][e];
+          sg += gg;
+          sgx += gg * xh[k][e];
+          dgam[k][e] += d[k][e] * xh[k][e];
+          dbet[k][e] += d[k][e];
+        }
+      }
+    }
+    sg = warp_sum(sg) / E;
+    sgx = warp_sum(sgx) / E;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int c = (k * 32 + lane) * W;
+      if (c < E) {
+        float o[W];
+#pragma unroll
+        for (int e = 0; e < W; ++e) o[e] = rs * (d[k][e] * gam[k][e] - sg - xh[k][e] * sgx);
+        Vec<T>::store(dx + row * E + c, o);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < NV; ++k) {
+    const int c = (k * 32 + lane) * W;
+    if (c < E) {
+#pragma unroll
+      for (int e = 0; e < W; ++e) { atomicAdd(&acc[c + e], dgam[k][e]); atomicAdd(&acc[E + c + e], dbet[k][e]); }
+    }
+  }
+  __syncthreads();
+  float* p = partials + (long long)blockIdx.x * 2 * E;
+  for (int i = threadIdx.x; i < 2 * E; i += blockDim.x) p[i] = acc[i];
+}
+
 template <typename T>
 __global__ void __launch_bounds__(FIN_THREADS)
 layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, int E, T* dgamma, T* dbeta,
@@ -726,15 +796,34 @@ int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const 
   const size_t smem = (size_t)2 * E * sizeof(float);
   RNN_REQUIRE(smem <= 48 * 1024, RNN_ERR_SHAPE);
   if (is_f32) {
-    layernorm_bwd_kernel<float><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
-                                                               mean, rstd, (float*)dx, (float*)ws, M, E);
+    const int nv = ceil_div_i(E, 32 * 4);   // 4-wide column groups per lane
+    if (nv <= 2)
+      layernorm_bwd_reg_kernel<float, 2><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
+                                                                        mean, rstd, (float*)dx, (float*)ws, M, E);
+    else if (nv <= 4)
+      layernorm_bwd_reg_kernel<float, 4><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
+                                                                        mean, rstd, (float*)dx, (float*)ws, M, E);
+    else if (nv <= 8)
+      layernorm_bwd_reg_kernel<float, 8><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
+                                                                        mean, rstd, (float*)dx, (float*)ws, M, E);
+    else
+      layernorm_bwd_kernel<float><<<blocks, 256, smem, stream>>>((const float*)dy, (const float*)xin, (const float*)gamma,
+                                                                 mean, rstd, (float*)dx, (float*)ws, M, E);
     RNN_CHECK_LAUNCH();
     layernorm_bwd_finalize_kernel<float><<<ceil_div_i(E, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, blocks, E,
                                                                                 (float*)dgamma, (float*)dbeta,
                                                                                 accumulate_grads);
   } else {
-    layernorm_bwd_kernel<bf16><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
-                                                              mean, rstd, (bf16*)dx, (float*)ws, M, E);
+    const int nv = ceil_div_i(E, 32 * 8);   // 8-wide column groups per lane
+    if (nv <= 2)
+      layernorm_bwd_reg_kernel<bf16, 2><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
+                                                                       mean, rstd, (bf16*)dx, (float*)ws, M, E);
+    else if (nv <= 4)
+      layernorm_bwd_reg_kernel<bf16, 4><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
+                                                                       mean, rstd, (bf16*)dx, (float*)ws, M, E);
+    else
+      layernorm_bwd_kernel<bf16><<<blocks, 256, smem, stream>>>((const bf16*)dy, (const bf16*)xin, (const bf16*)gamma,
+                                                                mean, rstd, (bf16*)dx, (float*)ws, M, E);
     RNN_CHECK_LAUNCH();
     layernorm_bwd_finalize_kernel<bf16><<<ceil_div_i(E, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, blocks, E,
                                                                                (bf16*)dgamma, (bf16*)dbeta,

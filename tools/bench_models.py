@@ -68,6 +68,13 @@ def main():
                 enc(xx).float().sum().backward()
             ms = timed(step, 3, 5)
             out.write(f"TransformerEncoder {tag} B{B} T{T} E{E} H{H} fwd+bwd {str(dt)[6:]}\teager\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
+            # the same step replayed as a CUDA graph: GPU time without the Python launch path
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gph):
+                step()
+            ms = timed(gph.replay, 3, 10)
+            out.write(f"TransformerEncoder {tag} B{B} T{T} E{E} H{H} fwd+bwd {str(dt)[6:]}\tgraph\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
+            del gph
     if out is not sys.stdout:
         out.close()
 
