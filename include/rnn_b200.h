@@ -108,6 +108,14 @@ int rnn_conv2d_wgrad_f32(const rnn_conv_desc* d, const float* x, const float* dy
 /* fp32 counterpart of rnn_gemm_bf16 (same a_mn / b_mn meaning); nn.Linear in fp32 models. */
 int rnn_gemm_f32(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
                  const float* bias, int relu, int accumulate, cudaStream_t stream);
+/* The same GEMM at fp32 accuracy on the bf16 tensor cores: both operands are split into three bf16 pieces
+ * (24 mantissa bits) and the six significant piece products run as one tcgen05 GEMM over a 6x longer reduction.
+ * No accumulate mode; N % 8 == 0, K % 4 == 0 (and M % 8 == 0 when a_mn) -- rnn_gemm_f32_tc_supported().
+ * ws: rnn_gemm_f32_tc_workspace() bytes (the split operands and split-K partials). */
+int rnn_gemm_f32_tc_supported(int M, int N, int K, int a_mn, int b_mn);
+size_t rnn_gemm_f32_tc_workspace(int M, int N, int K, int has_epilogue);
+int rnn_gemm_f32_tc(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
+                    const float* bias, int relu, void* ws, size_t ws_bytes, cudaStream_t stream);
 /* out[c] (+)= sum_r x[r,c] -- bias gradient of nn.Linear / nn.Conv2d (autograd of attention.py:85,
  * transformer.py:24-25). */
 size_t rnn_colsum_workspace(long long M, int C);

@@ -533,6 +533,49 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   }
 }
 
+// fp32 GEMM on the bf16 tensor cores: x = x1 + x2 + x3 with x1 = bf16(x), x2 = bf16(x - x1), x3 = bf16(x - x1 - x2)
+// (24 mantissa bits in three pieces), and a.b ~= a1b1 + a1b2 + a2b1 + a1b3 + a2b2 + a3b1: every product of two bf16
+// numbers is exact in the fp32 accumulator and the dropped terms are below 2^-24 relative.  The six products are
+// ONE bf16 GEMM over a reduction six times as long: the pieces are laid out along K in the orders below.
+// layout 0: [rows][6 * cols] (pieces side by side; K-major operand), layout 1: [6 * rows][cols] (pieces stacked;
+// MN-major operand, rows = K).
+__constant__ int kPieceA[6] = {0, 0, 1, 0, 1, 2};
+__constant__ int kPieceB[6] = {0, 1, 0, 2, 1, 0};
+__global__ void __launch_bounds__(256)
+split3_kernel(const float* __restrict__ x, bf16* __restrict__ out, long long rows, int cols, int stacked, int is_b) {
+  const long long nvec = rows * (cols >> 2);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / (cols >> 2);
+    const int c = (int)(i - r * (cols >> 2)) * 4;
+    const float4 v = *reinterpret_cast<const float4*>(x + r * cols + c);
+    const float f[4] = {v.x, v.y, v.z, v.w};
+    uint2 piece[3];
+    {
+      float p1[4], p2[4], p3[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        p1[e] = __bfloat162float(__float2bfloat16(f[e]));
+        const float r1 = f[e] - p1[e];
+        p2[e] = __bfloat162float(__float2bfloat16(r1));
+        p3[e] = r1 - p2[e];
+      }
+      const float* ps[3] = {p1, p2, p3};
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        __nv_bfloat162 lo = __floats2bfloat162_rn(ps[k][0], ps[k][1]), hi = __floats2bfloat162_rn(ps[k][2], ps[k][3]);
+        piece[k].x = *reinterpret_cast<uint32_t*>(&lo);
+        piece[k].y = *reinterpret_cast<uint32_t*>(&hi);
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < 6; ++s) {
+      const int k = is_b ? kPieceB[s] : kPieceA[s];
+      bf16* dst = stacked ? out + ((long long)s * rows + r) * cols + c : out + r * (6ll * cols) + (long long)s * cols + c;
+      *reinterpret_cast<uint2*>(dst) = piece[k];
+    }
+  }
+}
+
 // Sum split-K partials (fp32) and finish the epilogue: out = [out +] sum_s ws[s] (+shift) (relu).
 __global__ void splitk_reduce_kernel(const float* __restrict__ ws, int splits, long long slab, int ncols,
                                      const float* __restrict__ shift, int relu, int accumulate, void* out,
@@ -1009,6 +1052,45 @@ int rnn_gemm_bf16(const void* A, const void* B, void* D, int M, int N, int K, in
     rc = launch_reduce(p.ws, p.splits, (long long)M * N, N, bias, relu, 0, D, out_f32, stream);
   }
   return rc;
+}
+
+// fp32 in / fp32 out GEMM at fp32 accuracy on the tensor cores (three-piece bf16 split, see split3_kernel).
+static bool f32_tc_shape_ok(int M, int N, int K, int a_mn, int b_mn) {
+  if (M <= 0 || N <= 0 || K <= 0 || (a_mn && !b_mn)) return false;
+  if (N % 8 != 0 || K % 4 != 0) return false;       // 16-byte rows of D and of the split operands
+  if (a_mn && M % 8 != 0) return false;
+  return (long long)6 * K < (1ll << 30);
+}
+int rnn_gemm_f32_tc_supported(int M, int N, int K, int a_mn, int b_mn) { return f32_tc_shape_ok(M, N, K, a_mn, b_mn); }
+size_t rnn_gemm_f32_tc_workspace(int M, int N, int K, int has_epilogue) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  const size_t a = ((size_t)6 * M * K * sizeof(bf16) + 255) & ~(size_t)255;
+  const size_t b = ((size_t)6 * N * K * sizeof(bf16) + 255) & ~(size_t)255;
+  return a + b + rnn_gemm_bf16_workspace(M, N, 6 * K, 1, has_epilogue);
+}
+int rnn_gemm_f32_tc(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
+                    const float* bias, int relu, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  RNN_REQUIRE(f32_tc_shape_ok(M, N, K, a_mn, b_mn), RNN_ERR_SHAPE);
+  const int has_epi = (bias != nullptr) || relu;
+  RNN_REQUIRE(ws != nullptr && ws_bytes >= rnn_gemm_f32_tc_workspace(M, N, K, has_epi), RNN_ERR_WORKSPACE);
+  RNN_REQUIRE(((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15u) == 0, RNN_ERR_ALIGN);
+  const size_t a_bytes = ((size_t)6 * M * K * sizeof(bf16) + 255) & ~(size_t)255;
+  const size_t b_bytes = ((size_t)6 * N * K * sizeof(bf16) + 255) & ~(size_t)255;
+  bf16* A3 = reinterpret_cast<bf16*>(ws);
+  bf16* B3 = reinterpret_cast<bf16*>(reinterpret_cast<unsigned char*>(ws) + a_bytes);
+  void* gws = reinterpret_cast<unsigned char*>(ws) + a_bytes + b_bytes;
+  // A is [M][K] (K-major: pieces side by side) or [K][M] (MN-major: pieces stacked along K); same for B
+  const long long a_rows = a_mn ? K : M, b_rows = b_mn ? K : N;
+  const int a_cols = a_mn ? M : K, b_cols = b_mn ? N : K;
+  RNN_REQUIRE(a_cols % 4 == 0 && b_cols % 4 == 0, RNN_ERR_SHAPE);
+  const int ga = ceil_div_i(a_rows * (a_cols / 4), 256), gb = ceil_div_i(b_rows * (b_cols / 4), 256);
+  const int cap = rnn_num_sms() * 16;
+  split3_kernel<<<ga < cap ? ga : cap, 256, 0, stream>>>(A, A3, a_rows, a_cols, a_mn, 0);
+  RNN_CHECK_LAUNCH();
+  split3_kernel<<<gb < cap ? gb : cap, 256, 0, stream>>>(B, B3, b_rows, b_cols, b_mn, 1);
+  RNN_CHECK_LAUNCH();
+  return rnn_gemm_bf16(A3, B3, D, M, N, 6 * K, a_mn, b_mn, bias, relu, 1, gws,
+                       ws_bytes - a_bytes - b_bytes, stream);
 }
 
 static int check_conv_desc(const rnn_conv_desc* d) {

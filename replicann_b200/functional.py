@@ -336,6 +336,17 @@ def gemm_f32(a, b, *, a_mn=False, b_mn=False, bias=None, relu=False, out=None, a
     if K != Kb:
         raise ValueError(f"reduction mismatch {K} vs {Kb}")
     d = out if out is not None else torch.empty((M, N), dtype=torch.float32, device=a.device)
+    # large enough and aligned: fp32-accurate GEMM on the tensor cores (three-piece bf16 split); else CUDA cores
+    if (_f32_tc_enabled and not accumulate and M * N * K >= (1 << 22) and d.is_contiguous()
+            and lib.rnn_gemm_f32_tc_supported(M, N, K, int(a_mn), int(b_mn))):
+        if bias is not None:
+            _req(bias, torch.float32, "bias")
+        nbytes = lib.rnn_gemm_f32_tc_workspace(M, N, K, int(bias is not None or relu))
+        ws = workspace(nbytes, a.device)
+        with _span("tc_gemm", 12.0 * M * N * K, f"f32x3 M{M} N{N} K{K} a_mn{int(a_mn)} b_mn{int(b_mn)}"):
+            check(lib.rnn_gemm_f32_tc(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
+                                      ptr(ws), nbytes, cur_stream()), "rnn_gemm_f32_tc")
+        return d
     check(lib.rnn_gemm_f32(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
                            int(accumulate), cur_stream()), "rnn_gemm_f32")
     return d
@@ -725,6 +736,7 @@ def attention_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, of
 
 
 _attn_tc_enabled = os.environ.get("RNN_ATTN_TC", "1") != "0"
+_f32_tc_enabled = os.environ.get("RNN_F32_TC", "1") != "0"
 
 
 def attention_tc_ok(q, k, v, n_heads, hs) -> bool:

@@ -71,3 +71,26 @@ def test_conv_fprop_with_fused_bn_statistics(name):
         rel = ((a - b).abs().max() / (b.abs().max() + 1e-12)).item()
         assert rel < 2e-5, (nm, rel)
     assert torch.allclose(rm1, rm2, rtol=1e-5, atol=1e-7) and torch.allclose(rv1, rv2, rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K,a_mn,b_mn", [(512, 256, 384, False, False), (1000, 264, 516, False, True),
+                                              (256, 512, 1024, True, True), (8192, 512, 512, False, False)])
+def test_gemm_f32_on_tensor_cores_is_fp32_accurate(M, N, K, a_mn, b_mn):
+    """rnn_gemm_f32_tc: fp32 operands split into three bf16 pieces, six piece products as one tcgen05 GEMM.
+    Against a float64 CPU product the error must be at fp32 level (1e-5 of max|ref|; a plain bf16 GEMM is 1e-2,
+    TF32 1e-3), with bias + ReLU fused."""
+    import torch
+    from replicann_b200 import functional as RF
+    g = torch.Generator().manual_seed(M + N + K)
+    a = torch.randn((K, M) if a_mn else (M, K), generator=g)
+    b = torch.randn((K, N) if b_mn else (N, K), generator=g)
+    bias = torch.randn(N, generator=g)
+    ref = (a.double().t() if a_mn else a.double()) @ (b.double() if b_mn else b.double().t())
+    got = RF.gemm_f32(a.cuda(), b.cuda(), a_mn=a_mn, b_mn=b_mn)
+    err = (got.cpu().double() - ref).abs().max().item() / ref.abs().max().item()
+    assert err < 1e-5, err
+    ref2 = torch.relu(ref + bias.double())
+    got2 = RF.gemm_f32(a.cuda(), b.cuda(), a_mn=a_mn, b_mn=b_mn, bias=bias.cuda(), relu=True)
+    err2 = (got2.cpu().double() - ref2).abs().max().item() / ref2.abs().max().item()
+    assert err2 < 1e-5, err2
