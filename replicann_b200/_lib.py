@@ -121,6 +121,19 @@ def ptr(t):
     return C.c_void_p(t.data_ptr())
 
 
+_raw_stream = None
+
+
 def cur_stream():
+    """cudaStream_t of torch's current stream on the current device.  Called once per kernel launch, so it goes
+    through torch's raw accessors (a few hundred ns) rather than building a torch.cuda.Stream object (~20 us)."""
+    global _raw_stream
     import torch
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if _raw_stream is None:
+        get_raw = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        get_dev = getattr(torch._C, "_cuda_getDevice", None)
+        if get_raw is not None and get_dev is not None:
+            _raw_stream = lambda: get_raw(get_dev())                      # noqa: E731
+        else:
+            _raw_stream = lambda: torch.cuda.current_stream().cuda_stream  # noqa: E731
+    return C.c_void_p(_raw_stream())

@@ -15,6 +15,7 @@ from . import _lib
 from ._lib import check, conv_desc, cur_stream, ptr
 
 _workspaces: dict[tuple[int, int], torch.Tensor] = {}
+_gemm_ws_bytes: dict[tuple, int] = {}   # workspace size per GEMM shape (saves one library call per launch)
 _tls = threading.local()
 
 # Optional per-call device timing used by bench.py: when `_profile` is a list, every instrumented wrapper
@@ -73,7 +74,6 @@ class _Side:
     def __init__(self, device):
         self.stream = torch.cuda.Stream(device=device)
         self.pending: list = []        # [(event after the group's last kernel, tensors kept alive, on_join)]
-        self.callback_queued = False
 
 
 _sides: dict[int, _Side] = {}
@@ -134,16 +134,13 @@ def side_join(device=None, keep: int = 0) -> None:
 
 
 def side_join_at_end_of_backward(device) -> None:
-    """Queue (once per backward pass) an autograd-engine callback that joins every outstanding group, so that
-    whatever runs after `.backward()` -- optimizer, all-reduce, the end of a CUDA-graph capture -- sees them."""
-    st = _side(device)
-    if st.callback_queued:
-        return
-    st.callback_queued = True
+    """Queue an autograd-engine callback that joins every outstanding group when the running backward pass ends,
+    so that whatever comes after `.backward()` -- optimizer, all-reduce, the end of a CUDA-graph capture -- sees
+    the weight gradients.  Queued by every block (the callback is a no-op once nothing is pending): no state
+    survives a backward pass that raised half-way."""
     dev = torch.device(device)
 
     def _cb():
-        st.callback_queued = False
         with torch.cuda.device(dev):
             side_join(dev)
 
@@ -179,7 +176,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     d = out if out is not None else torch.empty((M, N), dtype=out_dtype, device=a.device)
     if bias is not None:
         _req(bias, torch.float32, "bias")
-    nbytes = lib.rnn_gemm_bf16_workspace(M, N, K, int(out_f32), int(bias is not None or relu))
+    key = (M, N, K, out_f32, bias is not None or relu)
+    nbytes = _gemm_ws_bytes.get(key)
+    if nbytes is None:
+        nbytes = _gemm_ws_bytes[key] = lib.rnn_gemm_bf16_workspace(M, N, K, int(out_f32), int(key[4]))
     ws = workspace(nbytes, a.device)
     with _span("tc_gemm", 2.0 * M * N * K, f"M{M} N{N} K{K} a_mn{int(a_mn)} b_mn{int(b_mn)}"):
         check(lib.rnn_gemm_bf16(ptr(a), ptr(b), ptr(d), M, N, K, int(a_mn), int(b_mn), ptr(bias), int(relu),
