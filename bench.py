@@ -220,14 +220,22 @@ def run_gpu(args) -> None:
         RF.set_profile(prof)
         barrier()
         launches0 = RF.launch_count()
-        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        p0.record()
+        # Each eager step is enqueued behind a ~30 ms spin kernel: the host gets ahead of the device, so the
+        # event pairs bracket back-to-back kernels and not the Python launch path between them.
+        spin = int(30e-3 * torch.cuda.get_device_properties(dev).clock_rate * 1e3) if hasattr(
+            torch.cuda.get_device_properties(dev), "clock_rate") else 60_000_000
+        prof_ms = 0.0
+        marks = []
         for _ in range(args.steps):
+            torch.cuda._sleep(spin)
+            p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            p0.record()
             eager.step(x, y)
-        p1.record()
+            p1.record()
+            marks.append((p0, p1))
         torch.cuda.synchronize()
         RF.set_profile(None)
-        prof_ms = p0.elapsed_time(p1)
+        prof_ms = sum(a_.elapsed_time(b_) for a_, b_ in marks)
         launches = RF.launch_count() - launches0   # the graph replays exactly these kernels, K times
 
     # per-kernel-family device time inside the timed region
