@@ -276,6 +276,18 @@ int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, c
                          const void* dz, void* dq, void* dk, void* dv, void* ws, size_t ws_bytes,
                          cudaStream_t stream);
 
+/* fp32 form of the same pipeline at fp32 accuracy (the reference's default dtype): every operand of the six
+ * contractions is split into three bf16 pieces and each contraction is one batched tcgen05 GEMM over a reduction
+ * six times as long, fp32 out; head size, T and Tk multiples of 8.  `saved` keeps the fp32 probabilities. */
+int rnn_attention_f32_tc_supported(const rnn_attn_desc* d);
+size_t rnn_attention_f32_tc_saved_bytes(const rnn_attn_desc* d);
+size_t rnn_attention_f32_tc_workspace(const rnn_attn_desc* d);
+int rnn_attention_f32_tc_fwd(const rnn_attn_desc* d, const float* q, const float* k, const float* v, const void* mask,
+                             float* z, void* saved, void* ws, size_t ws_bytes, cudaStream_t stream);
+int rnn_attention_f32_tc_bwd(const rnn_attn_desc* d, const float* q, const float* k, const float* v,
+                             const void* saved, const float* dz, float* dq, float* dk, float* dv, void* ws,
+                             size_t ws_bytes, cudaStream_t stream);
+
 /* ---- fused optimizers over flat buckets ---------------------------------------------------------- */
 /* torch.optim.SGD (momentum, dampening, nesterov, weight_decay) on an fp32 master copy. */
 int rnn_sgd_step(float* w, float* buf, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16, long long n,

@@ -427,12 +427,35 @@ __device__ __forceinline__ float smax_score(const SmaxParams& p, float raw, int 
   return s;
 }
 
+// four consecutive probabilities in their storage type: bf16 (operands of the bf16 pipeline) or fp32 (the fp32
+// pipeline keeps them exact and splits them into bf16 pieces afterwards)
+__device__ __forceinline__ void store4(bf16* p, const float* f) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(f[0], f[1]), hi = __floats2bfloat162_rn(f[2], f[3]);
+  uint2 out;
+  out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(p) = out;
+}
+__device__ __forceinline__ void store4(float* p, const float* f) {
+  *reinterpret_cast<float4*>(p) = make_float4(f[0], f[1], f[2], f[3]);
+}
+__device__ __forceinline__ void load4(const bf16* p, float* f) {
+  const uint2 u = *reinterpret_cast<const uint2*>(p);
+  const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
+  const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
+  f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
+}
+__device__ __forceinline__ void load4(const float* p, float* f) {
+  const float4 v = *reinterpret_cast<const float4*>(p);
+  f[0] = v.x; f[1] = v.y; f[2] = v.z; f[3] = v.w;
+}
+
 // One warp per score row: P = softmax(S * scale (+ mask)), Pd = dropout(P).  Lanes walk the row four elements at a
 // time (Tk is a multiple of 8 here): 128-bit loads of the scores, one Philox call per four probabilities, 64-bit
 // stores.  Three passes over a row of a few KB (served by L1 after the first); same Philox word per element as
 // the fused kernel (keep_scale above).
+template <typename TP>
 __global__ void __launch_bounds__(128)
-attn_softmax_fwd_kernel(const float* __restrict__ S, bf16* __restrict__ P, bf16* __restrict__ Pd, long long rows,
+attn_softmax_fwd_kernel(const float* __restrict__ S, TP* __restrict__ P, TP* __restrict__ Pd, long long rows,
                         SmaxParams p) {
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
@@ -468,41 +491,33 @@ attn_softmax_fwd_kernel(const float* __restrict__ S, bf16* __restrict__ P, bf16*
     score4(j4, s);
 #pragma unroll
     for (int e = 0; e < 4; ++e) pv[e] = __expf(s[e] - m) * inv;
-    __nv_bfloat162 lo = __floats2bfloat162_rn(pv[0], pv[1]), hi = __floats2bfloat162_rn(pv[2], pv[3]);
-    uint2 out;
-    out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
-    *reinterpret_cast<uint2*>(P + r * p.Tk + 4 * j4) = out;
+    store4(P + r * p.Tk + 4 * j4, pv);
     if (Pd != P) {
       const uint4 rnd = philox4(p.seed, p.offset, (row_idx >> 2) + j4);
-      lo = __floats2bfloat162_rn(rnd.x >= thresh ? pv[0] * keep : 0.f, rnd.y >= thresh ? pv[1] * keep : 0.f);
-      hi = __floats2bfloat162_rn(rnd.z >= thresh ? pv[2] * keep : 0.f, rnd.w >= thresh ? pv[3] * keep : 0.f);
-      out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
-      *reinterpret_cast<uint2*>(Pd + r * p.Tk + 4 * j4) = out;
+      const float pk[4] = {rnd.x >= thresh ? pv[0] * keep : 0.f, rnd.y >= thresh ? pv[1] * keep : 0.f,
+                           rnd.z >= thresh ? pv[2] * keep : 0.f, rnd.w >= thresh ? pv[3] * keep : 0.f};
+      store4(Pd + r * p.Tk + 4 * j4, pk);
     }
   }
 }
 
 // dS = scale * P * (dPd * keep - delta), delta_i = sum_j dPd_ij * Pd_ij (= dz_i . z_i).  `keep` is read off the
 // stored pair: an element with P != 0 and Pd == 0 was dropped (P == 0 contributes nothing either way).
+template <typename TP>
 __global__ void __launch_bounds__(128)
-attn_softmax_bwd_kernel(const bf16* __restrict__ P, const bf16* __restrict__ Pd, const float* __restrict__ dPd,
-                        bf16* __restrict__ dS, long long rows, int Tk, float scale, float p_drop) {
+attn_softmax_bwd_kernel(const TP* __restrict__ P, const TP* __restrict__ Pd, const float* dPd, TP* dS,
+                        long long rows, int Tk, float scale, float p_drop) {   // dS may alias dPd (fp32 pipeline)
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * 4 + (threadIdx.x >> 5);
   if (r >= rows) return;
-  const uint2* prow = reinterpret_cast<const uint2*>(P + r * Tk);      // four bf16 per step (Tk % 8 == 0)
-  const uint2* pdrow = reinterpret_cast<const uint2*>(Pd + r * Tk);
+  const TP* prow = P + r * Tk;      // four elements per step (Tk % 8 == 0)
+  const TP* pdrow = Pd + r * Tk;
   const float4* grow = reinterpret_cast<const float4*>(dPd + r * Tk);
   const int n4 = Tk >> 2;
-  auto unpack4 = [](const uint2& u, float* f) {
-    const float2 a = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.x));
-    const float2 b = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&u.y));
-    f[0] = a.x; f[1] = a.y; f[2] = b.x; f[3] = b.y;
-  };
   float delta = 0.f;
   for (int j4 = lane; j4 < n4; j4 += 32) {
     float pd[4];
-    unpack4(pdrow[j4], pd);
+    load4(pdrow + 4 * j4, pd);
     const float4 g = grow[j4];
     delta += (g.x * pd[0] + g.y * pd[1]) + (g.z * pd[2] + g.w * pd[3]);
   }
@@ -510,20 +525,110 @@ attn_softmax_bwd_kernel(const bf16* __restrict__ P, const bf16* __restrict__ Pd,
   const float keep = 1.f / (1.f - p_drop);
   for (int j4 = lane; j4 < n4; j4 += 32) {
     float pv[4], pd[4];
-    unpack4(prow[j4], pv);
+    load4(prow + 4 * j4, pv);
     const float4 g4 = grow[j4];
     float g[4] = {g4.x, g4.y, g4.z, g4.w};
     if (Pd != P) {
-      unpack4(pdrow[j4], pd);
+      load4(pdrow + 4 * j4, pd);
 #pragma unroll
       for (int e = 0; e < 4; ++e) g[e] = pd[e] != 0.f ? g[e] * keep : 0.f;
     }
-    __nv_bfloat162 lo = __floats2bfloat162_rn(scale * pv[0] * (g[0] - delta), scale * pv[1] * (g[1] - delta));
-    __nv_bfloat162 hi = __floats2bfloat162_rn(scale * pv[2] * (g[2] - delta), scale * pv[3] * (g[3] - delta));
-    uint2 out;
-    out.x = *reinterpret_cast<uint32_t*>(&lo); out.y = *reinterpret_cast<uint32_t*>(&hi);
-    *reinterpret_cast<uint2*>(dS + r * Tk + 4 * j4) = out;
+    const float ds[4] = {scale * pv[0] * (g[0] - delta), scale * pv[1] * (g[1] - delta),
+                         scale * pv[2] * (g[2] - delta), scale * pv[3] * (g[3] - delta)};
+    store4(dS + r * Tk + 4 * j4, ds);
   }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// fp32 pipeline on the tensor cores at fp32 accuracy.  Every operand of the six contractions is split into three
+// bf16 pieces (x = x1 + x2 + x3, see split3_kernel in tc_gemm.cu) and repacked into dense per-(batch, head) slabs
+// with the pieces laid out along the reduction dimension, so that each contraction is one batched bf16 GEMM over
+// a reduction six times as long, with fp32 output.  Piece orders: operand A {1,1,2,1,2,3}, operand B {1,2,1,3,2,1}.
+//   side layout    [z][rows][6 * cols]  (K-major operand:  K = cols, pieces side by side)
+//   stacked layout [z][6 * rows][cols]  (MN-major operand: K = rows, pieces stacked)
+// Source element (b, r, h, c) = x[b * bs + r * rs + h * cols + c]; H = 1 describes a dense [B][rows][cols] tensor.
+// ---------------------------------------------------------------------------------------------------------------
+__constant__ int kAttnPieceA[6] = {0, 0, 1, 0, 1, 2};
+__constant__ int kAttnPieceB[6] = {0, 1, 0, 2, 1, 0};
+
+__global__ void __launch_bounds__(256)
+split3_heads_kernel(const float* __restrict__ x, long long bs, long long rs, int B, int H, int rows, int cols,
+                    bf16* __restrict__ out, int stacked, int is_b) {
+  const int c4n = cols >> 2;
+  const long long total = (long long)B * H * rows * c4n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long t = i;
+    const int c = (int)(t % c4n) * 4; t /= c4n;
+    const int r = (int)(t % rows); t /= rows;
+    const int h = (int)(t % H);
+    const int b = (int)(t / H);
+    const long long z = (long long)b * H + h;
+    float f[4];
+    load4(x + b * bs + r * rs + (long long)h * cols + c, f);
+    float piece[3][4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      piece[0][e] = __bfloat162float(__float2bfloat16(f[e]));
+      const float r1 = f[e] - piece[0][e];
+      piece[1][e] = __bfloat162float(__float2bfloat16(r1));
+      piece[2][e] = r1 - piece[1][e];
+    }
+#pragma unroll
+    for (int sidx = 0; sidx < 6; ++sidx) {
+      const int k = is_b ? kAttnPieceB[sidx] : kAttnPieceA[sidx];
+      bf16* dst = stacked ? out + ((z * 6 + sidx) * rows + r) * cols + c
+                          : out + (z * rows + r) * (6ll * cols) + (long long)sidx * cols + c;
+      store4(dst, k == 0 ? piece[0] : k == 1 ? piece[1] : piece[2]);
+    }
+  }
+}
+
+// dense fp32 slabs [B*H][rows][cols] -> the concatenated-heads layout out[b*bs + r*rs + h*cols + c]
+__global__ void __launch_bounds__(256)
+gather_heads_kernel(const float* __restrict__ slab, float* __restrict__ out, long long bs, long long rs, int B, int H,
+                    int rows, int cols) {
+  const int c4n = cols >> 2;
+  const long long total = (long long)B * H * rows * c4n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    long long t = i;
+    const int c = (int)(t % c4n) * 4; t /= c4n;
+    const int r = (int)(t % rows); t /= rows;
+    const int h = (int)(t % H);
+    const int b = (int)(t / H);
+    const float4 v = *reinterpret_cast<const float4*>(slab + i * 4);
+    *reinterpret_cast<float4*>(out + b * bs + r * rs + (long long)h * cols + c) = v;
+  }
+}
+
+int ew_blocks(long long total) {
+  const long long b = (total + 255) / 256, cap = (long long)rnn_num_sms() * 16;
+  return (int)(b < 1 ? 1 : (b > cap ? cap : b));
+}
+int launch_split(const float* x, long long bs, long long rs, int B, int H, int rows, int cols, bf16* out, int stacked,
+                 int is_b, cudaStream_t stream) {
+  split3_heads_kernel<<<ew_blocks((long long)B * H * rows * (cols / 4)), 256, 0, stream>>>(x, bs, rs, B, H, rows, cols,
+                                                                                         out, stacked, is_b);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+int launch_gather(const float* slab, float* out, long long bs, long long rs, int B, int H, int rows, int cols,
+                  cudaStream_t stream) {
+  gather_heads_kernel<<<ew_blocks((long long)B * H * rows * (cols / 4)), 256, 0, stream>>>(slab, out, bs, rs, B, H, rows,
+                                                                                         cols);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+// one batched GEMM over dense slabs: D[z] (fp32 [M][N]) = A[z] . B[z]^T with a reduction of 6 * K
+int slab_gemm(int nz, int M, int N, int K, int a_mn, int b_mn, const bf16* A, const bf16* Bm, float* D,
+              cudaStream_t stream) {
+  rnn_bgemm_desc g;
+  memset(&g, 0, sizeof(g));
+  g.batches = nz; g.heads = 1;
+  g.M = M; g.N = N; g.K = 6 * K; g.a_mn = a_mn; g.b_mn = b_mn; g.out_f32 = 1;
+  if (a_mn) { g.a_ld = M; g.a_bstride = 6ll * K * M; } else { g.a_ld = 6ll * K; g.a_bstride = 6ll * K * M; }
+  if (b_mn) { g.b_ld = N; g.b_bstride = 6ll * K * N; } else { g.b_ld = 6ll * K; g.b_bstride = 6ll * K * N; }
+  g.d_ld = N; g.d_bstride = (long long)M * N;
+  return rnn_gemm_batched_bf16(&g, A, Bm, D, stream);
 }
 
 int tc_check(const rnn_attn_desc* d) {
@@ -642,7 +747,7 @@ int rnn_attention_tc_fwd(const rnn_attn_desc* d, const void* q, const void* k, c
   sp.H = d->H; sp.T = d->T; sp.Tk = d->Tk; sp.scale = d->scale; sp.mask = mask; sp.mask_kind = d->mask_kind;
   sp.mask_bs = d->mask_bs; sp.mask_rs = d->mask_rs; sp.p_drop = d->p_drop; sp.seed = d->seed; sp.offset = d->offset;
   const long long rows = (long long)d->B * d->H * d->T;
-  attn_softmax_fwd_kernel<<<ceil_div_i(rows, 4), 128, 0, stream>>>(S, P, Pd, rows, sp);
+  attn_softmax_fwd_kernel<bf16><<<ceil_div_i(rows, 4), 128, 0, stream>>>(S, P, Pd, rows, sp);
   RNN_CHECK_LAUNCH();
   // z = w v  (:47), written straight into the concatenated-heads layout
   memset(&g, 0, sizeof(g));
@@ -687,7 +792,7 @@ int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, c
   if (rc != RNN_OK) return rc;
   // softmax / dropout / scale backward
   const long long rows = (long long)d->B * d->H * d->T;
-  attn_softmax_bwd_kernel<<<ceil_div_i(rows, 4), 128, 0, stream>>>(P, Pd, dPd, dS, rows, d->Tk, d->scale, d->p_drop);
+  attn_softmax_bwd_kernel<bf16><<<ceil_div_i(rows, 4), 128, 0, stream>>>(P, Pd, dPd, dS, rows, d->Tk, d->scale, d->p_drop);
   RNN_CHECK_LAUNCH();
   // dq = ds k
   memset(&g, 0, sizeof(g));
@@ -706,5 +811,147 @@ int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, c
   spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->q_rs, d->q_bs, d->hs);
   spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->k_rs, d->k_bs, d->hs);
   return rnn_gemm_batched_bf16(&g, dS, q, dk, stream);
+}
+
+// ---- fp32 attention on the tensor cores at fp32 accuracy (three-piece bf16 splits, see above) -----------------
+namespace {
+struct F32Plan {
+  long long n;          // B*H*T*Tk
+  size_t x, big, f, o;  // byte sizes of: a small split operand, a probability-sized split operand, an fp32 score
+                        // tensor, an fp32 output slab set
+  size_t total;
+};
+size_t up256(size_t v) { return (v + 255) & ~(size_t)255; }
+F32Plan f32_plan(const rnn_attn_desc* d) {
+  F32Plan p;
+  const long long nz = (long long)d->B * d->H, tm = d->T > d->Tk ? d->T : d->Tk;
+  p.n = nz * d->T * d->Tk;
+  p.x = up256((size_t)nz * 6 * tm * d->hs * sizeof(bf16));
+  p.big = up256((size_t)p.n * 6 * sizeof(bf16));
+  p.f = up256((size_t)p.n * sizeof(float));
+  p.o = up256((size_t)nz * tm * d->hs * sizeof(float));
+  p.total = 2 * p.x + p.big + p.f + p.o;
+  return p;
+}
+int f32_tc_check(const rnn_attn_desc* d) {
+  int rc = check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(d->hs % 8 == 0 && d->T % 8 == 0 && d->Tk % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->q_rs % 4 == 0 && d->k_rs % 4 == 0 && d->v_rs % 4 == 0 && d->z_rs % 4 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE(d->q_bs % 4 == 0 && d->k_bs % 4 == 0 && d->v_bs % 4 == 0 && d->z_bs % 4 == 0, RNN_ERR_SHAPE);
+  return RNN_OK;
+}
+}  // namespace
+
+int rnn_attention_f32_tc_supported(const rnn_attn_desc* d) {
+  if (d == nullptr || d->hs <= 0) return 0;
+  return d->hs % 8 == 0 && d->hs <= 32 * MAXD && d->T % 8 == 0 && d->Tk % 8 == 0 && d->q_rs % 4 == 0 &&
+         d->k_rs % 4 == 0 && d->v_rs % 4 == 0 && d->z_rs % 4 == 0 && d->q_bs % 4 == 0 && d->k_bs % 4 == 0 &&
+         d->v_bs % 4 == 0 && d->z_bs % 4 == 0;
+}
+// fp32 probabilities kept from forward to backward: P, and dropout(P) when dropout is active
+size_t rnn_attention_f32_tc_saved_bytes(const rnn_attn_desc* d) {
+  if (d == nullptr) return 0;
+  const size_t one = (size_t)d->B * d->H * d->T * d->Tk * sizeof(float);
+  return d->p_drop > 0.f ? 2 * one : one;
+}
+size_t rnn_attention_f32_tc_workspace(const rnn_attn_desc* d) { return d == nullptr ? 0 : f32_plan(d).total; }
+
+int rnn_attention_f32_tc_fwd(const rnn_attn_desc* d, const float* q, const float* k, const float* v, const void* mask,
+                             float* z, void* saved, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  int rc = f32_tc_check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE((d->mask_kind == 0) == (mask == nullptr), RNN_ERR_DTYPE);
+  const F32Plan pl = f32_plan(d);
+  RNN_REQUIRE(saved != nullptr && ws != nullptr && ws_bytes >= pl.total, RNN_ERR_WORKSPACE);
+  unsigned char* w = reinterpret_cast<unsigned char*>(ws);
+  bf16* X1 = reinterpret_cast<bf16*>(w);
+  bf16* X2 = reinterpret_cast<bf16*>(w + pl.x);
+  bf16* BIG = reinterpret_cast<bf16*>(w + 2 * pl.x);
+  float* S = reinterpret_cast<float*>(w + 2 * pl.x + pl.big);
+  float* O = reinterpret_cast<float*>(w + 2 * pl.x + pl.big + pl.f);
+  float* P = reinterpret_cast<float*>(saved);
+  float* Pd = d->p_drop > 0.f ? P + pl.n : P;
+  const int nz = d->B * d->H;
+  // S = q k^T  (nn/attention.py:37)
+  rc = launch_split(q, d->q_bs, d->q_rs, d->B, d->H, d->T, d->hs, X1, 0, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(k, d->k_bs, d->k_rs, d->B, d->H, d->Tk, d->hs, X2, 0, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->T, d->Tk, d->hs, 0, 0, X1, X2, S, stream);
+  if (rc != RNN_OK) return rc;
+  // scale, mask, softmax, dropout (:38-46)
+  SmaxParams sp;
+  sp.H = d->H; sp.T = d->T; sp.Tk = d->Tk; sp.scale = d->scale; sp.mask = mask; sp.mask_kind = d->mask_kind;
+  sp.mask_bs = d->mask_bs; sp.mask_rs = d->mask_rs; sp.p_drop = d->p_drop; sp.seed = d->seed; sp.offset = d->offset;
+  const long long rows = (long long)nz * d->T;
+  attn_softmax_fwd_kernel<float><<<ceil_div_i(rows, 4), 128, 0, stream>>>(S, P, Pd, rows, sp);
+  RNN_CHECK_LAUNCH();
+  // z = w v  (:47)
+  rc = launch_split(Pd, (long long)d->T * d->Tk, d->Tk, nz, 1, d->T, d->Tk, BIG, 0, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(v, d->v_bs, d->v_rs, d->B, d->H, d->Tk, d->hs, X1, 1, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->T, d->hs, d->Tk, 0, 1, BIG, X1, O, stream);
+  if (rc != RNN_OK) return rc;
+  return launch_gather(O, z, d->z_bs, d->z_rs, d->B, d->H, d->T, d->hs, stream);
+}
+
+int rnn_attention_f32_tc_bwd(const rnn_attn_desc* d, const float* q, const float* k, const float* v,
+                             const void* saved, const float* dz, float* dq, float* dk, float* dv, void* ws,
+                             size_t ws_bytes, cudaStream_t stream) {
+  int rc = f32_tc_check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(d->dz_rs % 4 == 0 && d->dz_bs % 4 == 0, RNN_ERR_SHAPE);
+  const F32Plan pl = f32_plan(d);
+  RNN_REQUIRE(saved != nullptr && ws != nullptr && ws_bytes >= pl.total, RNN_ERR_WORKSPACE);
+  unsigned char* w = reinterpret_cast<unsigned char*>(ws);
+  bf16* X1 = reinterpret_cast<bf16*>(w);
+  bf16* X2 = reinterpret_cast<bf16*>(w + pl.x);
+  bf16* BIG = reinterpret_cast<bf16*>(w + 2 * pl.x);
+  float* G = reinterpret_cast<float*>(w + 2 * pl.x + pl.big);     // d(dropout(w)), then ds in place
+  float* O = reinterpret_cast<float*>(w + 2 * pl.x + pl.big + pl.f);
+  const float* P = reinterpret_cast<const float*>(saved);
+  const float* Pd = d->p_drop > 0.f ? P + pl.n : P;
+  const int nz = d->B * d->H;
+  const long long pslab = (long long)d->T * d->Tk;
+  // d(dropout(w)) = dz v^T
+  rc = launch_split(dz, d->dz_bs, d->dz_rs, d->B, d->H, d->T, d->hs, X1, 0, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(v, d->v_bs, d->v_rs, d->B, d->H, d->Tk, d->hs, X2, 0, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->T, d->Tk, d->hs, 0, 0, X1, X2, G, stream);
+  if (rc != RNN_OK) return rc;
+  // dv = dropout(w)^T dz
+  rc = launch_split(Pd, pslab, d->Tk, nz, 1, d->T, d->Tk, BIG, 1, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(dz, d->dz_bs, d->dz_rs, d->B, d->H, d->T, d->hs, X1, 1, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->Tk, d->hs, d->T, 1, 1, BIG, X1, O, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_gather(O, dv, d->v_bs, d->v_rs, d->B, d->H, d->Tk, d->hs, stream);
+  if (rc != RNN_OK) return rc;
+  // softmax / dropout / scale backward, in place over G (every element is read by its own thread before it is
+  // written; the row sum is complete before the first write)
+  const long long rows = (long long)nz * d->T;
+  attn_softmax_bwd_kernel<float><<<ceil_div_i(rows, 4), 128, 0, stream>>>(P, Pd, G, G, rows, d->Tk, d->scale, d->p_drop);
+  RNN_CHECK_LAUNCH();
+  // dq = ds k
+  rc = launch_split(G, pslab, d->Tk, nz, 1, d->T, d->Tk, BIG, 0, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(k, d->k_bs, d->k_rs, d->B, d->H, d->Tk, d->hs, X1, 1, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->T, d->hs, d->Tk, 0, 1, BIG, X1, O, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_gather(O, dq, d->q_bs, d->q_rs, d->B, d->H, d->T, d->hs, stream);
+  if (rc != RNN_OK) return rc;
+  // dk = ds^T q
+  rc = launch_split(G, pslab, d->Tk, nz, 1, d->T, d->Tk, BIG, 1, 0, stream);
+  if (rc != RNN_OK) return rc;
+  rc = launch_split(q, d->q_bs, d->q_rs, d->B, d->H, d->T, d->hs, X1, 1, 1, stream);
+  if (rc != RNN_OK) return rc;
+  rc = slab_gemm(nz, d->Tk, d->hs, d->T, 1, 1, BIG, X1, O, stream);
+  if (rc != RNN_OK) return rc;
+  return launch_gather(O, dk, d->k_bs, d->k_rs, d->B, d->H, d->Tk, d->hs, stream);
 }
 }  // extern "C"

@@ -785,6 +785,54 @@ def attention_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask=No
                                        ptr(ws), nbytes, cur_stream()), "rnn_attention_tc_bwd")
 
 
+def attention_f32_tc_ok(q, k, v, n_heads, hs) -> bool:
+    """Whether the fp32 tensor-core attention pipeline takes these operands (fp32, head size / T / Tk % 8, aligned
+    strides, and enough work to pay for the operand splits)."""
+    if not _attn_tc_enabled or not _f32_tc_enabled or q.dtype != torch.float32:
+        return False
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    if B * n_heads * T * Tk * hs < (1 << 22) or B * n_heads >= 65536:
+        return False
+    return (hs % 8 == 0 and hs <= 128 and T % 8 == 0 and Tk % 8 == 0
+            and all(t.stride(0) % 4 == 0 and t.stride(1) % 4 == 0 and t.data_ptr() % 16 == 0 for t in (q, k, v)))
+
+
+def attention_f32_tc_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, offset=0):
+    lib = _lib.load(); _cuda(q, k, v, mask)
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _check_qkv(t, n)
+        _req_dtype(t, torch.float32, n)
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    z = torch.empty((B, T, n_heads * hs), dtype=q.dtype, device=q.device)
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, None, scale, mask, p_drop, seed, offset)
+    saved = torch.empty(lib.rnn_attention_f32_tc_saved_bytes(d), dtype=torch.uint8, device=q.device)
+    nbytes = lib.rnn_attention_f32_tc_workspace(d)
+    ws = workspace(nbytes, q.device)
+    with _span("attention_tc", 24.0 * B * n_heads * T * Tk * hs, f"f32 fwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_f32_tc_fwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(saved), ptr(ws), nbytes,
+                                           cur_stream()), "rnn_attention_f32_tc_fwd")
+    return z, saved
+
+
+def attention_f32_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):
+    lib = _lib.load(); _cuda(q, k, v, dz)
+    _check_qkv(dz, "dz")
+    for a, b, n in ((dq, q, "dq"), (dk, k, "dk"), (dv, v, "dv")):
+        if a.stride() != b.stride() or a.shape != b.shape:
+            raise ValueError(f"{n} must have the shape and strides of its forward tensor")
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, dz, dz, scale, mask, p_drop, seed, offset)
+    d.z_bs, d.z_rs = T * n_heads * hs, n_heads * hs
+    nbytes = lib.rnn_attention_f32_tc_workspace(d)
+    ws = workspace(nbytes, q.device)
+    with _span("attention_tc", 48.0 * B * n_heads * T * Tk * hs, f"f32 bwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_f32_tc_bwd(d, ptr(q), ptr(k), ptr(v), ptr(saved), ptr(dz), ptr(dq), ptr(dk), ptr(dv),
+                                           ptr(ws), nbytes, cur_stream()), "rnn_attention_f32_tc_bwd")
+
+
 def attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):
     """Writes dq/dk/dv (pre-allocated, same strides as q/k/v)."""
     lib = _lib.load(); _cuda(q, k, v, z, dz)

@@ -486,10 +486,13 @@ class AttentionFn(Function):
             v = v if v.stride(-1) == 1 else v.contiguous()
         # bf16 with a 64-multiple head size: contractions on the tensor cores (batched tcgen05 GEMMs over all heads);
         # anything else: the fused fp32-FMA kernel
-        ctx.tc = RF.attention_tc_ok(q, k, v, n_heads, hs)
+        # fp32 large enough to pay for operand splits: the same pipeline at fp32 accuracy (three-piece bf16 splits)
+        ctx.tc = 1 if RF.attention_tc_ok(q, k, v, n_heads, hs) else (
+            2 if RF.attention_f32_tc_ok(q, k, v, n_heads, hs) else 0)
         ctx.cfg = (scale, p_drop, n_heads, hs, seed, offset, packed)
         if ctx.tc:
-            z, saved = RF.attention_tc_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
+            fwd = RF.attention_tc_fwd if ctx.tc == 1 else RF.attention_f32_tc_fwd
+            z, saved = fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
             ctx.save_for_backward(q, k, v, saved, mask)
             return z
         z, lse = RF.attention_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
@@ -515,7 +518,8 @@ class AttentionFn(Function):
         if ctx.tc:
             if dz.stride(0) % 8 or dz.stride(1) % 8 or dz.data_ptr() % 16:
                 dz = dz.contiguous()
-            RF.attention_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
+            bwd = RF.attention_tc_bwd if ctx.tc == 1 else RF.attention_f32_tc_bwd
+            bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
         else:
             RF.attention_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
         if packed:

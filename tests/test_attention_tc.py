@@ -110,3 +110,45 @@ def test_tc_attention_rejects_unsupported_shapes():
     assert not RF.attention_tc_ok(q, q, q, 1, 64)           # T = 12 is not a multiple of 8
     with pytest.raises(Exception):
         RF.attention_tc_fwd(q, q, q, 1, 64, 0.125)
+
+
+@pytest.mark.parametrize("B,H,T,Tk,hs,mask_kind,p_drop", [
+    (2, 4, 128, 128, 64, None, 0.0),
+    (6, 2, 72, 200, 32, "float", 0.0),       # cross attention, head size 32, ragged against the tiles
+    (2, 4, 128, 128, 64, "bool", 0.1),
+    (8, 12, 512, 512, 64, "float", 0.0),     # Track R shape L in the reference's default dtype
+])
+def test_f32_tc_attention_is_fp32_accurate(B, H, T, Tk, hs, mask_kind, p_drop):
+    """fp32 attention on the tensor cores (three-piece bf16 splits): forward and gradients against the fused fp32
+    kernel of the library (same Philox mask when dropout is on) at the fp32 tolerance of the north star (1e-4),
+    and against float64 torch on the CPU when there is no dropout."""
+    from replicann_b200 import functional as RF
+    g = torch.Generator().manual_seed(B * 100 + Tk)
+    E = H * hs
+    q = (torch.randn(B, T, E, generator=g) * 0.5)
+    k = (torch.randn(B, Tk, E, generator=g) * 0.5)
+    v = (torch.randn(B, Tk, E, generator=g) * 0.5)
+    dz = (torch.randn(B, T, E, generator=g) * 0.1)
+    mask = None
+    if mask_kind == "bool":
+        mask = torch.triu(torch.ones(T, Tk, dtype=torch.bool), diagonal=1)
+    elif mask_kind == "float":
+        mask = torch.tril(torch.ones(T, Tk))
+    scale = 1.0 / math.sqrt(E)
+    qd, kd, vd, dzd = q.cuda(), k.cuda(), v.cuda(), dz.cuda()
+    md = mask.cuda() if mask is not None else None
+    assert RF.attention_f32_tc_ok(qd, kd, vd, H, hs)
+    z, saved = RF.attention_f32_tc_fwd(qd, kd, vd, H, hs, scale, md, p_drop, 99, 3)
+    dq, dk, dv = (torch.empty_like(t) for t in (qd, kd, vd))
+    RF.attention_f32_tc_bwd(qd, kd, vd, saved, dzd, H, hs, scale, dq, dk, dv, md, p_drop, 99, 3)
+    zf, lse = RF.attention_fwd(qd, kd, vd, H, hs, scale, md, p_drop, 99, 3)
+    dqf, dkf, dvf = (torch.empty_like(t) for t in (qd, kd, vd))
+    RF.attention_bwd(qd, kd, vd, zf, dzd, lse, H, hs, scale, dqf, dkf, dvf, md, p_drop, 99, 3)
+    torch.cuda.synchronize()
+    for a, b, name in ((z, zf, "z"), (dq, dqf, "dq"), (dk, dkf, "dk"), (dv, dvf, "dv")):
+        assert rel(a, b) < 1e-4, (name, rel(a, b))
+    if p_drop == 0.0:
+        qr, kr, vr = (t.double().clone().requires_grad_(True) for t in (q, k, v))
+        zr = torch_ref(qr, kr, vr, H, hs, scale, mask.double() if mask_kind == "float" else mask)
+        zr.backward(dz.double())
+        assert rel(z, zr) < 1e-4 and rel(dq, qr.grad) < 1e-4 and rel(dk, kr.grad) < 1e-4 and rel(dv, vr.grad) < 1e-4
