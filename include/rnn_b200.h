@@ -108,6 +108,11 @@ int rnn_conv2d_wgrad_f32(const rnn_conv_desc* d, const float* x, const float* dy
 /* fp32 counterpart of rnn_gemm_bf16 (same a_mn / b_mn meaning); nn.Linear in fp32 models. */
 int rnn_gemm_f32(const float* A, const float* B, float* D, int M, int N, int K, int a_mn, int b_mn,
                  const float* bias, int relu, int accumulate, cudaStream_t stream);
+/* ReLU backward fused with the bias gradient that follows it (autograd of relu + bias add: transformer.py:24-25,
+ * CNN conv+bias+ReLU layers): dx = dy * (y > 0), dbias[c] (+)= sum_r dx[r, c].  C % 8 == 0 (bf16) / % 4 (fp32);
+ * ws: rnn_colsum_workspace(M, C). */
+int rnn_relu_bwd_colsum(const void* dy, const void* y, void* dx, long long M, int C, void* dbias, int accumulate,
+                        int is_f32, void* ws, size_t ws_bytes, cudaStream_t stream);
 /* The same GEMM at fp32 accuracy on the bf16 tensor cores: both operands are split into three bf16 pieces
  * (24 mantissa bits) and the six significant piece products run as one tcgen05 GEMM over a 6x longer reduction.
  * No accumulate mode; N % 8 == 0, K % 4 == 0 (and M % 8 == 0 when a_mn) -- rnn_gemm_f32_tc_supported().

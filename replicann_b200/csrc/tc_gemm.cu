@@ -767,12 +767,14 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     const int rc = make_tmap_out(&td, &p);
     if (rc != RNN_OK) return rc;
   }
-  static bool attr_set = false;
+  static bool attr_set[64] = {false};   // the attribute is per device
   auto kern = tc_kernel<BN, KIND, A_MN, B_MN, FUSED, STATS, CG>;
   constexpr int smem = Cfg<BN, CG, KIND>::SMEM_BYTES;
-  if (!attr_set) {
+  int dev = 0;
+  RNN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    attr_set = true;
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int units = rnn_num_sms() / CG;   // CTAs, or CTA pairs
   const int tiles = ceil_div_i(p.n_mblk, CG) * p.n_nblk * p.splits;

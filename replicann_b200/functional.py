@@ -427,6 +427,25 @@ def relu_bwd(dy, y):
     return dx
 
 
+def relu_bwd_colsum(dy, y, *, out, accumulate=False):
+    """dx = dy * (y > 0) and out[c] (+)= column sums of dx over the last dimension, in one pass; returns dx.
+    Falls back to the two separate kernels when the channel count is not a multiple of the vector width."""
+    lib = _lib.load(); _cuda(dy, y)
+    Cn = y.shape[-1]
+    w = 4 if y.dtype == torch.float32 else 8
+    if Cn % w or not dy.is_contiguous() or not y.is_contiguous() or out.dtype != y.dtype:
+        dx = relu_bwd(dy, y)
+        colsum(dx.reshape(-1, Cn), out=out, accumulate=accumulate)
+        return dx
+    M = y.numel() // Cn
+    dx = torch.empty_like(y)
+    nbytes = lib.rnn_colsum_workspace(M, Cn)
+    ws = workspace(nbytes, y.device)
+    check(lib.rnn_relu_bwd_colsum(ptr(dy), ptr(y), ptr(dx), M, Cn, ptr(out), int(accumulate), _is_f32(y), ptr(ws),
+                                  nbytes, cur_stream()), "rnn_relu_bwd_colsum")
+    return dx
+
+
 def tanh_fwd(x):
     lib = _lib.load(); _req(x, torch.float32, "x")
     y = torch.empty_like(x)

@@ -95,11 +95,18 @@ class Conv2dFn(Function):
         xh, weight, bias, y = ctx.saved_tensors
         wk = nhwc(weight)
         dyh = nhwc(dy)
-        if ctx.relu:
-            dyh = RF.relu_bwd(dyh, y)
         stride, pad = ctx.stride, ctx.pad
         f32 = weight.dtype == torch.float32
         dw = db = dx = None
+        want_db = bias is not None and ctx.needs_input_grad[2]
+        if ctx.relu and want_db and bias.is_leaf:
+            # ReLU backward and the bias gradient in one pass over dy
+            box = []
+            _write_param_grad(bias, lambda out, acc: box.append(RF.relu_bwd_colsum(dyh, y, out=out, accumulate=acc)))
+            dyh = box[0]
+            want_db = False
+        elif ctx.relu:
+            dyh = RF.relu_bwd(dyh, y)
         if ctx.needs_input_grad[1]:
             def wg(out, acc):
                 o = nhwc_param_view(out)
@@ -108,7 +115,7 @@ class Conv2dFn(Function):
                 else:
                     RF.conv2d_wgrad(xh, dyh, tuple(wk.shape), stride=stride, pad=pad, out=o, accumulate=acc)
             dw = _write_param_grad(weight, wg)
-        if bias is not None and ctx.needs_input_grad[2]:
+        if want_db:
             K = dyh.shape[-1]
             db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
         if ctx.needs_input_grad[0]:
@@ -211,10 +218,16 @@ class LinearFn(Function):
         dy2 = dy.reshape(-1, weight.shape[0])
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
-        if ctx.relu:
-            dy2 = RF.relu_bwd(dy2, y)
         f32 = weight.dtype == torch.float32
         dw = db = dx = None
+        want_db = bias is not None and ctx.needs_input_grad[2]
+        if ctx.relu and want_db and bias.is_leaf:
+            box = []
+            _write_param_grad(bias, lambda out, acc: box.append(RF.relu_bwd_colsum(dy2, y, out=out, accumulate=acc)))
+            dy2 = box[0]
+            want_db = False
+        elif ctx.relu:
+            dy2 = RF.relu_bwd(dy2, y)
         if ctx.needs_input_grad[1]:
             def wg(out, acc):
                 if f32:
@@ -225,7 +238,7 @@ class LinearFn(Function):
                     g = RF.gemm(dy2, x2, a_mn=True, b_mn=True)
                     RF.add(out, g, out=out)
             dw = _write_param_grad(weight, wg)
-        if bias is not None and ctx.needs_input_grad[2]:
+        if want_db:
             db = _write_param_grad(bias, lambda out, acc: RF.colsum(dy2, out=out, accumulate=acc))
         if ctx.needs_input_grad[0]:
             if f32:

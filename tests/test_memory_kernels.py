@@ -338,3 +338,28 @@ def test_colsum(dtype, tol):
     f = RF()
     x = rnd((1000, 96), 1, dtype)
     assert rel_err(f.colsum(x.cuda()), x.float().sum(0)) < tol
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,C,dt", [(5000, 64, "bf16"), (777, 4096, "bf16"), (1030, 24, "bf16"), (999, 36, "f32"),
+                                     (4096, 10, "f32")])
+def test_colsum_and_fused_relu_bwd_colsum(M, C, dt):
+    """Bias gradients: the vector column-sum kernel (C a multiple of the 16-byte vector) and the scalar one, and
+    ReLU backward fused with the column sum, against torch on the CPU (with and without accumulation)."""
+    import torch
+    from replicann_b200 import functional as RF
+    dtype = torch.bfloat16 if dt == "bf16" else torch.float32
+    g = torch.Generator().manual_seed(M + C)
+    x = torch.randn(M, C, generator=g).to(dtype)
+    y = torch.randn(M, C, generator=g).to(dtype)
+    ref = x.float().sum(0)
+    got = RF.colsum(x.cuda())
+    tol = 2e-2 if dt == "bf16" else 1e-4
+    assert ((got.float().cpu() - ref).abs().max() / ref.abs().max()).item() < tol
+    prev = torch.randn(C, generator=g).to(dtype)
+    out = prev.clone().cuda()
+    dx = RF.relu_bwd_colsum(x.cuda(), y.cuda(), out=out, accumulate=True)
+    dx_ref = torch.where(y.float() > 0, x.float(), torch.zeros(()))
+    assert torch.equal(dx.float().cpu(), dx_ref)                      # a select: exact
+    ref2 = dx_ref.sum(0) + prev.float()
+    assert ((out.float().cpu() - ref2).abs().max() / ref2.abs().max()).item() < tol
