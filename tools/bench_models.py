@@ -75,6 +75,31 @@ def main():
             ms = timed(gph.replay, 3, 10)
             out.write(f"TransformerEncoder {tag} B{B} T{T} E{E} H{H} fwd+bwd {str(dt)[6:]}\tgraph\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
             del gph
+    # the reference's decoder blocks (Track R rows a11 / a12), shape S, fp32, GPU time of forward + backward
+    from replicann_b200.arch.transformer import TransformerCrossDecoder, TransformerDecoder
+    B, T, E, H = 64, 128, 512, 8
+    for name, cls in (("TransformerDecoder", TransformerDecoder), ("TransformerCrossDecoder", TransformerCrossDecoder)):
+        # fp32: cast to bf16 the decoders' float tril mask raises the reference's TypeError (nn/attention.py:43-44)
+        dec = cls(H, E, context_size=T).cuda().train()
+        xx = torch.randn(B, T, E, device="cuda", requires_grad=True)
+        kv = torch.randn(B, T, E, device="cuda")
+
+        def dstep():
+            for p in dec.parameters():
+                p.grad = None
+            y_ = dec(xx, kv, kv) if cls is TransformerCrossDecoder else dec(xx)
+            y_.float().sum().backward()
+        try:
+            ms = timed(dstep, 3, 5)
+            out.write(f"{name} S B{B} T{T} E{E} H{H} fwd+bwd float32\teager\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
+            gph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gph):
+                dstep()
+            ms = timed(gph.replay, 3, 10)
+            out.write(f"{name} S B{B} T{T} E{E} H{H} fwd+bwd float32\tgraph\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
+            del gph
+        except Exception as ex:  # noqa: BLE001  (e.g. the reference's bf16 TypeError for the float decoder mask)
+            out.write(f"{name} S f32\t-\t-\t-\t{type(ex).__name__}: {str(ex)[:80]}\n")
     if out is not sys.stdout:
         out.close()
 
