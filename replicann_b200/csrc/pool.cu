@@ -80,11 +80,16 @@ template <> struct WIdx<8> {
 // Max pooling runs one grid row per output (fwd) / input (bwd) image row: blockIdx.y = row, blockIdx.z = image,
 // so a thread decodes only (column, channel group) -- the flat-index version spent ~250 instructions per 16 bytes
 // on integer divisions and was instruction-bound at 1 TB/s.
-template <typename T, bool VEC>
+template <typename T, bool VEC, int FX>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx,
                    unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift) {
   constexpr int VW = PV<T, VEC>::W;
+  // FX != 0: the window geometry is a compile-time constant (1: 3x3 stride 2 pad 1, 2: 2x2 stride 2, 3: 3x3 stride 2
+  // pad 0 -- the pools of ResNet, VGG and AlexNet), which turns the divisions below into shifts
+  const int gR = FX == 2 ? 2 : (FX ? 3 : g.R), gS = FX == 2 ? 2 : (FX ? 3 : g.S);
+  const int gsh = FX ? 2 : g.sh, gsw = FX ? 2 : g.sw;
+  const int gph = FX == 1 ? 1 : (FX ? 0 : g.ph), gpw = FX == 1 ? 1 : (FX ? 0 : g.pw);
   const int cgs = g.C / VW;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= g.Q * cgs) return;
@@ -93,17 +98,17 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
   const int p = blockIdx.y, n = blockIdx.z;
   float best[VW];
   int bl[VW];   // argmax as the position inside the (unclipped) R x S window
-  const int h0 = p * g.sh - g.ph, w0 = q * g.sw - g.pw;
+  const int h0 = p * gsh - gph, w0 = q * gsw - gpw;
   const int hs = h0 < 0 ? 0 : h0, ws = w0 < 0 ? 0 : w0;
-  const int he = min(h0 + g.R, g.H), we = min(w0 + g.S, g.W);
+  const int he = min(h0 + gR, g.H), we = min(w0 + gS, g.W);
 #pragma unroll
-  for (int e2 = 0; e2 < VW; ++e2) { best[e2] = -INFINITY; bl[e2] = (hs - h0) * g.S + (ws - w0); }
+  for (int e2 = 0; e2 < VW; ++e2) { best[e2] = -INFINITY; bl[e2] = (hs - h0) * gS + (ws - w0); }
   const T* xn = x + (long long)n * g.H * g.W * g.C + cg * VW;
   for (int h = hs; h < he; ++h)
     for (int w = ws; w < we; ++w) {
       float v[VW];
       PV<T, VEC>::load(xn + ((long long)h * g.W + w) * g.C, v);
-      const int local = (h - h0) * g.S + (w - w0);
+      const int local = (h - h0) * gS + (w - w0);
 #pragma unroll
       for (int e2 = 0; e2 < VW; ++e2)
         if (v[e2] > best[e2] || v[e2] != v[e2]) { best[e2] = v[e2]; bl[e2] = local; }
@@ -113,7 +118,7 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
   if (idx) {  // torch's flat index h * W + w inside the input plane
 #pragma unroll
     for (int e2 = 0; e2 < VW; ++e2) {
-      const int lh = bl[e2] / g.S, lw = bl[e2] - lh * g.S;
+      const int lh = bl[e2] / gS, lw = bl[e2] - lh * gS;
       idx[o + e2] = (h0 + lh) * g.W + (w0 + lw);
     }
   }
@@ -121,11 +126,16 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
 }
 
 // Gather form of the backward pass: every input element sums the dy of the windows whose argmax it is.
-template <typename T, bool VEC>
+template <typename T, bool VEC, int FX>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const unsigned char* __restrict__ widx,
                    T* __restrict__ dx, PoolGeom g, int cgs_shift) {
   constexpr int VW = PV<T, VEC>::W;
+  // FX != 0: the window geometry is a compile-time constant (1: 3x3 stride 2 pad 1, 2: 2x2 stride 2, 3: 3x3 stride 2
+  // pad 0 -- the pools of ResNet, VGG and AlexNet), which turns the divisions below into shifts
+  const int gR = FX == 2 ? 2 : (FX ? 3 : g.R), gS = FX == 2 ? 2 : (FX ? 3 : g.S);
+  const int gsh = FX ? 2 : g.sh, gsw = FX ? 2 : g.sw;
+  const int gph = FX == 1 ? 1 : (FX ? 0 : g.ph), gpw = FX == 1 ? 1 : (FX ? 0 : g.pw);
   const int cgs = g.C / VW;
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= g.W * cgs) return;
@@ -137,17 +147,17 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
 #pragma unroll
   for (int e2 = 0; e2 < VW; ++e2) acc[e2] = 0.f;
   // windows p with p*sh - ph <= h < p*sh - ph + R (the row bounds are the same for the whole block)
-  int p_lo = (h + g.ph - g.R + g.sh) / g.sh; if (h + g.ph - g.R + 1 <= 0) p_lo = 0;
-  int p_hi = (h + g.ph) / g.sh; if (p_hi > g.P - 1) p_hi = g.P - 1;
-  int q_lo = (w + g.pw - g.S + g.sw) / g.sw; if (w + g.pw - g.S + 1 <= 0) q_lo = 0;
-  int q_hi = (w + g.pw) / g.sw; if (q_hi > g.Q - 1) q_hi = g.Q - 1;
+  int p_lo = (h + gph - gR + gsh) / gsh; if (h + gph - gR + 1 <= 0) p_lo = 0;
+  int p_hi = (h + gph) / gsh; if (p_hi > g.P - 1) p_hi = g.P - 1;
+  int q_lo = (w + gpw - gS + gsw) / gsw; if (w + gpw - gS + 1 <= 0) q_lo = 0;
+  int q_hi = (w + gpw) / gsw; if (q_hi > g.Q - 1) q_hi = g.Q - 1;
   for (int p = p_lo; p <= p_hi; ++p)
     for (int q = q_lo; q <= q_hi; ++q) {
       const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
       float d[VW];
       PV<T, VEC>::load(dy + o, d);
       if (widx) {
-        const int local = (h - (p * g.sh - g.ph)) * g.S + (w - (q * g.sw - g.pw));
+        const int local = (h - (p * gsh - gph)) * gS + (w - (q * gsw - gpw));
         int l[VW];
         WIdx<VW>::load(widx + o, l);
 #pragma unroll
@@ -289,6 +299,15 @@ int pow2_shift(int v) {
   return s;
 }
 
+// 1: 3x3 stride 2 pad 1, 2: 2x2 stride 2 pad 0, 3: 3x3 stride 2 pad 0, else 0 (see the FX template parameter)
+int fixed_geometry(const PoolGeom& g) {
+  if (g.sh != 2 || g.sw != 2 || g.R != g.S || g.ph != g.pw) return 0;
+  if (g.R == 3 && g.ph == 1) return 1;
+  if (g.R == 2 && g.ph == 0) return 2;
+  if (g.R == 3 && g.ph == 0) return 3;
+  return 0;
+}
+
 int pgrid(long long total) {
   long long b = (total + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * 16;
@@ -322,12 +341,19 @@ int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* windo
   const int cgs = vec ? C / vw : C;
   const int sh_ = pow2_shift(cgs);
   const dim3 grid(ceil_div_i((long long)g.Q * cgs, 256), g.P, N);
+  const int fx = fixed_geometry(g);
   if (is_f32) {
-    if (vec) maxpool_fwd_kernel<float, true><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
-    else maxpool_fwd_kernel<float, false><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
+    if (vec) maxpool_fwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
+    else maxpool_fwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
+  } else if (!vec) {
+    maxpool_fwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
   } else {
-    if (vec) maxpool_fwd_kernel<bf16, true><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
-    else maxpool_fwd_kernel<bf16, false><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
+    switch (fx) {
+      case 1: maxpool_fwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
+      case 2: maxpool_fwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
+      case 3: maxpool_fwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
+      default: maxpool_fwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
+    }
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
@@ -344,12 +370,19 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
   const int cgs = vec ? C / vw : C;
   const int sh_ = pow2_shift(cgs);
   const dim3 grid(ceil_div_i((long long)W * cgs, 256), H, N);
+  const int fx = fixed_geometry(g);
   if (is_f32) {
-    if (vec) maxpool_bwd_kernel<float, true><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
-    else maxpool_bwd_kernel<float, false><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
+    if (vec) maxpool_bwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
+    else maxpool_bwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
+  } else if (!vec) {
+    maxpool_bwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
   } else {
-    if (vec) maxpool_bwd_kernel<bf16, true><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
-    else maxpool_bwd_kernel<bf16, false><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
+    switch (fx) {
+      case 1: maxpool_bwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
+      case 2: maxpool_bwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
+      case 3: maxpool_bwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
+      default: maxpool_bwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
+    }
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
