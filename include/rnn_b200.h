@@ -46,6 +46,12 @@ int rnn_version(void);
 int rnn_sm_count(void); /* SMs of the current device (148 on B200) */
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 unsigned long long rnn_launch_count(void);
+/* Dropout under CUDA graphs.  Every Philox-drawing kernel (rnn_dropout_fwd, the attention families) adds a
+ * device-side epoch to its `offset` argument; the epoch is 0 until this call, which enqueues kernels that advance
+ * it by 2^32.  Put one call at the head of a captured training step: each replay then draws fresh masks although
+ * the seed / offset arguments are frozen in the graph; forward and backward of one step see the same epoch.
+ * No counterpart in the reference (torch keeps its Philox offset in device memory under graphs for the same reason). */
+int rnn_rng_advance(cudaStream_t stream);
 
 /* ---- tensor-core contractions (tcgen05 + TMEM + TMA) -------------------------------------- */
 

@@ -38,11 +38,16 @@ constexpr int KC = 64;     // keys (or queries, in the dk/dv kernel) per shared-
 constexpr int ROWS = 16;   // rows handled per CTA (4 warps x 4)
 constexpr int MAXD = 4;    // head size <= 32 * MAXD = 128
 
+// Device-side RNG epoch of this file (see elementwise.cu): added to every Philox offset.
+static __device__ unsigned long long g_rng_epoch_attn = 0ull;
+__global__ void rng_advance_attn_kernel(unsigned long long inc) { g_rng_epoch_attn += inc; }
+
 // Philox-4x32-10: one call yields four 32-bit words.  Attention-weight element `idx` uses word (idx & 3) of the
 // block with counter (idx >> 2), so a kernel that walks four consecutive elements pays for one call.
 __device__ __forceinline__ uint4 philox4(unsigned long long seed, unsigned long long offset, unsigned long long ctr) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+  offset += g_rng_epoch_attn;
   uint32_t c0 = (uint32_t)ctr, c1 = (uint32_t)(ctr >> 32), c2 = (uint32_t)offset, c3 = (uint32_t)(offset >> 32);
 #pragma unroll
   for (int r = 0; r < 10; ++r) {
@@ -649,6 +654,12 @@ void spec_slab(long long& ld, long long& bstride, int& per_head, int& hoff, int 
 }
 
 }  // namespace
+
+int rnn_internal_rng_advance_attn(unsigned long long inc, cudaStream_t stream) {
+  rng_advance_attn_kernel<<<1, 1, 0, stream>>>(inc);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
 
 extern "C" {
 

@@ -45,6 +45,9 @@ int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, 
                              const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                              float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream);
 
+int rnn_internal_rng_advance_ew(unsigned long long inc, cudaStream_t stream);
+int rnn_internal_rng_advance_attn(unsigned long long inc, cudaStream_t stream);
+
 typedef __nv_bfloat16 bf16;
 
 static inline int ceil_div_i(long long a, long long b) { return (int)((a + b - 1) / b); }

@@ -207,6 +207,12 @@ __device__ __forceinline__ uint4 philox4x32(uint2 key, uint4 ctr) {
   return ctr;
 }
 
+// Device-side RNG epoch: added to every Philox `offset` of this file.  It stays 0 unless rnn_rng_advance() is
+// used; a training step captured in a CUDA graph puts one rnn_rng_advance() at its head, so every replay draws new
+// dropout masks although the (seed, offset) kernel arguments are frozen in the graph.
+static __device__ unsigned long long g_rng_epoch_ew = 0ull;
+__global__ void rng_advance_ew_kernel(unsigned long long inc) { g_rng_epoch_ew += inc; }
+
 // y = x * keep / (1 - p); the keep mask is written as one byte per element for the backward pass.
 template <typename T>
 __global__ void dropout_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, uint8_t* __restrict__ mask, long long n,
@@ -214,6 +220,7 @@ __global__ void dropout_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, u
   const float inv_keep = 1.f / (1.f - p);
   const uint32_t thresh = (uint32_t)(p * 4294967296.0);
   const long long n4 = (n + 3) / 4;
+  offset += g_rng_epoch_ew;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
     const uint4 r = philox4x32(make_uint2((uint32_t)seed, (uint32_t)(seed >> 32)),
                                make_uint4((uint32_t)i, (uint32_t)(i >> 32), (uint32_t)offset, (uint32_t)(offset >> 32)));
@@ -238,6 +245,12 @@ __global__ void dropout_bwd_kernel(const T* __restrict__ dy, const uint8_t* __re
 }
 
 }  // namespace
+
+int rnn_internal_rng_advance_ew(unsigned long long inc, cudaStream_t stream) {
+  rng_advance_ew_kernel<<<1, 1, 0, stream>>>(inc);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
 
 extern "C" {
 

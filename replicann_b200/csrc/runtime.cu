@@ -39,4 +39,11 @@ const char* rnn_last_error(void) { return g_err; }
 int rnn_version(void) { return 100; }
 int rnn_sm_count(void) { return rnn_num_sms(); }
 unsigned long long rnn_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+/* Advance the device-side dropout epoch (one tiny kernel per Philox-using translation unit). */
+int rnn_rng_advance(cudaStream_t stream) {
+  const unsigned long long inc = 1ull << 32;   // host-side offsets are small call counters: epochs never collide
+  int rc = rnn_internal_rng_advance_ew(inc, stream);
+  if (rc != RNN_OK) return rc;
+  return rnn_internal_rng_advance_attn(inc, stream);
+}
 }

@@ -48,6 +48,12 @@ class _span:
         return False
 
 
+def rng_advance() -> None:
+    """Advance the device-side dropout epoch on the current stream (see rnn_rng_advance in the header): call it at
+    the head of a step that is being captured into a CUDA graph, so that every replay draws new dropout masks."""
+    check(_lib.load().rnn_rng_advance(cur_stream()), "rnn_rng_advance")
+
+
 def launch_count() -> int:
     return int(_lib.load().rnn_launch_count())
 

@@ -11,6 +11,7 @@ from __future__ import annotations
 
 import torch
 
+from . import functional as RF
 from .nn.layers import Dropout, cross_entropy
 
 
@@ -21,6 +22,7 @@ class Trainer:
         self._want_graph, self._graph_warmup = cuda_graph, graph_warmup
         self._graph = None
         self._eager_steps = 0
+        self._has_dropout = False
         self._gx = self._gy = self._gloss = None
         if cuda_graph:
             self._check_graph_safe()
@@ -45,9 +47,10 @@ class Trainer:
             raise ValueError("cuda_graph=True supports the SGD optimizer only (AdamW's step count is a host value)")
         # With data parallelism the bucketed all-reduces are captured too: they run on the communication
         # stream, which forks from / joins the capturing stream through events (NCCL collectives are capturable).
-        for m in self._model.modules():
-            if isinstance(m, Dropout) and m.p > 0 and self._model.training:
-                raise ValueError("cuda_graph=True needs a model without active dropout (the RNG counter is host-side)")
+        # Dropout is fine: the captured step starts with rnn_rng_advance(), which moves the device-side epoch every
+        # Philox-drawing kernel adds to its (frozen) offset argument, so each replay draws fresh masks.
+        self._has_dropout = any(isinstance(m, Dropout) or "Attention" in type(m).__name__
+                                for m in self._model.modules())
 
     def _eager_step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         self._opt.zero_grad()
@@ -71,9 +74,13 @@ class Trainer:
             # a failed NCCL capture must not take the other ranks down with a hang: relaxed capture mode lets
             # the communicator's own bookkeeping calls through
             with torch.cuda.graph(g, capture_error_mode="thread_local"):
+                if self._has_dropout:
+                    RF.rng_advance()
                 self._gloss = self._eager_step(self._gx, self._gy)
         else:
             with torch.cuda.graph(g):
+                if self._has_dropout:
+                    RF.rng_advance()
                 self._gloss = self._eager_step(self._gx, self._gy)
         self._graph = g
 

@@ -42,9 +42,8 @@ def test_cuda_graph_refuses_host_dependent_steps():
     m = _model()
     with pytest.raises(ValueError, match="SGD"):
         Trainer(m, AdamW(m.parameters(), lr=1e-3), cuda_graph=True)
-    a = AlexNet().cuda().to(torch.bfloat16)  # p_dropout = 0.5, training mode
-    with pytest.raises(ValueError, match="dropout"):
-        Trainer(a, SGD(a.parameters(), lr=0.1), cuda_graph=True)
+    a = AlexNet().cuda().to(torch.bfloat16)  # p_dropout = 0.5, training mode: accepted (device-side RNG epoch)
+    Trainer(a, SGD(a.parameters(), lr=0.1), cuda_graph=True)
 
 
 @pytest.mark.parametrize("graph", [False, True])
@@ -101,3 +100,27 @@ def test_vgg_alexnet_dropout_train_mode_runs():
     x, y = torch.randn(4, 3, 224, 224, generator=g).cuda(), torch.randint(0, 16, (4,), generator=g).cuda()
     l1, l2 = tr.step(x, y).item(), tr.step(x, y).item()
     assert l1 == l1 and l2 == l2
+
+
+def test_graph_step_with_dropout_draws_new_masks_every_replay():
+    """A captured step starts with rnn_rng_advance(): the Philox offsets frozen in the graph are shifted by a
+    device-side epoch, so consecutive replays of the SAME graph on the SAME batch must give different losses
+    (different dropout masks), while an eval-mode forward stays deterministic."""
+    import torch
+    from replicann_b200.arch.alexnet import AlexNet
+    from replicann_b200.optim import SGD
+    from replicann_b200.training import Trainer
+    torch.manual_seed(0)
+    m = AlexNet(n_classes=16, p_dropout=0.5).cuda().to(torch.bfloat16)
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(8, 3, 224, 224, generator=g).cuda()
+    y = torch.randint(0, 16, (8,), generator=g).cuda()
+    tr = Trainer(m, SGD(m.parameters(), lr=0.0), cuda_graph=True, graph_warmup=1)   # lr 0: weights stay put
+    losses = [float(tr.step(x, y).item()) for _ in range(6)]
+    assert tr.graph_captured
+    replayed = losses[1:]
+    assert len({round(v, 6) for v in replayed}) >= 4, replayed       # fresh masks on (nearly) every replay
+    m.eval()
+    with torch.no_grad():
+        a, b = m(x), m(x)
+    assert torch.equal(a, b)
