@@ -309,6 +309,13 @@ int rnn_adamw_step(float* w, float* m, float* v, const void* grad, int grad_bf16
                    long long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                    float grad_scale, cudaStream_t stream);
 
+/* AdamW with the step count in device memory, and the kernel that moves such a counter: a step built from these
+ * has no host-side value that changes between steps, so it can be captured once and replayed (CUDA graph). */
+int rnn_adamw_step_dev(float* w, float* m, float* v, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16,
+                       long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                       const long long* step_dev, float grad_scale, cudaStream_t stream);
+int rnn_counter_add(long long* counter, long long inc, cudaStream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -57,7 +57,12 @@ template <typename G, typename Wc>
 __global__ void __launch_bounds__(256)
 adamw_kernel(float* __restrict__ w, float* __restrict__ m, float* __restrict__ v, const G* __restrict__ grad,
              Wc* __restrict__ wcopy, long long n, float lr, float b1, float b2, float eps, float wd, float bc1,
-             float bc2_sqrt, float gscale) {
+             float bc2_sqrt, float gscale, const long long* __restrict__ step_dev) {
+  if (step_dev != nullptr) {   // step count kept on the device (CUDA-graph replays): bias corrections from it
+    const float st = (float)(*step_dev);
+    bc1 = 1.f - powf(b1, st);
+    bc2_sqrt = sqrtf(1.f - powf(b2, st));
+  }
   for (long long i = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n;
        i += (long long)gridDim.x * blockDim.x * 4) {
     float p[4], g[4], mm[4], vv[4];
@@ -87,6 +92,8 @@ int ogrid(long long n) {
   return (int)(b > cap ? cap : (b < 1 ? 1 : b));
 }
 
+__global__ void counter_add_kernel(long long* c, long long inc) { *c += inc; }
+
 }  // namespace
 
 extern "C" {
@@ -110,6 +117,20 @@ int rnn_sgd_step(float* w, float* buf, const void* grad, int grad_bf16, void* wc
   return RNN_OK;
 }
 
+static int adamw_launch(float* w, float* m, float* v, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16,
+                        long long n, float lr, float beta1, float beta2, float eps, float weight_decay, float bc1,
+                        float bc2s, const long long* step_dev, float grad_scale, cudaStream_t stream) {
+  const int g = ogrid(n);
+#define ADAM_LAUNCH(G, W) \
+  adamw_kernel<G, W><<<g, 256, 0, stream>>>(w, m, v, (const G*)grad, (W*)wcopy, n, lr, beta1, beta2, eps, weight_decay, \
+                                            bc1, bc2s, grad_scale, step_dev)
+  if (grad_bf16) { if (wcopy_bf16) ADAM_LAUNCH(bf16, bf16); else ADAM_LAUNCH(bf16, float); }
+  else { if (wcopy_bf16) ADAM_LAUNCH(float, bf16); else ADAM_LAUNCH(float, float); }
+#undef ADAM_LAUNCH
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
 int rnn_adamw_step(float* w, float* m, float* v, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16,
                    long long n, float lr, float beta1, float beta2, float eps, float weight_decay, int step,
                    float grad_scale, cudaStream_t stream) {
@@ -117,13 +138,23 @@ int rnn_adamw_step(float* w, float* m, float* v, const void* grad, int grad_bf16
   if (n == 0) return RNN_OK;
   const float bc1 = 1.f - powf(beta1, (float)step);
   const float bc2s = sqrtf(1.f - powf(beta2, (float)step));
-  const int g = ogrid(n);
-#define ADAM_LAUNCH(G, W) \
-  adamw_kernel<G, W><<<g, 256, 0, stream>>>(w, m, v, (const G*)grad, (W*)wcopy, n, lr, beta1, beta2, eps, weight_decay, \
-                                            bc1, bc2s, grad_scale)
-  if (grad_bf16) { if (wcopy_bf16) ADAM_LAUNCH(bf16, bf16); else ADAM_LAUNCH(bf16, float); }
-  else { if (wcopy_bf16) ADAM_LAUNCH(float, bf16); else ADAM_LAUNCH(float, float); }
-#undef ADAM_LAUNCH
+  return adamw_launch(w, m, v, grad, grad_bf16, wcopy, wcopy_bf16, n, lr, beta1, beta2, eps, weight_decay, bc1, bc2s,
+                      nullptr, grad_scale, stream);
+}
+
+/* Same update with the step count read from device memory (*step_dev >= 1 when the kernel runs): nothing about the
+ * call changes from step to step, so it can be replayed from a CUDA graph.  rnn_counter_add moves the counter. */
+int rnn_adamw_step_dev(float* w, float* m, float* v, const void* grad, int grad_bf16, void* wcopy, int wcopy_bf16,
+                       long long n, float lr, float beta1, float beta2, float eps, float weight_decay,
+                       const long long* step_dev, float grad_scale, cudaStream_t stream) {
+  RNN_REQUIRE(n >= 0 && n % 4 == 0 && step_dev != nullptr, RNN_ERR_SHAPE);
+  if (n == 0) return RNN_OK;
+  return adamw_launch(w, m, v, grad, grad_bf16, wcopy, wcopy_bf16, n, lr, beta1, beta2, eps, weight_decay, 1.f, 1.f,
+                      step_dev, grad_scale, stream);
+}
+int rnn_counter_add(long long* counter, long long inc, cudaStream_t stream) {
+  RNN_REQUIRE(counter != nullptr, RNN_ERR_SHAPE);
+  counter_add_kernel<<<1, 1, 0, stream>>>(counter, inc);
   RNN_CHECK_LAUNCH();
   return RNN_OK;
 }

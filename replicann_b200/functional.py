@@ -703,12 +703,23 @@ def sgd_step(w, buf, grad, wcopy, *, lr, momentum=0.0, dampening=0.0, weight_dec
                            float(grad_scale), cur_stream()), "rnn_sgd_step")
 
 
-def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, step=1, grad_scale=1.0):
+def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, step=1, grad_scale=1.0,
+               step_dev=None):
+    """step_dev: int64 device tensor holding the step count (>= 1 when the kernel runs); overrides `step`."""
     lib = _lib.load(); _req(w, torch.float32, "w")
-    check(lib.rnn_adamw_step(ptr(w), ptr(m), ptr(v), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
-                             int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
-                             float(betas[0]), float(betas[1]), float(eps), float(weight_decay), int(step),
-                             float(grad_scale), cur_stream()), "rnn_adamw_step")
+    common = (ptr(w), ptr(m), ptr(v), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
+              int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
+              float(betas[0]), float(betas[1]), float(eps), float(weight_decay))
+    if step_dev is not None:
+        _req(step_dev, torch.int64, "step_dev")
+        check(lib.rnn_adamw_step_dev(*common, ptr(step_dev), float(grad_scale), cur_stream()), "rnn_adamw_step_dev")
+    else:
+        check(lib.rnn_adamw_step(*common, int(step), float(grad_scale), cur_stream()), "rnn_adamw_step")
+
+
+def counter_add(counter: torch.Tensor, inc: int = 1) -> None:
+    _req(counter, torch.int64, "counter")
+    check(_lib.load().rnn_counter_add(ptr(counter), int(inc), cur_stream()), "rnn_counter_add")
 
 
 # =========================================================================================== attention

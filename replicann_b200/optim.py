@@ -131,12 +131,32 @@ class AdamW(_FlatOptimizer):
                  weight_decay: float = 1e-2) -> None:
         super().__init__(params)
         self.lr, self.betas, self.eps, self.weight_decay = lr, betas, eps, weight_decay
+        self._step_dev = None   # int64 step count on the device: nothing host-side changes from step to step
+
+    def _device_steps(self) -> torch.Tensor:
+        if self._step_dev is None:
+            self._step_dev = torch.full((1,), self._steps, dtype=torch.int64, device=self.groups[0].master.device)
+        return self._step_dev
+
+    def state_dict(self) -> dict:
+        if self._step_dev is not None:
+            self._steps = int(self._step_dev.item())   # replays of a captured step do not pass through step()
+        return super().state_dict()
+
+    def load_state_dict(self, sd: dict) -> None:
+        super().load_state_dict(sd)
+        if self._step_dev is not None:
+            self._step_dev.fill_(self._steps)
 
     @torch.no_grad()
     def step(self) -> None:
+        """The bias corrections are computed on the device from a device-side step counter, so the same sequence
+        of launches serves every step (and can be replayed from a CUDA graph)."""
+        cnt = self._device_steps()
         self._steps += 1
+        RF.counter_add(cnt, 1)
         for g in self.groups:
             wcopy = None if g.master is g.work else g.work
             RF.adamw_step(g.master, g.zeros_state("exp_avg"), g.zeros_state("exp_avg_sq"), g.grad, wcopy, lr=self.lr,
-                          betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step=self._steps,
+                          betas=self.betas, eps=self.eps, weight_decay=self.weight_decay, step_dev=cnt,
                           grad_scale=self.grad_scale)

@@ -42,9 +42,9 @@ class Trainer:
     def _check_graph_safe(self) -> None:
         """A captured step replays identical kernel arguments, so anything that must change from step to
         step on the host side (dropout counters, Adam's bias correction, NCCL work handles) rules it out."""
-        from .optim import SGD
-        if not isinstance(self._opt, SGD):
-            raise ValueError("cuda_graph=True supports the SGD optimizer only (AdamW's step count is a host value)")
+        from .optim import SGD, AdamW
+        if not isinstance(self._opt, (SGD, AdamW)):
+            raise ValueError("cuda_graph=True supports this package's SGD and AdamW (fused, no host-side step state)")
         # With data parallelism the bucketed all-reduces are captured too: they run on the communication
         # stream, which forks from / joins the capturing stream through events (NCCL collectives are capturable).
         # Dropout is fine: the captured step starts with rnn_rng_advance(), which moves the device-side epoch every

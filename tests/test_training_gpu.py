@@ -35,13 +35,25 @@ def test_cuda_graph_step_matches_eager_step():
     assert all(l == l and abs(l) < 1e4 for l in losses[False])   # finite
 
 
-def test_cuda_graph_refuses_host_dependent_steps():
+def test_cuda_graph_accepts_adamw_and_dropout():
+    """AdamW keeps its step count on the device and dropout draws from a device-side epoch, so neither rules a
+    captured step out any more: the AdamW graph step must replay the eager AdamW step bit for bit."""
     from replicann_b200.arch.alexnet import AlexNet
     from replicann_b200.optim import SGD, AdamW
     from replicann_b200.training import Trainer
-    m = _model()
-    with pytest.raises(ValueError, match="SGD"):
-        Trainer(m, AdamW(m.parameters(), lr=1e-3), cuda_graph=True)
+    data = _batches(7)
+    res = {}
+    for graph in (False, True):
+        m = _model()
+        opt = AdamW(m.parameters(), lr=1e-3, weight_decay=1e-2)
+        tr = Trainer(m, opt, cuda_graph=graph)
+        res[graph] = [tr.step(x.cuda(), y.cuda()).item() for x, y in data]
+        res[(graph, "w")] = torch.cat([p.detach().float().flatten() for p in m.parameters()])
+        assert opt.state_dict()["steps"] == len(data)
+        if graph:
+            assert tr.graph_captured
+    assert res[True] == res[False]
+    assert torch.equal(res[(True, "w")], res[(False, "w")])
     a = AlexNet().cuda().to(torch.bfloat16)  # p_dropout = 0.5, training mode: accepted (device-side RNG epoch)
     Trainer(a, SGD(a.parameters(), lr=0.1), cuda_graph=True)
 
