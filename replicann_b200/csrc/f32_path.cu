@@ -274,10 +274,10 @@ relu_bwd_colsum_kernel(const T* __restrict__ dy, const T* __restrict__ y, T* __r
   }
 }
 
-// row blocks of the vector form: every thread sees >= 4 rows, about 4 resident blocks per SM in total
+// row blocks of the vector form: every thread sees >= 16 rows, at most about 4 resident blocks per SM in total
 int colsum_vec_rows(long long M, int C, int W) {
   const int cgs = C / W, tpr = cgs < 256 ? cgs : 256, rpp = 256 / tpr, gx = (cgs + tpr - 1) / tpr;
-  long long gy = (M + (long long)rpp * 4 - 1) / ((long long)rpp * 4);
+  long long gy = (M + (long long)rpp * 16 - 1) / ((long long)rpp * 16);   // >= 16 rows per thread: few partial rows
   long long cap = (long long)rnn_num_sms() * 4 / gx;
   if (cap < 1) cap = 1;
   if (gy > cap) gy = cap;

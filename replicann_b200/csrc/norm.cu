@@ -601,7 +601,7 @@ layernorm_bwd_finalize_kernel(const float* __restrict__ partials, int nparts, in
 }
 
 int ln_bwd_blocks(long long M) {
-  long long b = (M + 7) / 8;
+  long long b = (M + 31) / 32;   // 8 warps per block, >= 4 rows per warp: the per-block partial rows are the overhead
   const long long cap = (long long)rnn_num_sms() * 2;
   return (int)(b > cap ? cap : (b < 1 ? 1 : b));
 }
