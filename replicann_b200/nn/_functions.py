@@ -169,9 +169,15 @@ class FirstConv2dFn(Function):
         xp, weight, bias, y = ctx.saved_tensors
         d, sg = ctx.d, ctx.sg
         dyh = nhwc(dy)
-        if ctx.relu:
-            dyh = RF.relu_bwd(dyh, y)
         dw = db = None
+        want_db = bias is not None and ctx.needs_input_grad[2]
+        if ctx.relu and want_db and bias.is_leaf:
+            box = []   # ReLU backward and the bias gradient in one pass over dy
+            _write_param_grad(bias, lambda out, acc: box.append(RF.relu_bwd_colsum(dyh, y, out=out, accumulate=acc)))
+            dyh = box[0]
+            want_db = False
+        elif ctx.relu:
+            dyh = RF.relu_bwd(dyh, y)
         if ctx.needs_input_grad[1]:
             def wg(out, acc):
                 g = RF.first_conv_wgrad(xp, dyh, d, sg)
@@ -181,7 +187,7 @@ class FirstConv2dFn(Function):
                 else:
                     out.copy_(gv)
             dw = _write_param_grad(weight, wg)
-        if bias is not None and ctx.needs_input_grad[2]:
+        if want_db:
             K = dyh.shape[-1]
             db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
         return None, dw, db, None, None, None
