@@ -172,6 +172,42 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
   PV<T, VEC>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, acc);
 }
 
+// Backward of NON-OVERLAPPING windows (kernel == stride, no padding; VGG's 2x2/2 pools): every input element belongs
+// to exactly one window, so a thread owns one window, reads its dy / argmax once and writes the R*S input elements
+// (dy at the argmax, zero elsewhere).  Rows / columns beyond the last full window get zeros from the tail threads.
+template <typename T, int K>
+__global__ void __launch_bounds__(256)
+maxpool_bwd_tiled_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ widx, T* __restrict__ dx,
+                         PoolGeom g, int cgs_shift) {
+  constexpr int VW = PV<T, true>::W;
+  const int cgs = g.C / VW;
+  const int Qx = (g.W + K - 1) / K;                 // windows per row including a partial last one
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= Qx * cgs) return;
+  const int q = cgs_shift >= 0 ? (e >> cgs_shift) : (int)((unsigned)e / (unsigned)cgs);
+  const int cg = e - q * cgs;
+  const int p = blockIdx.y, n = blockIdx.z;         // p over ceil(H / K)
+  float d[VW];
+  int l[VW];
+  const bool full = p < g.P && q < g.Q;
+  if (full) {
+    const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
+    PV<T, true>::load(dy + o, d);
+    WIdx<VW>::load(widx + o, l);
+  }
+#pragma unroll
+  for (int r = 0; r < K; ++r)
+#pragma unroll
+    for (int sx = 0; sx < K; ++sx) {
+      const int h = p * K + r, w = q * K + sx;
+      if (h >= g.H || w >= g.W) continue;
+      float o[VW];
+#pragma unroll
+      for (int e2 = 0; e2 < VW; ++e2) o[e2] = (full && l[e2] == r * K + sx) ? d[e2] : 0.f;
+      PV<T, true>::store(dx + (((long long)n * g.H + h) * g.W + w) * g.C + cg * VW, o);
+    }
+}
+
 // count_include_pad = True, ceil_mode = False (torch defaults): divisor is always R*S.
 template <typename T, bool VEC>
 __global__ void __launch_bounds__(256)
@@ -371,6 +407,12 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
   const int sh_ = pow2_shift(cgs);
   const dim3 grid(ceil_div_i((long long)W * cgs, 256), H, N);
   const int fx = fixed_geometry(g);
+  if (!is_f32 && vec && window_idx != nullptr && fx == 2) {   // 2x2 stride 2, no padding: non-overlapping windows
+    const dim3 tg(ceil_div_i((long long)((W + 1) / 2) * cgs, 256), (H + 1) / 2, N);
+    maxpool_bwd_tiled_kernel<bf16, 2><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    RNN_CHECK_LAUNCH();
+    return RNN_OK;
+  }
   if (is_f32) {
     if (vec) maxpool_bwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
     else maxpool_bwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
