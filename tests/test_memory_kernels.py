@@ -121,7 +121,7 @@ def test_layernorm(dtype, tol, M, E, res):
 # ------------------------------------------------------------------------------------------ pooling
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("N,H,W,C,k,s,p", [(2, 112, 112, 64, 3, 2, 1), (2, 13, 13, 16, 3, 2, 0), (3, 28, 28, 8, 2, 2, 0),
-                                            (1, 7, 9, 24, 3, 1, 1), (2, 9, 7, 16, 2, 2, 0)])
+                                            (1, 7, 9, 24, 3, 1, 1), (2, 9, 7, 16, 2, 2, 0), (2, 15, 11, 8, 3, 2, 1)])
 def test_maxpool_indices_bit_exact(dtype, N, H, W, C, k, s, p):
     f = RF()
     x = rnd((N, H, W, C), 1, dtype)
