@@ -139,6 +139,15 @@ int rnn_nchw_f32_to_nhwc_bf16(const float* x, void* y, int N, int C, int H, int 
 /* Same, into a spatially zero-padded [N, Hp, Wp, Cpad] buffer (image at rows pad_h.., columns pad_w..). */
 int rnn_nchw_f32_to_nhwc_bf16_padded(const float* x, void* y, int N, int C, int H, int W, int Cpad, int pad_h,
                                      int pad_w, int Hp, int Wp, cudaStream_t stream);
+/* The same two conversions with the image pipeline's per-channel normalisation folded in (SURVEY 8f.2:
+ * "fp32 NCHW -> bf16 NHWC conversion + normalisation"; torchvision's Normalize(mean, std), which the reference's
+ * notebooks would apply on the host): v = (x - mean[c]) * inv_std[c] before the bf16 rounding.  mean / inv_std are
+ * device arrays of C floats, both NULL = no normalisation.  Padding (channels, borders) stays exactly zero. */
+int rnn_nchw_f32_to_nhwc_bf16_norm(const float* x, void* y, int N, int C, int H, int W, int Cpad, const float* mean,
+                                   const float* inv_std, cudaStream_t stream);
+int rnn_nchw_f32_to_nhwc_bf16_padded_norm(const float* x, void* y, int N, int C, int H, int W, int Cpad, int pad_h,
+                                          int pad_w, int Hp, int Wp, const float* mean, const float* inv_std,
+                                          cudaStream_t stream);
 int rnn_nhwc_bf16_to_nchw_f32(const void* x, float* y, int N, int C, int H, int W, int Cpad, cudaStream_t stream);
 /* F.relu (arch/transformer.py:30) and its autograd: dx = dy * (y > 0). */
 int rnn_relu_fwd(const void* x, void* y, long long n, int is_f32, cudaStream_t stream);

@@ -11,9 +11,11 @@ from ._stem import prepare_input
 
 
 class AlexNet(nn.Module):
-    def __init__(self, *, n_classes: int = 1000, p_dropout: float = 0.5) -> None:
+    def __init__(self, *, n_classes: int = 1000, p_dropout: float = 0.5, input_mean=None, input_std=None) -> None:
         super().__init__()
         self._conv1 = Conv2d(3, 64, 11, 4, 2, relu=True)
+        if input_mean is not None:   # per-channel image normalisation, fused into the input layout kernel
+            self._conv1.set_input_normalization(input_mean, input_std)
         self._pool1 = MaxPool2d(3, 2)
         self._conv2 = Conv2d(64, 192, 5, 1, 2, relu=True)
         self._pool2 = MaxPool2d(3, 2)

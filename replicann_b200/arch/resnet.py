@@ -86,10 +86,12 @@ class _BasicBlock(nn.Module):
 
 class ResNet(nn.Module):
     def __init__(self, layers: tuple[int, ...] = (3, 4, 6, 3), *, bottleneck: bool = True, n_classes: int = 1000,
-                 in_channels: int = 3, base_width: int = 64) -> None:
+                 in_channels: int = 3, base_width: int = 64, input_mean=None, input_std=None) -> None:
         super().__init__()
         block = _Bottleneck if bottleneck else _BasicBlock
         self._conv1 = Conv2d(in_channels, base_width, 7, 2, 3, bias=False)
+        if input_mean is not None:   # per-channel image normalisation, fused into the input layout kernel
+            self._conv1.set_input_normalization(input_mean, input_std)
         self._bn1 = BatchNorm2d(base_width, relu=True)
         self._maxpool = MaxPool2d(3, 2, 1)
         stages = []

@@ -12,7 +12,8 @@ _CFG_D = (64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 51
 
 
 class VGG(nn.Module):
-    def __init__(self, cfg=_CFG_D, *, n_classes: int = 1000, p_dropout: float = 0.5, hidden_size: int = 4096) -> None:
+    def __init__(self, cfg=_CFG_D, *, n_classes: int = 1000, p_dropout: float = 0.5, hidden_size: int = 4096,
+                 input_mean=None, input_std=None) -> None:
         super().__init__()
         feats = []
         ch = 3
@@ -23,6 +24,8 @@ class VGG(nn.Module):
                 feats.append(Conv2d(ch, v, 3, 1, 1, relu=True))
                 ch = v
         self._features = nn.ModuleList(feats)
+        if input_mean is not None:   # per-channel image normalisation, fused into the input layout kernel
+            self._features[0].set_input_normalization(input_mean, input_std)
         self._avgpool = AdaptiveAvgPool2d((7, 7))
         self._flatten = Flatten()
         self._fc1 = Linear(ch * 7 * 7, hidden_size, relu=True)

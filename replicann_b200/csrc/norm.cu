@@ -12,6 +12,8 @@
 #include "common.cuh"
 #include <stdlib.h>
 
+#include <atomic>
+
 namespace {
 
 // --------------------------------------------------------------------------------- BatchNorm
@@ -621,20 +623,26 @@ static __device__ __align__(256) unsigned char g_bn_static_scratch[RNN_BN_STATIC
 
 namespace {
 constexpr int kMaxDevices = 64;
-float* g_bn_static_addr[kMaxDevices] = {nullptr};
+// One slot per device ordinal.  Host threads may make their first call on a device at the same time: each then
+// looks the address up for itself and stores the same value, so an atomic slot (no lock) is all that is needed.
+// A cudaDeviceReset() destroys the context the address belongs to; the cached value is then stale, so do not
+// reset a device between calls of rnn_bn_stats_bf16_static on it.
+std::atomic<float*> g_bn_static_addr[kMaxDevices];
 
 // Resolve (first use on this device) or fetch (later uses) the device address of the built-in scratch.
 int bn_static_scratch_address(float** out) {
   int dev = -1;
   RNN_CUDA(cudaGetDevice(&dev));
   RNN_REQUIRE(dev >= 0 && dev < kMaxDevices, RNN_ERR_CUDA);
-  if (g_bn_static_addr[dev] == nullptr) {
+  float* addr = g_bn_static_addr[dev].load(std::memory_order_acquire);
+  if (addr == nullptr) {
     void* p = nullptr;
     RNN_CUDA(cudaGetSymbolAddress(&p, g_bn_static_scratch));
     RNN_REQUIRE(p != nullptr, RNN_ERR_CUDA);
-    g_bn_static_addr[dev] = reinterpret_cast<float*>(p);
+    addr = reinterpret_cast<float*>(p);
+    g_bn_static_addr[dev].store(addr, std::memory_order_release);
   }
-  *out = g_bn_static_addr[dev];
+  *out = addr;
   return RNN_OK;
 }
 }  // namespace

@@ -251,15 +251,28 @@ def first_conv_geometry(d):
     return hp.value, wp.value, sg.value
 
 
-def pack_first_input(x_nchw_f32, d):
-    """fp32 NCHW images -> bf16 [N, Hp, Wp, 8], spatially zero-padded, channels padded to 8."""
+def _norm_args(mean, inv_std, Cn):
+    if (mean is None) != (inv_std is None):
+        raise ValueError("give both mean and inv_std, or neither")
+    if mean is not None:
+        _req(mean, torch.float32, "mean"); _req(inv_std, torch.float32, "inv_std")
+        if mean.numel() != Cn or inv_std.numel() != Cn:
+            raise ValueError(f"mean / inv_std must have {Cn} entries (one per input channel)")
+
+
+def pack_first_input(x_nchw_f32, d, mean=None, inv_std=None):
+    """fp32 NCHW images -> bf16 [N, Hp, Wp, 8], spatially zero-padded, channels padded to 8; optional per-channel
+    normalisation (x - mean) * inv_std in the same pass."""
     lib = _lib.load()
     _req(x_nchw_f32, torch.float32, "x")
     hp, wp, _ = first_conv_geometry(d)
     N, Cn, H, W = x_nchw_f32.shape
+    _norm_args(mean, inv_std, Cn)
     y = torch.empty((N, hp, wp, 8), dtype=torch.bfloat16, device=x_nchw_f32.device)
-    check(lib.rnn_nchw_f32_to_nhwc_bf16_padded(ptr(x_nchw_f32), ptr(y), N, Cn, H, W, 8, d.pad_h, d.pad_w, hp, wp,
-                                               cur_stream()), "rnn_nchw_f32_to_nhwc_bf16_padded")
+    with _span("layout", 4.0 * N * Cn * H * W + 16.0 * N * hp * wp, f"N{N} C{Cn} {H}x{W} -> {hp}x{wp}x8"):
+        check(lib.rnn_nchw_f32_to_nhwc_bf16_padded_norm(ptr(x_nchw_f32), ptr(y), N, Cn, H, W, 8, d.pad_h, d.pad_w, hp,
+                                                        wp, ptr(mean), ptr(inv_std), cur_stream()),
+              "rnn_nchw_f32_to_nhwc_bf16_padded_norm")
     return y
 
 
@@ -399,13 +412,16 @@ def colsum(x2d, *, out=None, accumulate=False):
 
 
 # =========================================================================================== elementwise
-def nchw_to_nhwc_bf16(x, cpad=None):
+def nchw_to_nhwc_bf16(x, cpad=None, mean=None, inv_std=None):
     lib = _lib.load()
     _req(x, torch.float32, "x")
     N, Cn, H, W = x.shape
     cp = cpad or Cn
+    _norm_args(mean, inv_std, Cn)
     y = torch.empty((N, H, W, cp), dtype=torch.bfloat16, device=x.device)
-    check(lib.rnn_nchw_f32_to_nhwc_bf16(ptr(x), ptr(y), N, Cn, H, W, cp, cur_stream()), "rnn_nchw_f32_to_nhwc_bf16")
+    with _span("layout", 4.0 * N * Cn * H * W + 2.0 * N * H * W * cp, f"N{N} C{Cn} {H}x{W} -> C{cp}"):
+        check(lib.rnn_nchw_f32_to_nhwc_bf16_norm(ptr(x), ptr(y), N, Cn, H, W, cp, ptr(mean), ptr(inv_std), cur_stream()),
+              "rnn_nchw_f32_to_nhwc_bf16_norm")
     return y
 
 
@@ -739,11 +755,43 @@ def _attn_desc(B, H, T, Tk, hs, q, k, v, z, dz, scale, mask, p_drop, seed, offse
         d.mask_kind = 0
     else:
         d.mask_kind = 1 if mask.dtype in (torch.bool, torch.uint8) else 2
+        if mask.stride(-1) != 1 and mask.shape[-1] != 1:
+            raise ValueError("mask must have unit stride in its last dimension")
         if mask.dim() == 2:
+            if tuple(mask.shape) != (T, Tk):
+                raise ValueError(f"mask shape {tuple(mask.shape)} != ({T}, {Tk}); use broadcast_mask()")
             d.mask_bs, d.mask_rs = 0, mask.stride(0)
         else:
+            if mask.shape[0] not in (1, B) or tuple(mask.shape[1:]) != (T, Tk):
+                raise ValueError(f"mask shape {tuple(mask.shape)} != ({B}, {T}, {Tk}); use broadcast_mask()")
             d.mask_bs, d.mask_rs = (mask.stride(0) if mask.shape[0] > 1 else 0), mask.stride(1)
     return d
+
+
+def broadcast_mask(mask, q, k, v, n_heads, hs):
+    """Validate q / k / v against each other and bring `mask` to the [B, T, Tk] view the kernels index.
+
+    The reference applies the mask with `w.masked_fill(mask, -inf)` / `w += mask` on w [B, T, Tk]
+    (nn/attention.py:39-42), so anything that broadcasts TO that shape is legal -- [Tk], [1, Tk], [T, 1],
+    [B, 1, Tk], ... -- and anything else raises torch's broadcast RuntimeError.  The broadcast is a stride-0
+    view (the kernels take a batch and a row stride); only a mask whose last dimension is itself broadcast is
+    materialised."""
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        if t.dim() != 3:
+            raise ValueError(f"{n} must be [B, T, H*hs], got shape {tuple(t.shape)}")
+    B, T, Tk = q.shape[0], q.shape[1], k.shape[1]
+    width = n_heads * hs
+    if q.shape[-1] != width or k.shape[-1] != width or v.shape[-1] != width:
+        raise ValueError(f"q / k / v must have {n_heads} x {hs} = {width} features, got "
+                         f"{q.shape[-1]}, {k.shape[-1]}, {v.shape[-1]}")
+    if k.shape[0] != B or v.shape[0] != B or v.shape[1] != Tk:
+        raise ValueError(f"k / v must be [{B}, Tk, {width}] with the same Tk, got {tuple(k.shape)} and {tuple(v.shape)}")
+    if mask is None:
+        return None
+    if mask.dim() > 3:
+        raise RuntimeError(f"mask of shape {tuple(mask.shape)} does not broadcast to the attention weights [{B}, {T}, {Tk}]")
+    m = mask.expand(B, T, Tk)   # raises torch's RuntimeError when the shapes do not broadcast
+    return m if m.stride(-1) == 1 or Tk == 1 else m.contiguous()
 
 
 def _req_dtype(t, dtype, name):

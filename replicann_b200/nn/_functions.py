@@ -149,13 +149,14 @@ class FirstConv2dFn(Function):
     gradient is produced (images do not require grad)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu):
+    def forward(ctx, x, weight, bias, stride, pad, relu, norm=None):
         from .._lib import conv_desc
         N, Cn, H, W = x.shape
         K, _, R, S = weight.shape
         d = conv_desc(N, H, W, Cn, K, R, S, stride, pad)
         _, _, sg = RF.first_conv_geometry(d)
-        xp = RF.pack_first_input(x if x.is_contiguous() else x.contiguous(), d)
+        mean, inv_std = norm if norm is not None else (None, None)
+        xp = RF.pack_first_input(x if x.is_contiguous() else x.contiguous(), d, mean, inv_std)
         # filter [K,C,R,S] -> [K,R,SG*8 taps,8 ch] with zeros beyond S and C (tiny; data movement only)
         wp = torch.zeros((K, R, sg * 8, 8), dtype=weight.dtype, device=weight.device)
         wp[:, :, :S, :Cn].copy_(weight.detach().permute(0, 2, 3, 1))
@@ -190,7 +191,7 @@ class FirstConv2dFn(Function):
         if want_db:
             K = dyh.shape[-1]
             db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
-        return None, dw, db, None, None, None
+        return None, dw, db, None, None, None, None
 
 
 def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
@@ -255,6 +256,94 @@ class LinearFn(Function):
         return dx, dw, db, None
 
 
+class PackedLinearFn(Function):
+    """y = x . W^T (+ b) where W stacks the weights of several nn.Linear modules row-wise -- the per-head q / k / v
+    projections of a multi-head attention module (reference nn/attention.py:85-96, 149-192 runs them one head at a
+    time and concatenates) as ONE tcgen05 GEMM.
+
+    `pack` = (W view, dW view, b view | None, db view | None) into the flat optimizer buffers when the member
+    parameters are laid out back to back there (optim.ParamPack): nothing is concatenated and the weight gradient
+    is written in place.  `pack` = None: W is assembled with one torch.cat of the members and the gradient is
+    scattered back into each member's .grad (honouring the optimizer's overwrite / accumulate state), so either way
+    no gradient reaches the members through autograd's AccumulateGrad.
+    The member parameters are passed as inputs only so that the node exists when x itself needs no gradient."""
+
+    @staticmethod
+    def forward(ctx, x, relu, n_w, pack, *members):
+        ws, bs = members[:n_w], members[n_w:]
+        if pack is not None:
+            w, gw, b, gb = pack
+        else:
+            w = torch.cat([m.detach() for m in ws], dim=0)
+            b = torch.cat([m.detach() for m in bs], dim=0) if bs else None
+            gw = gb = None
+        x2 = x.reshape(-1, x.shape[-1])
+        if not x2.is_contiguous():
+            x2 = x2.contiguous()
+        if w.dtype == torch.float32:
+            y = RF.gemm_f32(x2, w, bias=b, relu=relu)
+        else:
+            y = RF.gemm(x2, w, bias=_bias_f32(b), relu=relu)
+        ctx.relu, ctx.xshape, ctx.n_w = relu, x.shape, n_w
+        ctx.members, ctx.gw, ctx.gb = members, gw, gb
+        ctx.save_for_backward(x2, w, y if relu else None)
+        return y.reshape(*x.shape[:-1], w.shape[0])
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, w, y = ctx.saved_tensors
+        ws, bs = ctx.members[:ctx.n_w], ctx.members[ctx.n_w:]
+        dy2 = dy.reshape(-1, w.shape[0])
+        if not dy2.is_contiguous():
+            dy2 = dy2.contiguous()
+        if ctx.relu:
+            dy2 = RF.relu_bwd(dy2, y)
+        f32 = w.dtype == torch.float32
+
+        def state(ms):
+            """overwrite / accumulate state of a member list: all members of a pack move together"""
+            acc = [grad_target(m)[1] for m in ms]
+            if any(a != acc[0] for a in acc):
+                raise RuntimeError("packed parameters have diverging gradient state")
+            return acc[0]
+
+        def wgrad(out, acc):
+            if f32:
+                RF.gemm_f32(dy2, x2, a_mn=True, b_mn=True, out=out, accumulate=acc)
+            elif not acc:
+                RF.gemm(dy2, x2, a_mn=True, b_mn=True, out=out)
+            else:
+                RF.add(out, RF.gemm(dy2, x2, a_mn=True, b_mn=True), out=out)
+
+        if ws[0].requires_grad:
+            if ctx.gw is not None:
+                wgrad(ctx.gw, state(ws))
+            else:
+                g = torch.empty_like(w)
+                wgrad(g, False)
+                n = ws[0].shape[0]
+                for i, m in enumerate(ws):
+                    tgt, acc = grad_target(m)
+                    (tgt.add_ if acc else tgt.copy_)(g[i * n:(i + 1) * n])
+            for m in ws:
+                _notify(m)
+        if bs and bs[0].requires_grad:
+            if ctx.gb is not None:
+                RF.colsum(dy2, out=ctx.gb, accumulate=state(bs))
+            else:
+                g = RF.colsum(dy2)
+                n = bs[0].shape[0]
+                for i, m in enumerate(bs):
+                    tgt, acc = grad_target(m)
+                    (tgt.add_ if acc else tgt.copy_)(g[i * n:(i + 1) * n])
+            for m in bs:
+                _notify(m)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = (RF.gemm_f32(dy2, w, b_mn=True) if f32 else RF.gemm(dy2, w, b_mn=True)).reshape(ctx.xshape)
+        return (dx, None, None, None) + (None,) * len(ctx.members)
+
+
 # ------------------------------------------------------------------------------------------ BatchNorm2d
 class BatchNormFn(Function):
     """y = relu(BN(x) + residual) with batch statistics (training) or running statistics (eval)."""
@@ -295,7 +384,8 @@ class BatchNormFn(Function):
         if need_g:
             dg, acc = grad_target(gamma)
             db, acc_b = grad_target(beta)
-            acc = acc or acc_b
+            if acc != acc_b:
+                raise RuntimeError("BatchNorm weight/bias gradient state out of sync")
         else:
             dg = db = None
             acc = False
@@ -503,6 +593,7 @@ class AttentionFn(Function):
             q = q_or_qkv if q_or_qkv.stride(-1) == 1 else q_or_qkv.contiguous()
             k = k if k.stride(-1) == 1 else k.contiguous()
             v = v if v.stride(-1) == 1 else v.contiguous()
+        mask = RF.broadcast_mask(mask, q, k, v, n_heads, hs)
         # bf16 with a 64-multiple head size: contractions on the tensor cores (batched tcgen05 GEMMs over all heads);
         # anything else: the fused fp32-FMA kernel
         # fp32 large enough to pay for operand splits: the same pipeline at fp32 accuracy (three-piece bf16 splits)

@@ -21,6 +21,7 @@ import torch
 import torch.nn as nn
 from torch import Tensor
 
+from ..optim import ParamPack
 from . import _functions as Fn
 from .layers import Dropout, Linear
 
@@ -34,15 +35,13 @@ def _check_mask(mask: Tensor | None) -> Tensor | None:
         m = mask
     else:
         raise TypeError(f"Unexpected type `{mdtype}` of the `mask`.")
-    if m.dim() not in (2, 3):
-        raise ValueError("mask must be [T, Tk] or [B, T, Tk]")
-    return m if m.stride(-1) == 1 else m.contiguous()
+    return m   # broadcast against [B, T, Tk] (and shape errors) happen in AttentionFn, once q and k are known
 
 
 def _rng_args(x: Tensor):
     Dropout._global_calls += 1
     seed = torch.cuda.initial_seed() if x.is_cuda else torch.initial_seed()
-    return seed & 0xFFFFFFFFFFFFFFFF, Dropout._global_calls
+    return (seed ^ Dropout._seed_mix) & 0xFFFFFFFFFFFFFFFF, Dropout._global_calls
 
 
 class _AttentionHead(nn.Module):
@@ -115,6 +114,13 @@ class _MultiheadAttention(nn.Module):
         )
         self._proj = Linear(n_heads * head_size, embedding_size, bias=proj_bias)
         self._dropout = Dropout(p_dropout)
+        # the kernels see ONE [n*H*hs, E] projection matrix; the per-head Linear parameters stay separate
+        # nn.Parameters (state_dict parity with the reference) and are declared as a pack so that the flat
+        # optimizer lays them out back to back in this order (see optim.ParamPack)
+        names = ("_query", "_key", "_value") if hasattr(self._heads[0], "_key") else ("_query",)
+        self._wpack = ParamPack.declare([getattr(h, n).weight for n in names for h in self._heads])
+        self._bpack = (ParamPack.declare([getattr(h, n).bias for n in names for h in self._heads])
+                       if head_bias else None)
 
     @property
     def embedding_size(self) -> int:
@@ -128,14 +134,18 @@ class _MultiheadAttention(nn.Module):
     def n_heads(self) -> int:
         return len(self._heads)
 
-    # ---- packing helpers: the per-head Linear parameters stay separate (state_dict parity); the kernels see
-    # one [n*H*hs, E] matrix.  torch.cat is differentiable, so gradients land in each head's own .weight.grad.
-    def _packed(self, names: tuple[str, ...]) -> tuple[Tensor, Tensor | None]:
-        ws = [getattr(h, n).weight for n in names for h in self._heads]
-        w = torch.cat(ws, dim=0)
-        if getattr(self._heads[0], names[0]).bias is None:
-            return w, None
-        return w, torch.cat([getattr(h, n).bias for n in names for h in self._heads], dim=0)
+    def _project(self, x: Tensor) -> Tensor:
+        """All per-head projections of `x` as one GEMM: [.., n*H*hs] with column blocks q_0..q_{H-1} | k_0.. | v_0..
+        (what the reference's per-head Linears + torch.cat produce, nn/attention.py:149-192)."""
+        ws = self._wpack.members
+        bs = self._bpack.members if self._bpack is not None else []
+        pack = None
+        vw = self._wpack.views()
+        if vw is not None:
+            vb = self._bpack.views() if self._bpack is not None else (None, None)
+            if vb is not None:
+                pack = (vw[0], vw[1], vb[0], vb[1])
+        return Fn.PackedLinearFn.apply(x, False, len(ws), pack, *ws, *bs)
 
     def _head_dropout(self) -> float:
         return self._heads[0]._dropout.p if self.training else 0.0
@@ -203,8 +213,7 @@ class MultiheadCrossAttention(_MultiheadAttention):
         split_size = self.embedding_size // H
         if split_size != hs:
             raise RuntimeError(f"head_size ({hs}) must equal embedding_size // n_heads ({split_size})")
-        wq, bq = self._packed(("_query",))
-        q = Fn.LinearFn.apply(x, wq, bq, False)
+        q = self._project(x)
         # k / v are used unprojected: head h reads columns [h*split, (h+1)*split) -- the strided layout the
         # kernel takes; only the first H chunks are used, as `torch.split(...)[:H]` does
         seed, offset = _rng_args(x)
@@ -219,8 +228,7 @@ class MultiheadSelfAttention(_MultiheadAttention):
     def forward(self, x: Tensor, /, mask: Tensor | None = None, *, return_kv: bool = False) -> Tensor:
         mask = _check_mask(mask)
         H, hs = self.n_heads, self.head_size
-        w, b = self._packed(("_query", "_key", "_value"))
-        qkv = Fn.LinearFn.apply(x, w, b, False)
+        qkv = self._project(x)
         seed, offset = _rng_args(x)
         z = Fn.AttentionFn.apply(qkv, None, None, mask, self._heads[0]._scale_coeff, self._head_dropout(), H, hs,
                                  seed, offset, True)

@@ -40,7 +40,23 @@ class Conv2d(nn.Module):
         w = w.contiguous(memory_format=torch.channels_last)
         self.weight = nn.Parameter(w)
         self.bias = nn.Parameter(torch.empty(out_channels, device=device, dtype=dtype)) if bias else None
+        self.register_buffer("_in_mean", None, persistent=False)
+        self.register_buffer("_in_inv_std", None, persistent=False)
         self.reset_parameters()
+
+    def set_input_normalization(self, mean, std) -> None:
+        """For a network's FIRST layer fed with fp32 NCHW images: fold `(x - mean[c]) / std[c]` (torchvision's
+        Normalize) into the layout / cast kernel that already touches every input element.  Kept in non-persistent
+        buffers, so state_dicts still interchange with torch.nn.Conv2d.  `None, None` removes it."""
+        if mean is None:
+            self._in_mean = self._in_inv_std = None
+            return
+        m = torch.as_tensor(mean, dtype=torch.float32).flatten().cpu()
+        sd = torch.as_tensor(std, dtype=torch.float32).flatten().cpu()
+        if m.numel() != self.in_channels or sd.numel() != self.in_channels:
+            raise ValueError(f"mean / std must have {self.in_channels} entries")
+        self._in_mean = m.contiguous().to(self.weight.device)
+        self._in_inv_std = (1.0 / sd).contiguous().to(self.weight.device)
 
     def reset_parameters(self) -> None:
         nn.init.kaiming_uniform_(self.weight, a=math.sqrt(5))
@@ -55,6 +71,9 @@ class Conv2d(nn.Module):
         w = self.weight
         if not w.permute(0, 2, 3, 1).is_contiguous():
             w.data = w.data.contiguous(memory_format=torch.channels_last)
+        if self._in_mean is not None and self._in_mean.dtype != torch.float32:   # the kernels read fp32 constants
+            self._in_mean = self._in_mean.float()
+            self._in_inv_std = self._in_inv_std.float()
         return self
 
     @property
@@ -82,7 +101,11 @@ class Conv2d(nn.Module):
         if (w.dtype == torch.bfloat16 and x.dtype == torch.float32 and self.in_channels <= 8
                 and x.shape[1] == self.in_channels and not x.requires_grad):
             # network input: fp32 NCHW images straight into the packed-pixel first-layer kernels
-            return Fn.FirstConv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu)
+            norm = (self._in_mean, self._in_inv_std) if self._in_mean is not None else None
+            return Fn.FirstConv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu, norm)
+        if self._in_mean is not None:
+            raise RuntimeError("input normalisation is fused into the fp32-image first-layer path only; "
+                               "this input does not take it (normalise it upstream)")
         if x.shape[1] != self.in_channels:
             # a channel-padded input (see arch/_stem.prepare_input): zero-pad the filter to match
             if w.dtype == torch.bfloat16 and x.shape[1] > self.in_channels:
@@ -286,6 +309,7 @@ class Dropout(nn.Module):
     with p = 0 or .eval(), as SURVEY.md section 4 prescribes)."""
 
     _global_calls = 0
+    _seed_mix = 0   # set per rank by parallel.DataParallel so that replicas draw different masks
 
     def __init__(self, p: float = 0.5, inplace: bool = False) -> None:
         super().__init__()
@@ -302,7 +326,7 @@ class Dropout(nn.Module):
             return x
         Dropout._global_calls += 1
         seed = torch.cuda.initial_seed() if x.is_cuda else torch.initial_seed()
-        return Fn.DropoutFn.apply(x, self._p, seed & 0xFFFFFFFFFFFFFFFF, Dropout._global_calls)
+        return Fn.DropoutFn.apply(x, self._p, (seed ^ Dropout._seed_mix) & 0xFFFFFFFFFFFFFFFF, Dropout._global_calls)
 
     def extra_repr(self) -> str:
         return f"p={self._p}"

@@ -17,10 +17,57 @@ from . import functional as RF
 _ALIGN = 8  # elements: keeps every parameter 16-byte aligned in bf16 (TMA base-address requirement)
 
 
+class ParamPack:
+    """Parameters that one kernel wants to see as ONE matrix (the per-head q/k/v projection weights of a
+    multi-head attention module, nn/attention.py:85-96 of the reference keeps them as separate nn.Linear
+    modules).  A module declares the pack with `ParamPack.declare([...])`; the flat optimizer then lays the
+    members out back to back, in this order, so that a single view of the flat weight (and gradient) buffer is
+    the packed matrix: no concatenation in forward, no split in backward, gradients land in place."""
+
+    def __init__(self, members):
+        self.members = list(members)
+        self._cache = None   # (weight ptr, grad ptr, views) of the last successful lookup
+
+    @staticmethod
+    def declare(members) -> "ParamPack":
+        pk = ParamPack(members)
+        for m in pk.members:
+            m._rnn_pack = pk
+        return pk
+
+    def views(self):
+        """(packed weight view, packed gradient view) into the optimizer's flat buffers, or None when the members
+        are not (or no longer) laid out contiguously there."""
+        ms = self.members
+        g = getattr(ms[0], "_rnn_group", None)
+        if g is None:
+            return None
+        c = self._cache
+        if c is not None:
+            g0, g1 = ms[0].grad, ms[-1].grad
+            if (g0 is not None and g1 is not None and c[0] == (ms[0].data_ptr(), ms[-1].data_ptr())
+                    and c[1] == (g0.data_ptr(), g1.data_ptr())):
+                return c[2]
+        n, off0, es = ms[0].numel(), ms[0]._rnn_offset, g.work.element_size()
+        for i, m in enumerate(ms):
+            if getattr(m, "_rnn_group", None) is not g or m._rnn_offset != off0 + i * n or m.numel() != n:
+                return None
+            if m.data_ptr() != g.work.data_ptr() + (off0 + i * n) * es:
+                return None   # .data was re-homed (e.g. model.to(...) after the optimizer was built)
+            if m.grad is None or m.grad.data_ptr() != g.grad.data_ptr() + (off0 + i * n) * es:
+                return None
+        shape = (len(ms) * ms[0].shape[0],) + tuple(ms[0].shape[1:])
+        total = n * len(ms)
+        out = g.work[off0:off0 + total].view(shape), g.grad[off0:off0 + total].view(shape)
+        self._cache = ((ms[0].data_ptr(), ms[-1].data_ptr()), (ms[0].grad.data_ptr(), ms[-1].grad.data_ptr()), out)
+        return out
+
+
 class _FlatGroup:
     """One dtype's parameters flattened: work (param dtype), grad (param dtype), master/state (fp32)."""
 
     def __init__(self, params: list[torch.nn.Parameter]):
+        params = self._pack_order(params)
         self.params = params
         dev, dt = params[0].device, params[0].dtype
         self.dtype = dt
@@ -42,6 +89,28 @@ class _FlatGroup:
             p._rnn_offset = o
         self.master = self.work if dt == torch.float32 else self.work.float()
         self.state: dict[str, torch.Tensor] = {}
+
+    @staticmethod
+    def _pack_order(params: list) -> list:
+        """Layout order: the given order, except that the members of a declared ParamPack sit back to back (in
+        pack order) where the first of them would have been.  A pack is honoured only when all of its members
+        are in this group and need no alignment padding between them."""
+        ids = {id(p) for p in params}
+        out, done = [], set()
+        for p in params:
+            pk = getattr(p, "_rnn_pack", None)
+            if pk is None or not all(id(m) in ids and m.numel() % _ALIGN == 0 and m.numel() == pk.members[0].numel()
+                                     for m in pk.members):
+                if id(p) not in done:
+                    out.append(p)
+                    done.add(id(p))
+                continue
+            if id(p) in done:
+                continue
+            for m in pk.members:
+                out.append(m)
+                done.add(id(m))
+        return out
 
     @staticmethod
     def _view(flat: torch.Tensor, p: torch.Tensor, off: int) -> torch.Tensor:
@@ -78,10 +147,35 @@ class _FlatOptimizer:
         return [g.grad for g in self.groups]
 
     def zero_grad(self, set_to_none: bool = False) -> None:
-        """No memset: the next gradient kernel of each parameter overwrites instead of accumulating."""
+        """One memset per flat gradient buffer (51 MB for ResNet-50: ~10 us), plus the `fresh` mark that lets the
+        library's own gradient kernels overwrite instead of read-modify-write.  The memset is what keeps
+        gradients that arrive through stock autograd correct (AccumulateGrad does `p.grad += g` into the flat
+        view; e.g. a parameter used through torch.cat or any other ATen op), and it gives a parameter that
+        receives no gradient in a step a zero gradient (torch.optim semantics with set_to_none=False: momentum
+        and weight decay still apply).  `set_to_none` is accepted for signature parity and ignored: the
+        gradients must stay views of the flat buffer."""
+        self._reattach_grads()
         for g in self.groups:
+            g.grad.zero_()
             for p in g.params:
                 p._rnn_fresh = True
+
+    def _reattach_grads(self) -> None:
+        """`model.zero_grad()` (set_to_none=True is torch's default) or user code may have replaced a parameter's
+        .grad; the fused update reads the flat buffer, so put the views back (keeping a foreign gradient's
+        values)."""
+        for g in self.groups:
+            base, es = g.grad.data_ptr(), g.grad.element_size()
+            for p, o in zip(g.params, g.offsets):
+                gr = p.grad
+                if gr is not None and gr.data_ptr() == base + o * es:
+                    continue
+                view = g._view(g.grad, p, o)
+                if gr is None:
+                    view.zero_()
+                else:
+                    view.copy_(gr)
+                p.grad = view
 
     def state_dict(self) -> dict:
         return {"steps": self._steps,
@@ -116,6 +210,7 @@ class SGD(_FlatOptimizer):
 
     @torch.no_grad()
     def step(self) -> None:
+        self._reattach_grads()
         first = self._steps == 0
         for g in self.groups:
             buf = g.zeros_state("momentum_buffer") if self.momentum != 0 else None
@@ -152,6 +247,7 @@ class AdamW(_FlatOptimizer):
     def step(self) -> None:
         """The bias corrections are computed on the device from a device-side step counter, so the same sequence
         of launches serves every step (and can be replayed from a CUDA graph)."""
+        self._reattach_grads()
         cnt = self._device_steps()
         self._steps += 1
         RF.counter_add(cnt, 1)

@@ -8,6 +8,12 @@ are laid out in reverse registration order, bucket 0 completes first during back
 gradient kernel of a bucket has been enqueued, an event is recorded on the compute stream, the
 communication stream waits on it and issues `all_reduce(sum)`; the optimizer kernel then scales by
 1/world_size.  Works with any torch.distributed backend (NCCL on GPUs, gloo in the CPU tests).
+
+A bucket is launched when every DISTINCT parameter in it has reported its LAST gradient kernel of the step.  How
+many gradient kernels a parameter has per step (more than one when a module is applied twice in a forward pass)
+is learned during the first step, in which every bucket is launched by `finish()`; from the second step on the
+launch happens inside backward.  Dropout: every rank draws from its own Philox stream (the rank is mixed into the
+seed), as independent replicas would.
 """
 from __future__ import annotations
 
@@ -73,6 +79,11 @@ class DataParallel:
                     dist.broadcast(g.master, src=0, group=process_group)
             for b in model.buffers():
                 dist.broadcast(b, src=0, group=process_group)
+        self._uses: dict[int, int] | None = None   # gradient notifications per parameter and step (learned in step 1)
+        self._count: dict[int, int] = {}
+        if self.world_size > 1:
+            from .nn.layers import Dropout
+            Dropout._seed_mix = (self.rank * 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
         self._hook = self._on_grad_ready
         Fn.grad_ready_hooks.append(self._hook)
 
@@ -85,6 +96,9 @@ class DataParallel:
             Fn.grad_ready_hooks.remove(self._hook)
 
     def begin_step(self) -> None:
+        if self._uses is None and self._count:
+            self._uses = dict(self._count)
+        self._count = {}
         for b in self._buckets:
             b.pending, b.handle, b.launched = b.n_params, None, False
 
@@ -103,8 +117,17 @@ class DataParallel:
 
     def _on_grad_ready(self, p) -> None:
         b = self._param_bucket.get(id(p))
-        if b is None or b.launched:
+        if b is None:
             return
+        c = self._count[id(p)] = self._count.get(id(p), 0) + 1
+        if self._uses is None:
+            return                      # first step: only learn the counts; finish() launches every bucket
+        expected = self._uses.get(id(p), 1)
+        if c > expected and b.launched:
+            raise RuntimeError("a parameter received more gradient kernels than in the first step after its "
+                               "bucket's all-reduce was launched; rebuild DataParallel for the new graph")
+        if c != expected or b.launched:
+            return                      # an earlier use of a shared parameter: more accumulation is to come
         b.pending -= 1
         if b.pending == 0:
             self._launch(b)

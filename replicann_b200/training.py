@@ -24,7 +24,14 @@ class Trainer:
         self._eager_steps = 0
         self._has_dropout = False
         self._gx = self._gy = self._gloss = None
+        self._hyper = None          # optimizer hyper-parameters baked into the captured launches
+        self._bn_counts: list = []  # (BatchNorm2d, batches counted per step): replays bypass Module.forward
+        self._replays = 0
         if cuda_graph:
+            if graph_warmup < 1:
+                # the first SGD-momentum step initialises the momentum buffer (first_step=True); captured, every
+                # replay would re-initialise it
+                raise ValueError("cuda_graph=True needs graph_warmup >= 1 eager step before the capture")
             self._check_graph_safe()
 
     @property
@@ -63,7 +70,17 @@ class Trainer:
         self._opt.step()
         return loss.detach()
 
+    def _opt_hyper(self) -> tuple:
+        """Host scalars that become kernel arguments of the captured optimizer launches."""
+        o = self._opt
+        return tuple((k, getattr(o, k)) for k in ("lr", "momentum", "dampening", "weight_decay", "nesterov", "betas",
+                                                  "eps", "grad_scale") if hasattr(o, k))
+
     def _capture(self, x: torch.Tensor, y: torch.Tensor) -> None:
+        from .nn.layers import BatchNorm2d
+        bns = [m for m in self._model.modules() if isinstance(m, BatchNorm2d)]
+        before = [m._batches_pending for m in bns]
+        self._hyper = self._opt_hyper()
         self._gx = torch.empty_like(x)
         self._gy = torch.empty_like(y)
         self._gx.copy_(x)
@@ -83,6 +100,8 @@ class Trainer:
                     RF.rng_advance()
                 self._gloss = self._eager_step(self._gx, self._gy)
         self._graph = g
+        self._bn_counts = [(m, m._batches_pending - b) for m, b in zip(bns, before) if m._batches_pending != b]
+        self._replays = 0
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """One optimisation step on a batch already resident on the device; returns the (device) loss."""
@@ -95,17 +114,32 @@ class Trainer:
             self._capture(x, y)
         elif x.shape != self._gx.shape or x.dtype != self._gx.dtype:
             raise ValueError("the captured step takes batches of the shape and dtype it was captured with")
+        elif self._opt_hyper() != self._hyper:
+            # lr / momentum / weight decay are kernel arguments frozen into the graph: a schedule that moved
+            # them gets a fresh capture (one eager-speed step) instead of being silently ignored
+            self._graph = None
+            self._capture(x, y)
         self._gx.copy_(x, non_blocking=True)
         self._gy.copy_(y, non_blocking=True)
-        self._graph.replay()
+        self._replay()
         return self._gloss
+
+    def _replay(self) -> None:
+        self._graph.replay()
+        if self._replays:   # the capture pass itself counted this step's batches once
+            for m, n in self._bn_counts:
+                m._batches_pending += n
+        self._replays += 1
 
     def step_from_host(self, x_host: torch.Tensor, y_host: torch.Tensor) -> float:
         """End-to-end step: pinned host batch -> device, train step, loss back to the host."""
         if self._graph is not None:
+            if self._opt_hyper() != self._hyper:
+                return float(self.step(x_host.to(self._gx.device, non_blocking=True),
+                                       y_host.to(self._gy.device, non_blocking=True)).item())
             self._gx.copy_(x_host, non_blocking=True)
             self._gy.copy_(y_host, non_blocking=True)
-            self._graph.replay()
+            self._replay()
             return float(self._gloss.item())
         dev = next(self._model.parameters()).device
         x = x_host.to(dev, non_blocking=True)

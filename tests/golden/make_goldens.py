@@ -5,7 +5,7 @@ Track N (CNN operators / training steps): outputs of `torch` CPU -- the third-pa
 reference's arithmetic lives (pyproject.toml:11; locked 2.4.0, installed version recorded in each file).
 Track R (transformer blocks): outputs of the reference's OWN classes imported from /root/reference/src.
 The fixtures are small on purpose; they pin the oracle (tests/test_oracle.py) and the CUDA path
-(tests/test_golden_gpu.py) without needing /root/reference at test time.
+(tests/test_transformer_gpu.py and tests/test_oracle.py) without needing /root/reference at test time.
 """
 import sys
 from pathlib import Path

@@ -263,6 +263,59 @@ def test_layout_roundtrip_and_padding():
     assert torch.equal(back.cpu(), x.to(torch.bfloat16).float())
 
 
+@pytest.mark.parametrize("N,C,H,W,R,S,stride,pad", [
+    (4, 3, 224, 224, 7, 7, 2, 3),     # ResNet stem: the image fast path (W % 4 == 0, 8 padded rows per block)
+    (2, 3, 67, 67, 11, 11, 4, 2),     # W % 4 != 0: generic padded kernel
+    (3, 1, 28, 28, 5, 5, 1, 2),       # one channel
+    (2, 3, 30, 36, 3, 3, 1, 1),       # Hp not a multiple of the rows per block
+])
+@pytest.mark.parametrize("norm", [False, True])
+def test_input_layout_kernel_with_normalisation(N, C, H, W, R, S, stride, pad, norm):
+    """fp32 NCHW -> bf16 NHWC (+ per-channel normalisation), into the zero-padded packed-pixel buffer
+    of the first convolution and into the plain channel-padded layout.  Bit-exact against torch: same fp32
+    arithmetic ((x - mean) * (1/std)), same round-to-nearest-even to bf16, exact zeros in every padding."""
+    from replicann_b200._lib import conv_desc
+    f = RF()
+    x = rnd((N, C, H, W), 5, scale=0.5) + 0.4
+    mean = torch.tensor([0.485, 0.456, 0.406][:C])
+    inv_std = 1.0 / torch.tensor([0.229, 0.224, 0.225][:C])
+    ref = x
+    kw = {}
+    if norm:
+        ref = (x - mean.view(1, C, 1, 1)) * inv_std.view(1, C, 1, 1)
+        kw = dict(mean=mean.cuda(), inv_std=inv_std.cuda())
+    ref = ref.to(torch.bfloat16).permute(0, 2, 3, 1)
+    d = conv_desc(N, H, W, C, 64, R, S, stride, pad)
+    hp, wp, _ = f.first_conv_geometry(d)
+    y = f.pack_first_input(x.cuda(), d, **kw).cpu()
+    assert tuple(y.shape) == (N, hp, wp, 8)
+    assert torch.equal(y[:, pad:pad + H, pad:pad + W, :C], ref)
+    border = y.clone()
+    border[:, pad:pad + H, pad:pad + W, :C] = 0
+    assert (border == 0).all()
+    y2 = f.nchw_to_nhwc_bf16(x.cuda(), cpad=8, **kw).cpu()
+    assert torch.equal(y2[..., :C], ref) and (y2[..., C:] == 0).all()
+
+
+def test_first_layer_with_fused_normalisation_matches_normalise_then_conv():
+    """Conv2d.set_input_normalization: forward and weight gradient equal those of normalising on the host first."""
+    from replicann_b200.nn.layers import Conv2d
+    torch.manual_seed(0)
+    mean, std = (0.485, 0.456, 0.406), (0.229, 0.224, 0.225)
+    a = Conv2d(3, 64, 7, 2, 3, bias=False).cuda().to(torch.bfloat16)
+    b = Conv2d(3, 64, 7, 2, 3, bias=False).cuda().to(torch.bfloat16)
+    b.load_state_dict(a.state_dict())
+    a.set_input_normalization(mean, std)
+    assert set(a.state_dict()) == set(b.state_dict())   # the constants are not part of the checkpoint
+    x = rnd((4, 3, 64, 64), 9, scale=0.3) + 0.45
+    xn = (x - torch.tensor(mean).view(1, 3, 1, 1)) * (1.0 / torch.tensor(std)).view(1, 3, 1, 1)
+    ya, yb = a(x.cuda()), b(xn.cuda())
+    assert torch.equal(ya, yb)
+    dy = rnd(tuple(ya.shape), 10, torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    ya.backward(dy); yb.backward(dy)
+    assert torch.equal(a.weight.grad, b.weight.grad)
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_relu_add_cast(dtype):
     f = RF()

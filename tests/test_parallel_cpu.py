@@ -40,15 +40,30 @@ def _worker(rank, world, port, q):
         dist.all_gather(gathered, w0)
         assert torch.equal(gathered[0], gathered[1]), "parameters were not broadcast from rank 0"
         assert opt.grad_scale == 1.0 / world
+        params = list(model.parameters())[::-1]
+        shared = params[0]   # reports two gradient kernels per step (a module applied twice in one forward)
+        # first step: the number of gradient kernels per parameter is learned, finish() launches everything
+        dp.begin_step()
+        for p in params:
+            Fn.grad_target(p)[0].zero_()
+            Fn._notify(p)
+        Fn._notify(shared)
+        assert not any(b.launched for b in dp._buckets)
+        dp.finish()
+        assert all(b.launched for b in dp._buckets)
+        opt.zero_grad()
         # simulate backward: gradients appear in reverse registration order, each reported through the hook
         dp.begin_step()
         launched_before_finish = 0
-        params = list(model.parameters())[::-1]
         for i, p in enumerate(params):
             tgt, acc = Fn.grad_target(p)
             assert acc is False
             tgt.copy_(torch.full_like(p, float(rank + 1) * (i + 1)))
             Fn._notify(p)
+            if p is shared:
+                # the first of its two kernels must not release the bucket: the second accumulation is to come
+                assert not dp._param_bucket[id(p)].launched
+                Fn._notify(p)
             launched_before_finish = sum(b.launched for b in dp._buckets)
         assert launched_before_finish == dp.n_buckets  # every bucket went out during "backward"
         dp.finish()
@@ -62,6 +77,8 @@ def _worker(rank, world, port, q):
             tgt, _ = Fn.grad_target(p)
             tgt.fill_(1.0)
             Fn._notify(p)
+            if p is shared:
+                Fn._notify(p)
         assert sum(b.launched for b in dp._buckets) < dp.n_buckets
         dp.finish()
         assert all(b.launched for b in dp._buckets)

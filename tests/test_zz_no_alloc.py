@@ -62,6 +62,24 @@ def test_static_scratch_matches_workspace_entry_point_twice_in_a_row():
     _run_both(lib, 777, 64, seed=2)
 
 
+def test_static_scratch_at_its_widest_supported_input():
+    """C = RNN_BN_STATIC_MAX_C exactly: the widest input the built-in scratch is sized for."""
+    from replicann_b200 import _lib
+    _run_both(_lib.load(), 3000, 4096, seed=3)
+
+
+def test_static_scratch_on_a_second_device():
+    """Every device holds its own copy of the scratch array and gets its own address lookup: the entry point must
+    work with a device other than 0 current (hosts that drive several GPUs from one process)."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    from replicann_b200 import _lib
+    with torch.cuda.device(1):
+        torch.cuda.set_device(1)
+        _run_both(_lib.load(), 4096, 256, seed=4)
+    torch.cuda.set_device(0)
+
+
 def test_static_scratch_rejects_inputs_beyond_its_limit():
     from replicann_b200 import _lib
     lib = _lib.load()
