@@ -240,6 +240,20 @@ int rnn_softmax_ce(const void* logits, const long long* target, long long rows, 
 /* torch.argmax(x, dim=-1): first maximum wins. */
 int rnn_argmax(const void* x, long long* out, long long rows, int cols, int is_f32, cudaStream_t stream);
 
+/* ---- embeddings ------------------------------------------------------------------------------------------ */
+/* torch.nn.Embedding lookup for a token table tok[V, E] fused with the learned positional table pos[T, E]
+ * (nullable): out[n, :] = tok[ids[n], :] + pos[n % T, :] for n < n_tokens (= B * T).  Not in the reference: the
+ * embedding stage of the encoder / decoder stacks SURVEY.md 8(f).4 names as the next replication; it feeds
+ * TransformerEncoder / TransformerDecoder (arch/transformer.py:87-151).  An index outside [0, V) reads as zeros. */
+int rnn_embedding_fwd(const long long* ids, const void* tok, const void* pos, void* out, long long n_tokens, int T,
+                      int V, int E, int is_f32, cudaStream_t stream);
+/* Its autograd: dtok[v, :] (+)= sum of dy rows whose index is v (ascending token order, no floating-point atomics:
+ * bitwise reproducible), dpos[t, :] (+)= sum over the batch.  Either output may be NULL.  ws: V ints. */
+size_t rnn_embedding_bwd_workspace(int V);
+int rnn_embedding_bwd(const long long* ids, const void* dy, void* dtok, void* dpos, long long n_tokens, int T, int V,
+                      int E, int is_f32, int accumulate_tok, int accumulate_pos, void* ws, size_t ws_bytes,
+                      cudaStream_t stream);
+
 /* ---- batched GEMM (attention contractions on the tensor cores) -------------------------------------- */
 /* D_z = A_z . B_z^T, bf16 in, fp32 accumulate, for z = b * heads + h.  No counterpart in the reference: it is the
  * two torch.bmm-shaped `@` products of _AttentionHead._attention (nn/attention.py:37,47) and their autograd, for

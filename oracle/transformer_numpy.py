@@ -88,11 +88,19 @@ def encoder(p, x, n_heads, return_kv=False):
     return layer_norm(x + ffn(p, "_ffn", x), p["_ffn_ln.weight"], p["_ffn_ln.bias"]), k, v
 
 
+def _block_mask(p, T):
+    """The decoders' `_attn_mask` buffer as the reference feeds it to attention (arch/transformer.py:148): float32
+    tril(ones) in the reference itself (additive branch); a bool buffer (True = masked out) in the causal stacks of
+    replicann_b200.arch.stacks takes the masked_fill branch of nn/attention.py:39-40."""
+    m = p["_attn_mask"][:T, :T]
+    return m if m.dtype == np.bool_ else m.astype(np.float32)
+
+
 def decoder(p, x, n_heads):
     """TransformerDecoder.forward (arch/transformer.py:147-151): the float32 tril(ones) buffer takes the
     ADDITIVE mask branch -- +1 on and below the diagonal -- so the block is not causal."""
     T = x.shape[1]
-    mask = p["_attn_mask"][:T, :T].astype(np.float32)
+    mask = _block_mask(p, T)
     x = layer_norm(x + multihead_self_attention(p, "_attn", x, n_heads, mask), p["_attn_ln.weight"], p["_attn_ln.bias"])
     return layer_norm(x + ffn(p, "_ffn", x), p["_ffn_ln.weight"], p["_ffn_ln.bias"])
 
@@ -100,8 +108,61 @@ def decoder(p, x, n_heads):
 def cross_decoder(p, x, enc_k, enc_v, n_heads):
     """TransformerCrossDecoder.forward (arch/transformer.py:190-201)."""
     T = x.shape[1]
-    mask = p["_attn_mask"][:T, :T].astype(np.float32)
+    mask = _block_mask(p, T)
     x = layer_norm(x + multihead_self_attention(p, "_attn", x, n_heads, mask), p["_attn_ln.weight"], p["_attn_ln.bias"])
     x = layer_norm(x + multihead_cross_attention(p, "_cross_attn", x, enc_k, enc_v, n_heads),
                    p["_cross_attn_ln.weight"], p["_cross_attn_ln.bias"])
     return layer_norm(x + ffn(p, "_ffn", x), p["_ffn_ln.weight"], p["_ffn_ln.bias"])
+
+
+# ---------------------------------------------------------------------------------------------- stacks (SURVEY 8f.4)
+# Not in the reference: compositions of its blocks (arch/transformer.py:87-201) with torch.nn.Embedding /
+# nn.Linear / F.cross_entropy semantics.  PINNING: tests/golden/transformer_stacks.npz, produced by
+# make_goldens.py from a torch-CPU network assembled out of the reference's own block classes.
+def _sub(p, prefix):
+    return {k[len(prefix):]: v for k, v in p.items() if k.startswith(prefix)}
+
+
+def _n_blocks(p, prefix):
+    return 1 + max(int(k[len(prefix):].split(".")[0]) for k in p if k.startswith(prefix))
+
+
+def encoder_stack(p, x, n_heads, return_kv=False):
+    n = _n_blocks(p, "_blocks.")
+    for i in range(n - 1):
+        x = encoder(_sub(p, f"_blocks.{i}."), x, n_heads)
+    return encoder(_sub(p, f"_blocks.{n - 1}."), x, n_heads, return_kv=return_kv)
+
+
+def decoder_stack(p, x, n_heads):
+    for i in range(_n_blocks(p, "_blocks.")):
+        x = decoder(_sub(p, f"_blocks.{i}."), x, n_heads)
+    return x
+
+
+def cross_decoder_stack(p, x, enc_k, enc_v, n_heads):
+    for i in range(_n_blocks(p, "_blocks.")):
+        x = cross_decoder(_sub(p, f"_blocks.{i}."), x, enc_k, enc_v, n_heads)
+    return x
+
+
+def embedding(p, ids):
+    """tok[ids] + pos[arange(T)] (torch.nn.Embedding lookups)."""
+    return p["_tokens.weight"][ids] + p["_positions.weight"][np.arange(ids.shape[1])]
+
+
+def cross_entropy(logits, targets):
+    """F.cross_entropy(logits [N, V], targets [N]) with mean reduction."""
+    m = logits.max(axis=-1, keepdims=True)
+    lse = m[:, 0] + np.log(np.exp(logits - m).sum(axis=-1))
+    return float((lse - logits[np.arange(len(targets)), targets]).mean())
+
+
+def language_model(p, ids, n_heads, targets=None):
+    """embeddings -> decoder stack -> Linear head; with targets, the mean next-token cross-entropy."""
+    x = embedding(_sub(p, "_embedding."), ids)
+    x = decoder_stack(_sub(p, "_decoder."), x, n_heads)
+    logits = linear(x, p["_head.weight"], p.get("_head.bias"))
+    if targets is None:
+        return logits
+    return logits, cross_entropy(logits.reshape(-1, logits.shape[-1]), targets.reshape(-1))

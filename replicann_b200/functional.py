@@ -702,6 +702,38 @@ def softmax_ce(logits, target, grad_scale=None, want_grad=True):
     return row_loss[rows], dl
 
 
+def embedding_fwd(ids, tok, pos=None):
+    """ids int64 [B, T] -> [B, T, E] = tok[ids] (+ pos[:T])."""
+    lib = _lib.load(); _cuda(ids, tok, pos); _contig(ids, "ids"); _contig(tok, "tok")
+    if ids.dtype != torch.int64:
+        raise TypeError("embedding indices must be int64")
+    B, T = ids.shape
+    V, E = tok.shape
+    if pos is not None:
+        _contig(pos, "pos")
+        if pos.dtype != tok.dtype or pos.shape[0] < T or pos.shape[1] != E:
+            raise ValueError(f"positional table {tuple(pos.shape)} / {pos.dtype} does not cover T={T}, E={E} of the token table")
+    out = torch.empty((B, T, E), dtype=tok.dtype, device=tok.device)
+    with _span("embedding", float(B * T * E * tok.element_size() * (3 if pos is not None else 2)), f"fwd N{B * T} V{V} E{E}"):
+        check(lib.rnn_embedding_fwd(ptr(ids), ptr(tok), ptr(pos), ptr(out), B * T, T, V, E, _is_f32(tok), cur_stream()),
+              "rnn_embedding_fwd")
+    return out
+
+
+def embedding_bwd(ids, dy, dtok=None, dpos=None, *, accumulate_tok=False, accumulate_pos=False):
+    """Scatter-add of dy [B, T, E] into dtok [V, E] and / or column sums over the batch into dpos[:T]."""
+    lib = _lib.load(); _cuda(ids, dy, dtok, dpos); _contig(dy, "dy")
+    B, T = ids.shape
+    E = dy.shape[-1]
+    V = dtok.shape[0] if dtok is not None else 1
+    nbytes = lib.rnn_embedding_bwd_workspace(V) if dtok is not None else 0
+    ws = workspace(nbytes, dy.device)
+    with _span("embedding", float(B * T * E * dy.element_size() * 2), f"bwd N{B * T} V{V} E{E}"):
+        check(lib.rnn_embedding_bwd(ptr(ids), ptr(dy), ptr(dtok), ptr(dpos), B * T, T, V, E, _is_f32(dy),
+                                    int(accumulate_tok), int(accumulate_pos), ptr(ws), nbytes, cur_stream()),
+              "rnn_embedding_bwd")
+
+
 def argmax(x2d):
     lib = _lib.load(); _cuda(x2d); _contig(x2d, "x")
     out = torch.empty((x2d.shape[0],), dtype=torch.int64, device=x2d.device)

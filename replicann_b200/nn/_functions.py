@@ -576,6 +576,36 @@ class SoftmaxFn(Function):
         return RF.softmax_bwd(d2 if d2.is_contiguous() else d2.contiguous(), y).reshape(ctx.shape)
 
 
+# ------------------------------------------------------------------------------------------ embeddings
+class EmbeddingFn(Function):
+    """out = tok[ids] (+ pos[:T]) -- torch.nn.Embedding lookups of a token and a learned positional table in one
+    kernel; backward is the deterministic scatter-add / batch sum of rnn_embedding_bwd, written straight into the
+    tables' .grad (a token table tied to the LM head then receives its second contribution by accumulation)."""
+
+    @staticmethod
+    def forward(ctx, ids, tok, pos):
+        ids = ids if ids.is_contiguous() else ids.contiguous()
+        T = ids.shape[1]
+        ctx.save_for_backward(ids, tok, pos)
+        return RF.embedding_fwd(ids, tok.detach(), pos.detach()[:T] if pos is not None else None)
+
+    @staticmethod
+    def backward(ctx, dy):
+        ids, tok, pos = ctx.saved_tensors
+        dy = dy if dy.is_contiguous() else dy.contiguous()
+        T = ids.shape[1]
+        dtok = dpos = None
+        if ctx.needs_input_grad[1]:
+            dtok = _write_param_grad(tok, lambda out, acc: RF.embedding_bwd(ids, dy, dtok=out, accumulate_tok=acc))
+        if pos is not None and ctx.needs_input_grad[2]:
+            def pg(out, acc):
+                if not acc and out.shape[0] > T:
+                    out[T:].zero_()          # positions beyond this batch's length get no gradient
+                RF.embedding_bwd(ids, dy, dpos=out[:T], accumulate_pos=acc)
+            dpos = _write_param_grad(pos, pg)
+        return None, dtok, dpos
+
+
 # ------------------------------------------------------------------------------------------ attention
 class AttentionFn(Function):
     """z = dropout(softmax(q k^T * scale (+ mask))) v for all heads at once (nn/attention.py:28-50).

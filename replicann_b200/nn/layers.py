@@ -239,6 +239,37 @@ class LayerNorm(nn.Module):
         return Fn.LayerNormFn.apply(x, residual, self.weight, self.bias, self._eps)
 
 
+class Embedding(nn.Module):
+    """torch.nn.Embedding(num_embeddings, embedding_dim): weight [V, E], N(0, 1) init, int64 indices.
+    `forward(ids, positions=other_embedding)` adds a learned positional table in the same kernel."""
+
+    def __init__(self, num_embeddings: int, embedding_dim: int, *, device=None, dtype=None) -> None:
+        super().__init__()
+        self.weight = nn.Parameter(torch.empty((num_embeddings, embedding_dim), device=device, dtype=dtype))
+        nn.init.normal_(self.weight)
+
+    @property
+    def num_embeddings(self) -> int:
+        return self.weight.shape[0]
+
+    @property
+    def embedding_dim(self) -> int:
+        return self.weight.shape[1]
+
+    def forward(self, ids: Tensor, /, positions: "Embedding | None" = None) -> Tensor:
+        squeeze = ids.dim() == 1
+        ids2 = ids.unsqueeze(0) if squeeze else ids
+        if ids2.dim() != 2:
+            raise ValueError(f"indices must be [T] or [B, T], got {tuple(ids.shape)}")
+        if positions is not None and ids2.shape[1] > positions.num_embeddings:
+            raise IndexError(f"sequence length {ids2.shape[1]} exceeds the positional table ({positions.num_embeddings})")
+        out = Fn.EmbeddingFn.apply(ids2, self.weight, positions.weight if positions is not None else None)
+        return out.squeeze(0) if squeeze else out
+
+    def extra_repr(self) -> str:
+        return f"{self.num_embeddings}, {self.embedding_dim}"
+
+
 class ReLU(nn.Module):
     def __init__(self, inplace: bool = False) -> None:  # `inplace` accepted for signature parity; ignored
         super().__init__()

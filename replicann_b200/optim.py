@@ -128,8 +128,11 @@ class _FlatGroup:
 
 
 class _FlatOptimizer:
+    _TORCH_STATE: tuple = ()      # names of the per-parameter state tensors, as torch.optim calls them
+
     def __init__(self, params: Iterable[torch.nn.Parameter]):
         plist = [p for p in params if p.requires_grad]
+        self._registration_order = list(plist)
         if not plist:
             raise ValueError("optimizer got an empty parameter list")
         # Bucket construction is pure bookkeeping and works on any device (the gloo tests build buckets on
@@ -192,14 +195,84 @@ class _FlatOptimizer:
             if g.master is not g.work:
                 RF.cast_f32_to_bf16(g.master, out=g.work)
 
+    # ---- checkpoint interchange with torch.optim -------------------------------------
+    def _located(self):
+        """(registration index, parameter, group, offset) for every parameter, in registration order."""
+        where = {id(p): (g, o) for g in self.groups for p, o in zip(g.params, g.offsets)}
+        return [(i, p, *where[id(p)]) for i, p in enumerate(self._registration_order)]
+
+    def _torch_hyper(self) -> dict:
+        raise NotImplementedError
+
+    def torch_state_dict(self) -> dict:
+        """The optimizer state in torch.optim's own checkpoint format ({"state": {index: {...}}, "param_groups":
+        [...]}, parameters numbered in registration order): per-parameter tensors are cut out of the flat fp32
+        buffers and shaped like the parameter, so `torch.optim.SGD / AdamW(model.parameters()).load_state_dict()`
+        accepts the result and a `.pt` written from it resumes in plain PyTorch."""
+        steps = self._steps
+        sd_state = {}
+        for i, p, g, o in self._located():
+            ent = {}
+            for name in self._TORCH_STATE:
+                if name in g.state:
+                    ent[name] = g._view(g.state[name], p, o).detach().clone().contiguous()
+            if ent or steps:
+                if "step" in self._TORCH_EXTRA:
+                    ent["step"] = torch.tensor(float(steps))
+                if ent:
+                    sd_state[i] = ent
+        group = dict(self._torch_hyper(), params=list(range(len(self._registration_order))))
+        return {"state": sd_state, "param_groups": [group]}
+
+    def load_torch_state_dict(self, sd: dict) -> None:
+        """Inverse of torch_state_dict(): scatter a torch.optim checkpoint into the flat buffers (hyper-parameters
+        of its first param_group are adopted too).  The fp32 master weights are refreshed from the parameters."""
+        pg = sd["param_groups"][0]
+        self._adopt_torch_hyper(pg)
+        steps = 0
+        for i, p, g, o in self._located():
+            ent = sd["state"].get(pg["params"][i] if i < len(pg["params"]) else i)
+            if ent is None:
+                continue
+            for name in self._TORCH_STATE:
+                if name in ent and ent[name] is not None:
+                    g._view(g.zeros_state(name), p, o).copy_(ent[name].to(torch.float32))
+            if "step" in ent:
+                steps = max(steps, int(float(ent["step"])))
+        if "step" in self._TORCH_EXTRA:
+            self._steps = steps
+        elif any(sd["state"].values()):
+            self._steps = max(self._steps, 1)   # momentum buffers exist: the next step is not the first
+        self.sync_master_from_params()
+
+    _TORCH_EXTRA: tuple = ()
+
+    def _adopt_torch_hyper(self, pg: dict) -> None:
+        raise NotImplementedError
+
     def sync_master_from_params(self) -> None:
         """Call after load_state_dict() on the model: refresh the fp32 master copies from the weights."""
         for g in self.groups:
             if g.master is not g.work:
-                RF.cast_bf16_to_f32(g.work, out=g.master)
+                if g.work.is_cuda:
+                    RF.cast_bf16_to_f32(g.work, out=g.master)
+                else:   # bookkeeping on CPU tensors (checkpoint conversion, the gloo tests): no kernel involved
+                    g.master.copy_(g.work)
 
 
 class SGD(_FlatOptimizer):
+    _TORCH_STATE = ("momentum_buffer",)
+
+    def _torch_hyper(self) -> dict:
+        return {"lr": self.lr, "momentum": self.momentum, "dampening": self.dampening,
+                "weight_decay": self.weight_decay, "nesterov": self.nesterov, "maximize": False, "foreach": None,
+                "differentiable": False, "fused": None}
+
+    def _adopt_torch_hyper(self, pg: dict) -> None:
+        self.lr, self.momentum = pg.get("lr", self.lr), pg.get("momentum", self.momentum)
+        self.dampening, self.weight_decay = pg.get("dampening", self.dampening), pg.get("weight_decay", self.weight_decay)
+        self.nesterov = pg.get("nesterov", self.nesterov)
+
     def __init__(self, params, lr: float, *, momentum: float = 0.0, dampening: float = 0.0,
                  weight_decay: float = 0.0, nesterov: bool = False) -> None:
         super().__init__(params)
@@ -222,6 +295,28 @@ class SGD(_FlatOptimizer):
 
 
 class AdamW(_FlatOptimizer):
+    _TORCH_STATE = ("exp_avg", "exp_avg_sq")
+    _TORCH_EXTRA = ("step",)
+
+    def _torch_hyper(self) -> dict:
+        return {"lr": self.lr, "betas": tuple(self.betas), "eps": self.eps, "weight_decay": self.weight_decay,
+                "amsgrad": False, "maximize": False, "foreach": None, "capturable": False, "differentiable": False,
+                "fused": None, "decoupled_weight_decay": True}
+
+    def _adopt_torch_hyper(self, pg: dict) -> None:
+        self.lr, self.betas = pg.get("lr", self.lr), tuple(pg.get("betas", self.betas))
+        self.eps, self.weight_decay = pg.get("eps", self.eps), pg.get("weight_decay", self.weight_decay)
+
+    def torch_state_dict(self) -> dict:
+        if self._step_dev is not None:
+            self._steps = int(self._step_dev.item())
+        return super().torch_state_dict()
+
+    def load_torch_state_dict(self, sd: dict) -> None:
+        super().load_torch_state_dict(sd)
+        if self._step_dev is not None:
+            self._step_dev.fill_(self._steps)
+
     def __init__(self, params, lr: float = 1e-3, *, betas=(0.9, 0.999), eps: float = 1e-8,
                  weight_decay: float = 1e-2) -> None:
         super().__init__(params)

@@ -194,9 +194,101 @@ def transformer_blocks():
     np.savez_compressed(HERE / "transformer_blocks.npz", **out)
 
 
+def transformer_stacks():
+    """stacks, embeddings and LM loss.  The reference has no such classes; the oracle is a torch-CPU
+    network assembled from the reference's OWN block classes (arch/transformer.py:87-201) plus torch.nn.Embedding /
+    torch.nn.Linear / F.cross_entropy, with the attribute names of replicann_b200.arch.stacks so that state_dicts
+    interchange.  fp32, eval mode (see the dropout note in transformer_blocks)."""
+    sys.path.insert(0, "/root/reference/src")
+    import torch.nn as nn
+    from replicann.arch.transformer import TransformerCrossDecoder, TransformerDecoder, TransformerEncoder
+    out = dict(META)
+
+    class Stack(nn.Module):
+        def __init__(self, blocks, causal_ctx=None):
+            super().__init__()
+            self._blocks = nn.ModuleList(blocks)
+            if causal_ctx is not None:
+                for b in self._blocks:
+                    b._attn_mask = torch.triu(torch.ones(causal_ctx, causal_ctx, dtype=torch.bool), diagonal=1)
+
+    class Emb(nn.Module):
+        def __init__(self, V, E, ctx):
+            super().__init__()
+            self._tokens = nn.Embedding(V, E)
+            self._positions = nn.Embedding(ctx, E)
+
+        def forward(self, ids):
+            return self._tokens(ids) + self._positions(torch.arange(ids.shape[1]))
+
+    class LM(nn.Module):
+        def __init__(self, V, L, H, E, ctx, causal, tie):
+            super().__init__()
+            self._embedding = Emb(V, E, ctx)
+            self._decoder = Stack([TransformerDecoder(H, E, context_size=ctx, p_dropout=0.0) for _ in range(L)],
+                                  ctx if causal else None)
+            self._head = nn.Linear(E, V, bias=not tie)
+            if tie:
+                self._head.weight = self._embedding._tokens.weight
+
+        def forward(self, ids):
+            x = self._embedding(ids)
+            for b in self._decoder._blocks:
+                x = b(x)
+            return self._head(x)
+
+    def record(tag, mod, extra):
+        out.update({f"{tag}:sd:{k}": v.detach().numpy() for k, v in mod.state_dict().items()})
+        out.update({f"{tag}:grad:{n}": p.grad.numpy() for n, p in mod.named_parameters() if p.grad is not None})
+        out.update({f"{tag}:{k}": (v.detach().numpy() if torch.is_tensor(v) else v) for k, v in extra.items()})
+
+    g = torch.Generator().manual_seed(4321)
+    V, L, H, E, ctx, B, T = 48, 2, 2, 16, 12, 3, 8
+    for tag, causal, tie in (("lm", True, False), ("lm_tied_noncausal", False, True)):
+        torch.manual_seed(7)
+        lm = LM(V, L, H, E, ctx, causal, tie).eval()
+        ids = torch.randint(0, V, (B, T), generator=g)
+        ids[0, :3] = 5                       # repeated tokens: several rows scatter into one table row
+        tgt = torch.randint(0, V, (B, T), generator=g)
+        logits = lm(ids)
+        loss = F.cross_entropy(logits.reshape(-1, V), tgt.reshape(-1))
+        loss.backward()
+        record(tag, lm, dict(ids=ids, targets=tgt, logits=logits, loss=np.float32(loss.item()),
+                             cfg=np.array([V, L, H, E, ctx, int(causal), int(tie)])))
+
+    def wsum(o):
+        return (o * torch.arange(o.numel(), dtype=torch.float32).reshape(o.shape).cos()).sum()
+
+    torch.manual_seed(8)
+    enc = Stack([TransformerEncoder(H, E, p_dropout=0.0) for _ in range(L)]).eval()
+    x = torch.randn(B, T, E, generator=g).requires_grad_()
+    h = x
+    for b in enc._blocks[:-1]:
+        h = b(h)
+    y, k, v = enc._blocks[-1](h, return_kv=True)
+    (wsum(y) + 0.5 * wsum(k) - 0.25 * wsum(v)).backward()
+    record("encstack", enc, dict(x=x, y=y, k=k, v=v, dx=x.grad))
+
+    torch.manual_seed(9)
+    xd = Stack([TransformerCrossDecoder(H, E, context_size=ctx, p_dropout=0.0) for _ in range(L)], ctx).eval()
+    x2 = torch.randn(B, T, E, generator=g).requires_grad_()
+    ek = k.detach().clone().requires_grad_()
+    ev = v.detach().clone().requires_grad_()
+    h = x2
+    for b in xd._blocks:
+        h = b(h, ek, ev)
+    wsum(h).backward()
+    record("xdecstack", xd, dict(x=x2, y=h, dx=x2.grad, dek=ek.grad, dev=ev.grad))
+    np.savez_compressed(HERE / "transformer_stacks.npz", **out)
+
+
 if __name__ == "__main__":
-    cnn_ops()
-    model_steps()
-    transformer_blocks()
+    if len(sys.argv) > 1 and sys.argv[1] == "stacks":   # add the round-2 fixture without rewriting the others
+        transformer_stacks()
+    else:
+        cnn_ops()
+        model_steps()
+        transformer_blocks()
+        transformer_stacks()
     for f in sorted(HERE.glob("*.npz")):
         print(f.name, f.stat().st_size)

@@ -151,3 +151,32 @@ def test_attention_masks(tb):
 
 def test_reference_cross_attention_return_kv_defect_is_recorded(tb):
     assert "not enough values to unpack" in str(tb["mca_kv_raises"])
+
+
+# ------------------------------------------------------------------------------------------ stacks
+@pytest.fixture(scope="module")
+def ts():
+    return np.load(G / "transformer_stacks.npz")
+
+
+@pytest.mark.parametrize("tag", ["lm", "lm_tied_noncausal"])
+def test_language_model_logits_and_loss(ts, tag):
+    p = _sd(ts, tag)
+    H = int(ts[f"{tag}:cfg"][2])
+    logits, loss = T.language_model(p, ts[f"{tag}:ids"], H, ts[f"{tag}:targets"])
+    assert rel(logits, ts[f"{tag}:logits"]) < 1e-5
+    assert abs(loss - float(ts[f"{tag}:loss"])) < 1e-5 * max(1.0, abs(float(ts[f"{tag}:loss"])))
+    causal = bool(ts[f"{tag}:cfg"][5])
+    assert p["_decoder._blocks.0._attn_mask"].dtype == (np.bool_ if causal else np.float32)
+    # causal stack: perturbing the last token leaves every earlier position's logits unchanged
+    ids2 = ts[f"{tag}:ids"].copy()
+    ids2[:, -1] = (ids2[:, -1] + 1) % int(ts[f"{tag}:cfg"][0])
+    moved = np.abs(T.language_model(p, ids2, H)[:, :-1] - logits[:, :-1]).max()
+    assert (moved < 1e-6) if causal else (moved > 1e-5)
+
+
+def test_encoder_and_cross_decoder_stacks(ts):
+    y, k, v = T.encoder_stack(_sd(ts, "encstack"), ts["encstack:x"], 2, return_kv=True)
+    assert rel(y, ts["encstack:y"]) < 1e-5 and rel(k, ts["encstack:k"]) < 1e-5 and rel(v, ts["encstack:v"]) < 1e-5
+    out = T.cross_decoder_stack(_sd(ts, "xdecstack"), ts["xdecstack:x"], k, v, 2)
+    assert rel(out, ts["xdecstack:y"]) < 1e-5
