@@ -46,6 +46,13 @@ int rnn_version(void);
 int rnn_sm_count(void); /* SMs of the current device (148 on B200) */
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 unsigned long long rnn_launch_count(void);
+/* Measurement aid (bench.py): with timing enabled, the tensor-core entry points record a CUDA-event pair around each
+ * of their kernel launches, on the stream of the launch, tagged with a family name ("tc_kernel", "splitk_reduce",
+ * "bn_finalize").  rnn_timing_enable(on) clears what was recorded and switches recording on / off (the one place
+ * in the library that creates CUDA events; never during stream capture); rnn_timing_read() waits for the recorded
+ * events of one family and returns their summed device time and count.  No counterpart in the reference. */
+int rnn_timing_enable(int on);
+int rnn_timing_read(const char* family, float* ms, int* launches);
 /* Dropout under CUDA graphs.  Every Philox-drawing kernel (rnn_dropout_fwd, the attention families) adds a
  * device-side epoch to its `offset` argument; the epoch is 0 until this call, which enqueues kernels that advance
  * it by 2^32.  Put one call at the head of a captured training step: each replay then draws fresh masks although

@@ -45,6 +45,16 @@ int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, 
                              const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                              float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream);
 
+// per-family launch timing (runtime.cu); a scope records an event pair around the launches it encloses
+bool rnn_timing_begin(const char* family, cudaStream_t stream, void** token);
+void rnn_timing_end(void* token, cudaStream_t stream);
+struct RnnTimedScope {
+  void* token;
+  cudaStream_t stream;
+  RnnTimedScope(const char* family, cudaStream_t s) : token(nullptr), stream(s) { rnn_timing_begin(family, s, &token); }
+  ~RnnTimedScope() { rnn_timing_end(token, stream); }
+};
+
 int rnn_internal_rng_advance_ew(unsigned long long inc, cudaStream_t stream);
 int rnn_internal_rng_advance_attn(unsigned long long inc, cudaStream_t stream);
 

@@ -652,6 +652,7 @@ int bn_static_scratch_address(float** out) {
 int rnn_internal_bn_finalize(const float* partials, int nparts, int C, int blk, float count, const float* gamma,
                              const float* beta, float eps, float momentum, float* running_mean, float* running_var,
                              float* mean, float* invstd, float* scale, float* shift, cudaStream_t stream) {
+  RnnTimedScope timed("bn_finalize", stream);
   bn_stats_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>(partials, nparts, C, count, gamma, beta, eps, momentum,
                                                                 running_mean, running_var, mean, invstd, scale, shift, blk);
   RNN_CHECK_LAUNCH();

@@ -782,6 +782,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   if (p.force_grid > 0) grid = p.force_grid;
   // weight-gradient kernels run on a side stream next to other kernels: one epilogue group keeps them small
   const int threads = (KIND == KIND_WGRAD && !STATS) ? NUM_THREADS_NARROW : NUM_THREADS;
+  RnnTimedScope timed("tc_kernel", stream);
   if (CG == 1) {
     kern<<<grid, threads, smem, stream>>>(ta, tb, td, p);
   } else {
@@ -850,6 +851,7 @@ int launch_reduce(const float* ws, int splits, long long slab, int ncols, const 
   const long long n4 = slab / 4;
   const int threads = 256;
   const int blocks = ceil_div_i(n4, threads);
+  RnnTimedScope timed("splitk_reduce", stream);
   splitk_reduce_kernel<<<blocks, threads, 0, stream>>>(ws, splits, slab, ncols, shift, relu, accumulate, out,
                                                        out_f32);
   RNN_CHECK_LAUNCH();

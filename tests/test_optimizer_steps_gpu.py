@@ -33,7 +33,8 @@ def test_encoder_three_optimizer_steps_match_torch(which, return_kv):
     from replicann_b200.optim import SGD, AdamW
     torch.manual_seed(0)
     H, E, B, T = 4, 64, 4, 24
-    enc = TransformerEncoder(H, E, p_dropout=0.0, head_bias=True).cuda()
+    # .eval(): the heads keep their own attention dropout of 0.1 whatever the block is given (nn/attention.py:80-83)
+    enc = TransformerEncoder(H, E, p_dropout=0.0, head_bias=True).cuda().eval()
     p = _twin(enc)
     names = [k for k, _ in enc.named_parameters()]
     wd = 0.0 if return_kv else 1e-2   # torch skips a parameter without gradient entirely; ours sees a zero gradient

@@ -11,8 +11,16 @@ are compared with what the reference block produced from the same (x_i, dy_i).  
 packed-pixel first convolution, BatchNorm+ReLU, max-pool) and the head (global average pool, Linear) are
 checked the same way.
 
-Tolerance (north_star): relative error <= 1e-2 of max|ref| and cosine similarity >= 0.999, on every tensor, with
-no noise-floor allowance.
+Tolerances (north_star: "bf16 paths within 1e-2 on logits and loss with gradient cosine similarity at least 0.999"),
+on every tensor, with no noise-floor allowance:
+  * forward outputs (block outputs, stem output, logits): max error <= 1e-2 of max|ref| AND cosine >= 0.999;
+  * gradients (dx and every dW / dgamma / dbeta): cosine >= 0.999 AND relative L2 error <= 5e-2 (the second bound
+    catches a wrong scale, which a cosine cannot see).
+Why gradients are not held to a max-norm bound: a ReLU whose pre-activation is within one fp32 rounding of zero
+can switch between two correct implementations; in a 6.4 M-element tensor a handful do, and each moves ONE
+gradient element by the full size of the incoming gradient.  Measured on the first run of this test (round 2):
+block-input gradients at cosine 0.99990-0.99999 with single elements off by up to 0.4 of max|ref|.  The printed
+`max` column keeps that figure visible.
 """
 import pytest
 import torch
@@ -22,7 +30,8 @@ import ref_models as R
 
 pytestmark = pytest.mark.gpu
 
-REL_TOL = 1e-2
+REL_TOL = 1e-2      # forward outputs: max error relative to max|ref|
+L2_TOL = 5e-2       # gradients: ||got - ref|| / ||ref||
 COS_TOL = 0.999
 
 
@@ -73,12 +82,20 @@ def _nets(kind):
     return R.RefResNet((1, 1, 1, 1), True, 16), ResNet((1, 1, 1, 1), bottleneck=True, n_classes=16), 64, 16
 
 
-def _check(tag, got, ref, fails):
-    r, c = _rel(got, ref), _cos(got, ref)
-    ok = r <= REL_TOL and c >= COS_TOL
-    print(f"STAT {tag}: rel {r:.3e} cos {c:.6f}{'' if ok else '  <-- FAIL'}", flush=True)
+def _l2(a, b):
+    a, b = a.detach().float().cpu().flatten().double(), b.detach().float().cpu().flatten().double()
+    return ((a - b).norm() / (b.norm() + 1e-300)).item()
+
+
+def _check(tag, got, ref, fails, grad=None):
+    """grad=None: decided from the tag (" grad" / " dx" are gradients)."""
+    if grad is None:
+        grad = tag.endswith(" grad") or tag.endswith(" dx")
+    r, c, l2 = _rel(got, ref), _cos(got, ref), _l2(got, ref)
+    ok = bool(torch.isfinite(got).all()) and c >= COS_TOL and (l2 <= L2_TOL if grad else r <= REL_TOL)
+    print(f"STAT {tag}: max {r:.3e} l2 {l2:.3e} cos {c:.6f}{'' if ok else '  <-- FAIL'}", flush=True)
     if not ok:
-        fails.append((tag, r, c))
+        fails.append((tag, r, l2, c))
 
 
 @pytest.mark.parametrize("kind", ["resnet50", "resnet18", "small_bottleneck"])
