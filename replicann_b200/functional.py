@@ -48,6 +48,19 @@ class _span:
         return False
 
 
+def timing_enable(on: bool) -> None:
+    """Library-side CUDA-event pairs around individual tensor-core / split-K / finalize launches (bench.py)."""
+    check(_lib.load().rnn_timing_enable(int(on)), "rnn_timing_enable")
+
+
+def timing_read(family: str) -> tuple[float, int]:
+    """(summed device ms, launches) of one family since timing_enable(True); waits for the recorded events."""
+    import ctypes as C
+    ms, n = C.c_float(), C.c_int()
+    check(_lib.load().rnn_timing_read(family.encode(), C.byref(ms), C.byref(n)), "rnn_timing_read")
+    return float(ms.value), int(n.value)
+
+
 def rng_advance() -> None:
     """Advance the device-side dropout epoch on the current stream (see rnn_rng_advance in the header): call it at
     the head of a step that is being captured into a CUDA graph, so that every replay draws new dropout masks."""
@@ -406,8 +419,9 @@ def colsum(x2d, *, out=None, accumulate=False):
     o = out if out is not None else torch.empty((Cn,), dtype=x2d.dtype, device=x2d.device)
     nbytes = lib.rnn_colsum_workspace(M, Cn)
     ws = workspace(nbytes, x2d.device)
-    check(lib.rnn_colsum(ptr(x2d), M, Cn, ptr(o), int(accumulate), _is_f32(x2d), ptr(ws), nbytes, cur_stream()),
-          "rnn_colsum")
+    with _span('colsum', float(x2d.numel()) * x2d.element_size(), f"M{M} C{Cn}"):
+        check(lib.rnn_colsum(ptr(x2d), M, Cn, ptr(o), int(accumulate), _is_f32(x2d), ptr(ws), nbytes, cur_stream()),
+              "rnn_colsum")
     return o
 
 
@@ -438,14 +452,16 @@ def nhwc_bf16_to_nchw_f32(x, channels=None):
 def relu_fwd(x):
     lib = _lib.load(); _cuda(x); _contig(x, "x")
     y = torch.empty_like(x)
-    check(lib.rnn_relu_fwd(ptr(x), ptr(y), x.numel(), _is_f32(x), cur_stream()), "rnn_relu_fwd")
+    with _span('elementwise', float(2 * x.numel()) * x.element_size(), "relu_fwd"):
+        check(lib.rnn_relu_fwd(ptr(x), ptr(y), x.numel(), _is_f32(x), cur_stream()), "rnn_relu_fwd")
     return y
 
 
 def relu_bwd(dy, y):
     lib = _lib.load(); _cuda(dy, y)
     dx = torch.empty_like(y)
-    check(lib.rnn_relu_bwd(ptr(dy), ptr(y), ptr(dx), y.numel(), _is_f32(y), cur_stream()), "rnn_relu_bwd")
+    with _span('elementwise', float(3 * y.numel()) * y.element_size(), "relu_bwd"):
+        check(lib.rnn_relu_bwd(ptr(dy), ptr(y), ptr(dx), y.numel(), _is_f32(y), cur_stream()), "rnn_relu_bwd")
     return dx
 
 
@@ -463,8 +479,9 @@ def relu_bwd_colsum(dy, y, *, out, accumulate=False):
     dx = torch.empty_like(y)
     nbytes = lib.rnn_colsum_workspace(M, Cn)
     ws = workspace(nbytes, y.device)
-    check(lib.rnn_relu_bwd_colsum(ptr(dy), ptr(y), ptr(dx), M, Cn, ptr(out), int(accumulate), _is_f32(y), ptr(ws),
-                                  nbytes, cur_stream()), "rnn_relu_bwd_colsum")
+    with _span('colsum', float(3 * y.numel()) * y.element_size(), f"relu_bwd M{M} C{Cn}"):
+        check(lib.rnn_relu_bwd_colsum(ptr(dy), ptr(y), ptr(dx), M, Cn, ptr(out), int(accumulate), _is_f32(y), ptr(ws),
+                                      nbytes, cur_stream()), "rnn_relu_bwd_colsum")
     return dx
 
 
@@ -485,21 +502,24 @@ def tanh_bwd(dy, y):
 def add(a, b, out=None):
     lib = _lib.load(); _req(a, torch.bfloat16, "a"); _req(b, torch.bfloat16, "b")
     y = out if out is not None else torch.empty_like(a)
-    check(lib.rnn_add_bf16(ptr(a), ptr(b), ptr(y), a.numel(), cur_stream()), "rnn_add_bf16")
+    with _span('elementwise', float(6 * a.numel()), "add"):
+        check(lib.rnn_add_bf16(ptr(a), ptr(b), ptr(y), a.numel(), cur_stream()), "rnn_add_bf16")
     return y
 
 
 def cast_f32_to_bf16(x, out=None):
     lib = _lib.load(); _req(x, torch.float32, "x")
     y = out if out is not None else torch.empty(x.shape, dtype=torch.bfloat16, device=x.device)
-    check(lib.rnn_cast_f32_to_bf16(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_f32_to_bf16")
+    with _span('elementwise', float(6 * x.numel()), "cast"):
+        check(lib.rnn_cast_f32_to_bf16(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_f32_to_bf16")
     return y
 
 
 def cast_bf16_to_f32(x, out=None):
     lib = _lib.load(); _req(x, torch.bfloat16, "x")
     y = out if out is not None else torch.empty(x.shape, dtype=torch.float32, device=x.device)
-    check(lib.rnn_cast_bf16_to_f32(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_bf16_to_f32")
+    with _span('elementwise', float(6 * x.numel()), "cast"):
+        check(lib.rnn_cast_bf16_to_f32(ptr(x), ptr(y), x.numel(), cur_stream()), "rnn_cast_bf16_to_f32")
     return y
 
 
@@ -507,16 +527,18 @@ def dropout_fwd(x, p, seed, offset):
     lib = _lib.load(); _cuda(x); _contig(x, "x")
     y = torch.empty_like(x)
     mask = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
-    check(lib.rnn_dropout_fwd(ptr(x), ptr(y), ptr(mask), x.numel(), float(p), int(seed), int(offset), _is_f32(x),
-                              cur_stream()), "rnn_dropout_fwd")
+    with _span('elementwise', float(x.numel()) * (2 * x.element_size() + 1), "dropout_fwd"):
+        check(lib.rnn_dropout_fwd(ptr(x), ptr(y), ptr(mask), x.numel(), float(p), int(seed), int(offset), _is_f32(x),
+                                  cur_stream()), "rnn_dropout_fwd")
     return y, mask
 
 
 def dropout_bwd(dy, mask, p):
     lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
     dx = torch.empty_like(dy)
-    check(lib.rnn_dropout_bwd(ptr(dy), ptr(mask), ptr(dx), dy.numel(), float(p), _is_f32(dy), cur_stream()),
-          "rnn_dropout_bwd")
+    with _span('elementwise', float(dy.numel()) * (2 * dy.element_size() + 1), "dropout_bwd"):
+        check(lib.rnn_dropout_bwd(ptr(dy), ptr(mask), ptr(dx), dy.numel(), float(p), _is_f32(dy), cur_stream()),
+              "rnn_dropout_bwd")
     return dx
 
 
@@ -581,8 +603,9 @@ def layernorm_fwd(x2d, residual, gamma, beta, eps, keep_sum=True):
     y = torch.empty_like(x2d)
     xsum = torch.empty_like(x2d) if (residual is not None and keep_sum) else None
     st = torch.empty((2, M), dtype=torch.float32, device=x2d.device)
-    check(lib.rnn_layernorm_fwd(ptr(x2d), ptr(residual), ptr(gamma), ptr(beta), float(eps), ptr(y), ptr(xsum),
-                                ptr(st[0]), ptr(st[1]), M, E, _is_f32(x2d), cur_stream()), "rnn_layernorm_fwd")
+    with _span('layernorm', float(x2d.numel()) * x2d.element_size() * (3 if residual is not None else 2), f"fwd M{M} E{E}"):
+        check(lib.rnn_layernorm_fwd(ptr(x2d), ptr(residual), ptr(gamma), ptr(beta), float(eps), ptr(y), ptr(xsum),
+                                    ptr(st[0]), ptr(st[1]), M, E, _is_f32(x2d), cur_stream()), "rnn_layernorm_fwd")
     return y, (xsum if xsum is not None else x2d), st[0], st[1]
 
 
@@ -592,9 +615,10 @@ def layernorm_bwd(dy2d, xin2d, gamma, mean, rstd, dgamma, dbeta, accumulate):
     dx = torch.empty_like(xin2d)
     nbytes = lib.rnn_layernorm_bwd_workspace(M, E)
     ws = workspace(nbytes, xin2d.device)
-    check(lib.rnn_layernorm_bwd(ptr(dy2d), ptr(xin2d), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx), ptr(dgamma),
-                                ptr(dbeta), int(accumulate), M, E, _is_f32(xin2d), ptr(ws), nbytes, cur_stream()),
-          "rnn_layernorm_bwd")
+    with _span('layernorm', float(3 * xin2d.numel()) * xin2d.element_size(), f"bwd M{M} E{E}"):
+        check(lib.rnn_layernorm_bwd(ptr(dy2d), ptr(xin2d), ptr(gamma), ptr(mean), ptr(rstd), ptr(dx), ptr(dgamma),
+                                    ptr(dbeta), int(accumulate), M, E, _is_f32(xin2d), ptr(ws), nbytes, cur_stream()),
+              "rnn_layernorm_bwd")
     return dx
 
 
@@ -616,8 +640,9 @@ def maxpool2d_fwd(x, k, s, p, return_indices=True, return_window_idx=False):
     y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
     idx = torch.empty((N, P, Q, Cn), dtype=torch.int32, device=x.device) if return_indices else None
     widx = torch.empty((N, P, Q, Cn), dtype=torch.uint8, device=x.device) if return_window_idx else None
-    check(lib.rnn_maxpool2d_fwd(ptr(x), ptr(y), ptr(idx), ptr(widx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x),
-                                cur_stream()), "rnn_maxpool2d_fwd")
+    with _span('maxpool', float(x.numel() + 2 * y.numel()) * x.element_size(), f"fwd {tuple(x.shape)} k{kh} s{sh}"):
+        check(lib.rnn_maxpool2d_fwd(ptr(x), ptr(y), ptr(idx), ptr(widx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x),
+                                    cur_stream()), "rnn_maxpool2d_fwd")
     return y, idx, widx
 
 
@@ -628,8 +653,9 @@ def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None):
     sh, sw = (s, s) if isinstance(s, int) else s
     ph, pw = (p, p) if isinstance(p, int) else p
     dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
-    check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx) if window_idx is None else None, ptr(window_idx), ptr(dx), N, H, W,
-                                Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()), "rnn_maxpool2d_bwd")
+    with _span('maxpool', float(2 * dy.numel() + dx.numel()) * dy.element_size(), f"bwd {tuple(x_shape)} k{kh} s{sh}"):
+        check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx) if window_idx is None else None, ptr(window_idx), ptr(dx), N, H, W,
+                                    Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()), "rnn_maxpool2d_bwd")
     return dx
 
 
@@ -637,8 +663,9 @@ def avgpool2d_fwd(x, k, s, p):
     lib = _lib.load(); _cuda(x); _contig(x, "x")
     N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q = _pool_args(x, k, s, p)
     y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
-    check(lib.rnn_avgpool2d_fwd(ptr(x), ptr(y), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x), cur_stream()),
-          "rnn_avgpool2d_fwd")
+    with _span('avgpool', float(x.numel() + y.numel()) * x.element_size(), "fwd"):
+        check(lib.rnn_avgpool2d_fwd(ptr(x), ptr(y), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(x), cur_stream()),
+              "rnn_avgpool2d_fwd")
     return y
 
 
@@ -649,8 +676,9 @@ def avgpool2d_bwd(dy, x_shape, k, s, p):
     sh, sw = (s, s) if isinstance(s, int) else s
     ph, pw = (p, p) if isinstance(p, int) else p
     dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
-    check(lib.rnn_avgpool2d_bwd(ptr(dy), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()),
-          "rnn_avgpool2d_bwd")
+    with _span('avgpool', float(dy.numel() + dx.numel()) * dy.element_size(), "bwd"):
+        check(lib.rnn_avgpool2d_bwd(ptr(dy), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()),
+              "rnn_avgpool2d_bwd")
     return dx
 
 
@@ -658,7 +686,8 @@ def global_avgpool_fwd(x):
     lib = _lib.load(); _cuda(x); _contig(x, "x")
     N, H, W, Cn = x.shape
     y = torch.empty((N, 1, 1, Cn), dtype=x.dtype, device=x.device)
-    check(lib.rnn_global_avgpool_fwd(ptr(x), ptr(y), N, H * W, Cn, _is_f32(x), cur_stream()), "rnn_global_avgpool_fwd")
+    with _span('avgpool', float(x.numel() + y.numel()) * x.element_size(), "global fwd"):
+        check(lib.rnn_global_avgpool_fwd(ptr(x), ptr(y), N, H * W, Cn, _is_f32(x), cur_stream()), "rnn_global_avgpool_fwd")
     return y
 
 
@@ -666,8 +695,9 @@ def global_avgpool_bwd(dy, x_shape):
     lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
     N, H, W, Cn = x_shape
     dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
-    check(lib.rnn_global_avgpool_bwd(ptr(dy), ptr(dx), N, H * W, Cn, _is_f32(dy), cur_stream()),
-          "rnn_global_avgpool_bwd")
+    with _span('avgpool', float(dy.numel() + dx.numel()) * dy.element_size(), "global bwd"):
+        check(lib.rnn_global_avgpool_bwd(ptr(dy), ptr(dx), N, H * W, Cn, _is_f32(dy), cur_stream()),
+              "rnn_global_avgpool_bwd")
     return dx
 
 
@@ -697,8 +727,9 @@ def softmax_ce(logits, target, grad_scale=None, want_grad=True):
     row_loss = torch.empty((rows + 1,), dtype=torch.float32, device=logits.device)
     dl = torch.empty_like(logits) if want_grad else None
     gs = (1.0 / rows) if grad_scale is None else grad_scale
-    check(lib.rnn_softmax_ce(ptr(logits), ptr(target), rows, cols, float(gs), ptr(row_loss), ptr(row_loss[rows:]),
-                             ptr(dl), _is_f32(logits), cur_stream()), "rnn_softmax_ce")
+    with _span('softmax_ce', float(logits.numel() * (3 if want_grad else 2)) * logits.element_size(), f"{rows}x{cols}"):
+        check(lib.rnn_softmax_ce(ptr(logits), ptr(target), rows, cols, float(gs), ptr(row_loss), ptr(row_loss[rows:]),
+                                 ptr(dl), _is_f32(logits), cur_stream()), "rnn_softmax_ce")
     return row_loss[rows], dl
 
 
@@ -745,10 +776,11 @@ def argmax(x2d):
 def sgd_step(w, buf, grad, wcopy, *, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False,
              first_step=False, grad_scale=1.0):
     lib = _lib.load(); _req(w, torch.float32, "w")
-    check(lib.rnn_sgd_step(ptr(w), ptr(buf), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
-                           int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
-                           float(momentum), float(dampening), float(weight_decay), int(nesterov), int(first_step),
-                           float(grad_scale), cur_stream()), "rnn_sgd_step")
+    with _span('optimizer', float(w.numel()) * (8 + (8 if buf is not None else 0) + grad.element_size() + (wcopy.element_size() if wcopy is not None else 0)), f"sgd n{w.numel()}"):
+        check(lib.rnn_sgd_step(ptr(w), ptr(buf), ptr(grad), int(grad.dtype == torch.bfloat16), ptr(wcopy),
+                               int(wcopy is not None and wcopy.dtype == torch.bfloat16), w.numel(), float(lr),
+                               float(momentum), float(dampening), float(weight_decay), int(nesterov), int(first_step),
+                               float(grad_scale), cur_stream()), "rnn_sgd_step")
 
 
 def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-2, step=1, grad_scale=1.0,
@@ -760,9 +792,11 @@ def adamw_step(w, m, v, grad, wcopy, *, lr, betas=(0.9, 0.999), eps=1e-8, weight
               float(betas[0]), float(betas[1]), float(eps), float(weight_decay))
     if step_dev is not None:
         _req(step_dev, torch.int64, "step_dev")
-        check(lib.rnn_adamw_step_dev(*common, ptr(step_dev), float(grad_scale), cur_stream()), "rnn_adamw_step_dev")
+        with _span('optimizer', float(w.numel()) * (24 + grad.element_size() + (wcopy.element_size() if wcopy is not None else 0)), f"adamw n{w.numel()}"):
+            check(lib.rnn_adamw_step_dev(*common, ptr(step_dev), float(grad_scale), cur_stream()), "rnn_adamw_step_dev")
     else:
-        check(lib.rnn_adamw_step(*common, int(step), float(grad_scale), cur_stream()), "rnn_adamw_step")
+        with _span('optimizer', float(w.numel()) * (24 + grad.element_size() + (wcopy.element_size() if wcopy is not None else 0)), f"adamw n{w.numel()}"):
+            check(lib.rnn_adamw_step(*common, int(step), float(grad_scale), cur_stream()), "rnn_adamw_step")
 
 
 def counter_add(counter: torch.Tensor, inc: int = 1) -> None:

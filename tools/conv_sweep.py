@@ -23,24 +23,45 @@ VGG = [(128, 224, 64, 64, 3, 1, 1), (128, 112, 64, 128, 3, 1, 1), (128, 112, 128
        (128, 56, 256, 256, 3, 1, 1), (128, 28, 256, 512, 3, 1, 1), (128, 28, 512, 512, 3, 1, 1), (128, 14, 512, 512, 3, 1, 1)]
 
 
-def time_it(fn, iters=10):
-    for _ in range(3):
+_flush_buf = None
+
+
+def _flush_l2():
+    """Write a buffer larger than L2 (126 MB) so that the next timed launch starts from HBM."""
+    global _flush_buf
+    if _flush_buf is None:
+        _flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    _flush_buf.zero_()
+
+
+def time_it(fn, iters=10, warmup=3, flush_l2=False):
+    for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
+    if not flush_l2:
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / iters
+    pairs = []
     for _ in range(iters):
+        _flush_l2()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
         fn()
-    e1.record()
+        e1.record()
+        pairs.append((e0, e1))
     torch.cuda.synchronize()
-    return e0.elapsed_time(e1) / iters
+    return sum(a.elapsed_time(b) for a, b in pairs) / iters
 
 
-def main():
-    peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
-    peak = peaks.get("bf16_tflops", 1590.0)
-    out = open(sys.argv[1], "w") if len(sys.argv) > 1 else sys.stdout
-    out.write("net\tshape\tpass\tus\tTFLOP/s\tfrac_measured_peak\tfrac_nominal_2250\n")
+def sweep(RF, flush_l2=False, iters=10, warmup=3):
+    """Returns (rows, total FLOPs, total ms, launches): one row per (shape, pass)."""
+    rows, tot_fl, tot_ms = [], 0.0, 0.0
+    l0 = RF.launch_count()
     for net, shapes in (("resnet50", RESNET), ("vgg16", VGG)):
         for N, H, C, K, R, stride, pad in shapes:
             x = torch.randn(N, H, H, C, device="cuda").to(torch.bfloat16)
@@ -55,12 +76,30 @@ def main():
                                                                                 stride=stride, pad=pad)),
                              ("dgrad", lambda: RF.conv2d_dgrad(dy, w, tuple(x.shape), stride=stride, pad=pad)),
                              ("wgrad", lambda: RF.conv2d_wgrad(x, dy, tuple(w.shape), stride=stride, pad=pad))):
-                ms = time_it(fn)
-                tf = fl / ms / 1e9
-                out.write(f"{net}\tN{N} {H}x{H} C{C} K{K} {R}x{R} s{stride}\t{name}\t{ms*1e3:.1f}\t{tf:.1f}\t{tf/peak:.3f}\t{tf/2250:.3f}\n")
+                ms = time_it(fn, iters, warmup, flush_l2)
+                rows.append({"net": net, "shape": f"N{N} {H}x{H} C{C} K{K} {R}x{R} s{stride}", "pass": name,
+                             "us": ms * 1e3, "tflops": fl / ms / 1e9})
+                if name != "fprop+bnstats":      # the three passes of a training step count once each
+                    tot_fl += fl
+                    tot_ms += ms
             del x, w, dy
-    if out is not sys.stdout:
-        out.close()
+    return rows, tot_fl, tot_ms, RF.launch_count() - l0
+
+
+def write_tsv(rows, path, peak):
+    with open(path, "w") as out:
+        out.write("net\tshape\tpass\tus\tTFLOP/s\tfrac_measured_peak\tfrac_nominal_2250\n")
+        for r in rows:
+            out.write(f"{r['net']}\t{r['shape']}\t{r['pass']}\t{r['us']:.1f}\t{r['tflops']:.1f}\t"
+                      f"{r['tflops'] / peak:.3f}\t{r['tflops'] / 2250:.3f}\n")
+
+
+def main():
+    peaks = json.loads((ROOT / "MEASURED_PEAKS.json").read_text()) if (ROOT / "MEASURED_PEAKS.json").exists() else {}
+    peak = peaks.get("bf16_tflops", 1590.0)
+    rows, fl, ms, _ = sweep(RF)
+    write_tsv(rows, sys.argv[1] if len(sys.argv) > 1 else "/dev/stdout", peak)
+    print(f"total: {fl / ms / 1e9:.1f} TFLOP/s over fprop + dgrad + wgrad of every shape", file=sys.stderr)
 
 
 if __name__ == "__main__":

@@ -74,7 +74,9 @@ with open(out + "_dram_step.tsv", "w") as f:
         f.write(f"{k}\t{a[0]}\t{a[1]/1e9:.3f}\t{a[2]/1e9:.3f}\t{a[3]/1e3:.3f}\t{(a[1]+a[2])/max(a[3],1e-9)/1e3:.0f}\t"
                 f"{(a[1]+a[2])/a[0]:.0f}\n")
 tc = fam["tc_kernel"]
+bn = sum(a[1] + a[2] for k, a in fam.items() if k.startswith("bn_"))
 json.dump({"source": out + "_dram_step.tsv", "tc_kernel_dram_bytes_per_launch": (tc[1] + tc[2]) / max(tc[0], 1),
-           "tc_kernel_launches_per_step": tc[0], "step_dram_bytes": dram}, open(out + "_traffic.json", "w"), indent=1)
+           "tc_kernel_launches_per_step": tc[0], "step_dram_bytes": dram, "bn_family_dram_bytes_per_step": bn},
+          open(out + "_traffic.json", "w"), indent=1)
 print(open(out + "_launches_step.txt").read()[:3000])
 print(open(out + "_dram_step.tsv").read()[:1500])
