@@ -30,16 +30,16 @@ UNIT = "images/s"
 # selectable so that the driver can run them with the same JSON contract.
 CONFIGS = {
     "resnet50": {"metric": "train images/sec, ResNet-50 bf16", "batch": 256, "shape": (3, 224, 224), "classes": 1000,
-                 "dtype": "bf16", "cpu_batch": 8,
+                 "dtype": "bf16", "cpu_batch": 64, "cpu_steps": 8,
                  "workload": "ResNet-50 bf16 data-parallel training, batch 256/GPU, fused BN+ReLU, synthetic 3x224x224 (configs[3])"},
     "vgg16": {"metric": "train images/sec, VGG-16 bf16", "batch": 128, "shape": (3, 224, 224), "classes": 1000,
-              "dtype": "bf16", "cpu_batch": 4,
+              "dtype": "bf16", "cpu_batch": 16, "cpu_steps": 8,
               "workload": "VGG-16 bf16 data-parallel training, batch 128/GPU, dropout 0.5, synthetic 3x224x224 (configs[2])"},
     "alexnet": {"metric": "train images/sec, AlexNet bf16", "batch": 256, "shape": (3, 224, 224), "classes": 1000,
-                "dtype": "bf16", "cpu_batch": 32,
+                "dtype": "bf16", "cpu_batch": 256, "cpu_steps": 8,
                 "workload": "AlexNet bf16 fwd+bwd (+ fused SGD), batch 256, dropout 0.5, synthetic 3x224x224 (configs[1])"},
     "lenet5": {"metric": "train images/sec, LeNet-5 fp32", "batch": 64, "shape": (1, 28, 28), "classes": 10,
-               "dtype": "f32", "cpu_batch": 64,
+               "dtype": "f32", "cpu_batch": 64, "cpu_steps": 3000,
                "workload": "LeNet-5 fp32 train step, batch 64, synthetic 1x28x28 (configs[0])"},
 }
 
@@ -165,7 +165,7 @@ def run_reference(args) -> None:
     if rank != 0:
         return
     cfg = CONFIGS[args.config]
-    steps, warmup = max(args.steps, 5), max(args.warmup, 2)
+    steps, warmup = max(args.steps, 5, cfg["cpu_steps"] if args.config == "lenet5" else 0), max(args.warmup, 2)
     # one probe step sizes the per-step sample so that the whole run stays within ~3 minutes
     batch = cfg["cpu_batch"]
     probe = _torch_cpu_steps(args.config, batch, 1, 0, os.cpu_count() or 1)[0]
@@ -373,7 +373,8 @@ def run_gpu(args) -> None:
 
     cpu_base = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_base = _cpu_baseline(args.config, cfg["cpu_batch"], 5, 1)
+        # a bounded sample of the same workload, sized for roughly 10 s of host work on a 16-core box
+        cpu_base = _cpu_baseline(args.config, cfg["cpu_batch"], cfg["cpu_steps"], 2)
 
     if rank == 0:
         # DRAM bytes per launch / per step: from the committed ncu pass over one step (tools/step_profile.py)

@@ -652,7 +652,13 @@ int make_tmap_2d(CUtensorMap* m, const void* ptr, long long rows, long long cols
   CUresult r = g_encode_tiled(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box,
                               estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  RNN_REQUIRE(r == CUDA_SUCCESS, RNN_ERR_TENSORMAP);
+  if (r != CUDA_SUCCESS) {
+    char msg[256];
+    snprintf(msg, sizeof(msg), "cuTensorMapEncodeTiled(2d) -> CUresult %d: ptr %p rows %lld cols %lld ld %lld box_rows %d",
+             (int)r, ptr, rows, cols, ld, box_rows);
+    rnn_set_last_message(__FILE__, __LINE__, msg);
+    return RNN_ERR_TENSORMAP;
+  }
   return RNN_OK;
 }
 

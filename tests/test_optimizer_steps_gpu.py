@@ -62,11 +62,15 @@ def test_encoder_three_optimizer_steps_match_torch(which, return_kv):
         yo = enc(x.cuda(), return_kv=return_kv)
         yo = yo[0] + 0.1 * yo[1] + 0.2 * yo[2] if return_kv else yo
         ((yo - tgt.cuda()) ** 2).mean().backward()
+        # some gradients are analytically zero (a key bias shifts every score of a row alike and softmax does not see
+        # it): compare those against the scale of the whole gradient, not against their own rounding noise
+        gmax = max(float(v.abs().max()) for v in gref.values() if v is not None)
         for k, prm in enc.named_parameters():
             if gref[k] is None:
                 assert float(prm.grad.abs().max()) == 0.0, (step, k)   # cleared, not stale
             else:
-                assert rel(prm.grad, gref[k]) < 2e-4, (step, k, rel(prm.grad, gref[k]))
+                err = float((prm.grad.detach().float().cpu() - gref[k]).abs().max())
+                assert err < 2e-4 * max(float(gref[k].abs().max()), 1e-3 * gmax), (step, k, err)
         opt.step()
         for k, prm in enc.named_parameters():
             assert rel(prm, p[k]) < 1e-4, (step, k, rel(prm, p[k]))
