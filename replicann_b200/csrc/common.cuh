@@ -55,6 +55,8 @@ struct RnnTimedScope {
   ~RnnTimedScope() { rnn_timing_end(token, stream); }
 };
 
+int rnn_internal_tmap_3d(CUtensorMap* m, const void* ptr, long long slabs, long long rows, long long inner, long long ld,
+                         long long bstride, int box_rows);
 int rnn_internal_rng_advance_ew(unsigned long long inc, cudaStream_t stream);
 int rnn_internal_rng_advance_attn(unsigned long long inc, cudaStream_t stream);
 

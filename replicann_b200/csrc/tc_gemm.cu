@@ -628,6 +628,16 @@ EncodeTiledFn g_encode_tiled = nullptr;
 EncodeIm2colFn g_encode_im2col = nullptr;
 
 int load_driver_entry_points() {
+  // cuTensorMapEncode* are driver-API calls and need a CUDA context that is current on THIS host thread.  A thread
+  // that has not yet made a runtime call of its own (torch runs backward passes on autograd worker threads) has
+  // none bound, and the encode then fails with CUDA_ERROR_INVALID_CONTEXT (seen when a weight-gradient launch was
+  // the first CUDA work of a backward thread).  cudaSetDevice binds the primary context; it is a thread-local
+  // no-op when already bound.
+  {
+    int dev = 0;
+    RNN_CUDA(cudaGetDevice(&dev));
+    RNN_CUDA(cudaSetDevice(dev));
+  }
   if (g_encode_tiled && g_encode_im2col) return RNN_OK;
   void* f = nullptr;
   cudaDriverEntryPointQueryResult qr;
@@ -937,6 +947,15 @@ WgradPlan plan_wgrad(const rnn_conv_desc* d) {
 }
 
 }  // namespace
+
+// Tensor-map builders for the other translation units (the fused attention kernels in attention.cu): a bf16 tensor
+// [slabs][rows][inner] with a {64 inner, box_rows, 1} box in SWIZZLE_128B, for TMA loads and stores alike.
+int rnn_internal_tmap_3d(CUtensorMap* m, const void* ptr, long long slabs, long long rows, long long inner, long long ld,
+                         long long bstride, int box_rows) {
+  int rc = load_driver_entry_points();
+  if (rc != RNN_OK) return rc;
+  return make_tmap_3d(m, ptr, slabs, rows, inner, ld, bstride, box_rows);
+}
 
 // =============================================================================================
 // C ABI
