@@ -317,6 +317,20 @@ int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, c
                          const void* dz, void* dq, void* dk, void* dv, void* ws, size_t ws_bytes,
                          cudaStream_t stream);
 
+/* Fused form of the same attention (bf16, head size 64 or 128, T and Tk multiples of 8, strides multiples of 8
+ * elements -- rnn_attention_fused_supported()): ONE kernel per direction pair keeps scores and probabilities on the
+ * SM -- q k^T into TMEM by tcgen05.mma, scale / mask / softmax / Philox dropout on the accumulator rows read back with
+ * tcgen05.ld, probabilities handed to the second tcgen05.mma through shared memory -- so the [B,H,T,Tk] tensors of
+ * nn/attention.py:37-47 (and of rnn_attention_tc_*) never touch HBM.  Saved for backward: z and lse [B,H,T] only.
+ * Backward recomputes the probabilities from lse (same Philox counters): dq, then dk / dv; `delta` is [B,H,T] fp32
+ * scratch.  Same masks (bool: nonzero = masked out; float32: additive), scale and dropout stream as rnn_attention_fwd. */
+int rnn_attention_fused_supported(const rnn_attn_desc* d);
+int rnn_attention_fused_fwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                            void* z, float* lse, cudaStream_t stream);
+int rnn_attention_fused_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                            const void* z, const void* dz, const float* lse, float* delta, void* dq, void* dk, void* dv,
+                            cudaStream_t stream);
+
 /* fp32 form of the same pipeline at fp32 accuracy (the reference's default dtype): every operand of the six
  * contractions is split into three bf16 pieces and each contraction is one batched tcgen05 GEMM over a reduction
  * six times as long, fp32 out; head size, T and Tk multiples of 8.  `saved` keeps the fp32 probabilities. */

@@ -11,7 +11,7 @@
 // shared-memory K/V tiles; the GEMMs around it are the tcgen05 kernels in tc_gemm.cu.
 #include <string.h>
 
-#include "common.cuh"
+#include "tc_ptx.cuh"
 
 namespace {
 
@@ -636,6 +636,95 @@ int slab_gemm(int nz, int M, int N, int K, int a_mn, int b_mn, const bf16* A, co
   return rnn_gemm_batched_bf16(&g, A, Bm, D, stream);
 }
 
+#include "attention_fused.cuh"
+
+// ---- host side of the fused tcgen05 attention ------------------------------------------------------------------
+int fused_ok(const rnn_attn_desc* d) {
+  if (d == nullptr) return 0;
+  if (!(d->hs == 64 || d->hs == 128) || d->T % 8 != 0 || d->Tk % 8 != 0) return 0;
+  if (d->q_rs % 8 || d->k_rs % 8 || d->v_rs % 8 || d->z_rs % 8 || d->q_bs % 8 || d->k_bs % 8 || d->v_bs % 8 || d->z_bs % 8)
+    return 0;
+  return (long long)d->B * d->H < 65536 && d->B <= 65535 && d->H <= 65535;
+}
+
+fa::Params fused_params(const rnn_attn_desc* d, const void* mask) {
+  fa::Params p;
+  memset(&p, 0, sizeof(p));
+  p.B = d->B; p.H = d->H; p.T = d->T; p.Tk = d->Tk;
+  p.scale = d->scale;
+  p.mask = mask; p.mask_kind = d->mask_kind; p.mask_bs = d->mask_bs; p.mask_rs = d->mask_rs;
+  const long long esz = d->mask_kind == 2 ? 4 : 1;
+  p.mask_vec = mask != nullptr && (reinterpret_cast<uintptr_t>(mask) & 15u) == 0 && (d->mask_rs * esz) % 16 == 0 &&
+               (d->mask_bs * esz) % 16 == 0;
+  p.p_drop = d->p_drop; p.seed = d->seed; p.offset = d->offset;
+  return p;
+}
+
+// operand [B][rows][H*hs] with explicit row / batch strides -> 3-D tensor map, box {64, box_rows, 1}
+int fused_map(CUtensorMap* m, const void* ptr, const rnn_attn_desc* d, int rows, long long rs, long long bs, int box_rows) {
+  RNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15u) == 0, RNN_ERR_ALIGN);
+  const long long bstride = d->B == 1 ? (long long)rows * rs : bs;
+  return rnn_internal_tmap_3d(m, ptr, d->B, rows, (long long)d->H * d->hs, rs, bstride, box_rows);
+}
+
+template <int HS>
+int fused_fwd_launch(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask, void* z,
+                     float* lse, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv, tz;
+  int rc = fused_map(&tq, q, d, d->T, d->q_rs, d->q_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tk, k, d, d->Tk, d->k_rs, d->k_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tv, v, d, d->Tk, d->v_rs, d->v_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tz, z, d, d->T, d->z_rs, d->z_bs, 32);
+  if (rc != RNN_OK) return rc;
+  fa::Params p = fused_params(d, mask);
+  p.lse = lse;
+  auto kern = fa::fwd_kernel<HS>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  RNN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::FwdCfg<HS>::SMEM));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  kern<<<dim3(ceil_div_i(d->T, fa::BQ), d->H, d->B), fa::NTHREADS, fa::FwdCfg<HS>::SMEM, stream>>>(tq, tk, tv, tz, p);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
+template <int HS>
+int fused_bwd_launch(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask, const void* z,
+                     const void* dz, const float* lse, float* delta, void* dq, void* dk, void* dv, cudaStream_t stream) {
+  CUtensorMap tq, tk, tv, tdo, tdq, tdk, tdv;
+  int rc = fused_map(&tq, q, d, d->T, d->q_rs, d->q_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tk, k, d, d->Tk, d->k_rs, d->k_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tv, v, d, d->Tk, d->v_rs, d->v_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tdo, dz, d, d->T, d->dz_rs, d->dz_bs, 128);
+  if (rc == RNN_OK) rc = fused_map(&tdq, dq, d, d->T, d->q_rs, d->q_bs, 32);
+  if (rc == RNN_OK) rc = fused_map(&tdk, dk, d, d->Tk, d->k_rs, d->k_bs, 32);
+  if (rc == RNN_OK) rc = fused_map(&tdv, dv, d, d->Tk, d->v_rs, d->v_bs, 32);
+  if (rc != RNN_OK) return rc;
+  fa::Params p = fused_params(d, mask);
+  p.lse = const_cast<float*>(lse);
+  p.delta = delta;
+  p.z = reinterpret_cast<const bf16*>(z); p.dz = reinterpret_cast<const bf16*>(dz);
+  p.z_bs = d->z_bs; p.z_rs = d->z_rs; p.dz_bs = d->dz_bs; p.dz_rs = d->dz_rs;
+  auto k1 = fa::dq_kernel<HS>;
+  auto k2 = fa::dkdv_kernel<HS>;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  RNN_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    RNN_CUDA(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::DqCfg<HS>::SMEM));
+    RNN_CUDA(cudaFuncSetAttribute(k2, cudaFuncAttributeMaxDynamicSharedMemorySize, fa::DkvCfg<HS>::SMEM));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  k1<<<dim3(ceil_div_i(d->T, fa::BQ), d->H, d->B), fa::NTHREADS, fa::DqCfg<HS>::SMEM, stream>>>(tq, tk, tv, tdo, tdq, p);
+  RNN_CHECK_LAUNCH();
+  k2<<<dim3(ceil_div_i(d->Tk, fa::BKV), d->H, d->B), fa::NTHREADS, fa::DkvCfg<HS>::SMEM, stream>>>(tq, tk, tv, tdo, tdk, tdv, p);
+  RNN_CHECK_LAUNCH();
+  return RNN_OK;
+}
+
 int tc_check(const rnn_attn_desc* d) {
   int rc = check(d);
   if (rc != RNN_OK) return rc;
@@ -822,6 +911,31 @@ int rnn_attention_tc_bwd(const rnn_attn_desc* d, const void* q, const void* k, c
   spec_heads(g.b_ld, g.b_bstride, g.b_per_head, g.b_hoff, d->q_rs, d->q_bs, d->hs);
   spec_heads(g.d_ld, g.d_bstride, g.d_per_head, g.d_hoff, d->k_rs, d->k_bs, d->hs);
   return rnn_gemm_batched_bf16(&g, dS, q, dk, stream);
+}
+
+// ---- fused tcgen05 attention (scores stay in TMEM / shared memory; see attention_fused.cuh) ----------------------
+int rnn_attention_fused_supported(const rnn_attn_desc* d) { return fused_ok(d); }
+
+int rnn_attention_fused_fwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                            void* z, float* lse, cudaStream_t stream) {
+  int rc = check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(fused_ok(d), RNN_ERR_SHAPE);
+  RNN_REQUIRE((d->mask_kind == 0) == (mask == nullptr), RNN_ERR_DTYPE);
+  if (d->hs == 64) return fused_fwd_launch<64>(d, q, k, v, mask, z, lse, stream);
+  return fused_fwd_launch<128>(d, q, k, v, mask, z, lse, stream);
+}
+
+int rnn_attention_fused_bwd(const rnn_attn_desc* d, const void* q, const void* k, const void* v, const void* mask,
+                            const void* z, const void* dz, const float* lse, float* delta, void* dq, void* dk, void* dv,
+                            cudaStream_t stream) {
+  int rc = check(d);
+  if (rc != RNN_OK) return rc;
+  RNN_REQUIRE(fused_ok(d) && d->dz_rs % 8 == 0 && d->dz_bs % 8 == 0, RNN_ERR_SHAPE);
+  RNN_REQUIRE((d->mask_kind == 0) == (mask == nullptr), RNN_ERR_DTYPE);
+  RNN_REQUIRE(lse != nullptr && delta != nullptr, RNN_ERR_WORKSPACE);
+  if (d->hs == 64) return fused_bwd_launch<64>(d, q, k, v, mask, z, dz, lse, delta, dq, dk, dv, stream);
+  return fused_bwd_launch<128>(d, q, k, v, mask, z, dz, lse, delta, dq, dk, dv, stream);
 }
 
 // ---- fp32 attention on the tensor cores at fp32 accuracy (three-piece bf16 splits, see above) -----------------

@@ -935,6 +935,51 @@ def attention_tc_bwd(q, k, v, saved, dz, n_heads, hs, scale, dq, dk, dv, mask=No
                                        ptr(ws), nbytes, cur_stream()), "rnn_attention_tc_bwd")
 
 
+_attn_fused_enabled = os.environ.get("RNN_ATTN_FUSED", "1") != "0"
+
+
+def attention_fused_ok(q, k, v, n_heads, hs) -> bool:
+    """Whether the fused tcgen05 attention takes these operands: bf16, head size 64 or 128, T / Tk multiples of 8,
+    16-byte aligned rows.  (RNN_ATTN_FUSED=0 routes to the unfused tensor-core pipeline instead: A/B timing.)"""
+    if not (_attn_fused_enabled and _attn_tc_enabled) or q.dtype != torch.bfloat16 or hs not in (64, 128):
+        return False
+    B, T, _ = q.shape
+    return (T % 8 == 0 and k.shape[1] % 8 == 0 and B * n_heads < 65536
+            and all(t.stride(0) % 8 == 0 and t.stride(1) % 8 == 0 and t.data_ptr() % 16 == 0 for t in (q, k, v)))
+
+
+def attention_fused_fwd(q, k, v, n_heads, hs, scale, mask=None, p_drop=0.0, seed=0, offset=0):
+    """Fused tensor-core attention forward: z [B,T,H*hs] and the log-sum-exp [B,H,T] (all that backward needs)."""
+    lib = _lib.load(); _cuda(q, k, v, mask)
+    for t, n in ((q, "q"), (k, "k"), (v, "v")):
+        _check_qkv(t, n)
+        _req_dtype(t, torch.bfloat16, n)
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    z = torch.empty((B, T, n_heads * hs), dtype=q.dtype, device=q.device)
+    lse = torch.empty((B, n_heads, T), dtype=torch.float32, device=q.device)
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, None, scale, mask, p_drop, seed, offset)
+    with _span("attention_fused", 4.0 * B * n_heads * T * Tk * hs, f"fwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_fused_fwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(lse), cur_stream()),
+              "rnn_attention_fused_fwd")
+    return z, lse
+
+
+def attention_fused_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask=None, p_drop=0.0, seed=0, offset=0):
+    lib = _lib.load(); _cuda(q, k, v, z, dz)
+    _check_qkv(dz, "dz")
+    for a, b, n in ((dq, q, "dq"), (dk, k, "dk"), (dv, v, "dv")):
+        if a.stride() != b.stride() or a.shape != b.shape:
+            raise ValueError(f"{n} must have the shape and strides of its forward tensor")
+    B, T, _ = q.shape
+    Tk = k.shape[1]
+    delta = torch.empty((B, n_heads, T), dtype=torch.float32, device=q.device)
+    d = _attn_desc(B, n_heads, T, Tk, hs, q, k, v, z, dz, scale, mask, p_drop, seed, offset)
+    with _span("attention_fused", 10.0 * B * n_heads * T * Tk * hs, f"bwd B{B} H{n_heads} T{T} Tk{Tk} hs{hs}"):
+        check(lib.rnn_attention_fused_bwd(d, ptr(q), ptr(k), ptr(v), ptr(mask), ptr(z), ptr(dz), ptr(lse), ptr(delta),
+                                          ptr(dq), ptr(dk), ptr(dv), cur_stream()), "rnn_attention_fused_bwd")
+
+
 def attention_f32_tc_ok(q, k, v, n_heads, hs) -> bool:
     """Whether the fp32 tensor-core attention pipeline takes these operands (fp32, head size / T / Tk % 8, aligned
     strides, and enough work to pay for the operand splits)."""

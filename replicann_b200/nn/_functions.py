@@ -627,9 +627,14 @@ class AttentionFn(Function):
         # bf16 with a 64-multiple head size: contractions on the tensor cores (batched tcgen05 GEMMs over all heads);
         # anything else: the fused fp32-FMA kernel
         # fp32 large enough to pay for operand splits: the same pipeline at fp32 accuracy (three-piece bf16 splits)
-        ctx.tc = 1 if RF.attention_tc_ok(q, k, v, n_heads, hs) else (
-            2 if RF.attention_f32_tc_ok(q, k, v, n_heads, hs) else 0)
+        ctx.tc = 3 if RF.attention_fused_ok(q, k, v, n_heads, hs) else (
+            1 if RF.attention_tc_ok(q, k, v, n_heads, hs) else (2 if RF.attention_f32_tc_ok(q, k, v, n_heads, hs) else 0))
         ctx.cfg = (scale, p_drop, n_heads, hs, seed, offset, packed)
+        if ctx.tc == 3:
+            # fused tcgen05 kernel: scores and probabilities stay on the SM; only z and the log-sum-exp are kept
+            z, lse = RF.attention_fused_fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
+            ctx.save_for_backward(q, k, v, z, lse, mask)
+            return z
         if ctx.tc:
             fwd = RF.attention_tc_fwd if ctx.tc == 1 else RF.attention_f32_tc_fwd
             z, saved = fwd(q, k, v, n_heads, hs, scale, mask, p_drop, seed, offset)
@@ -642,7 +647,7 @@ class AttentionFn(Function):
     @staticmethod
     def backward(ctx, dz):
         scale, p_drop, n_heads, hs, seed, offset, packed = ctx.cfg
-        if ctx.tc:
+        if ctx.tc in (1, 2):
             q, k, v, saved, mask = ctx.saved_tensors
         else:
             q, k, v, z, lse, mask = ctx.saved_tensors
@@ -655,7 +660,11 @@ class AttentionFn(Function):
             dq = torch.empty_strided(q.shape, q.stride(), dtype=q.dtype, device=q.device)
             dk = torch.empty_strided(k.shape, k.stride(), dtype=k.dtype, device=k.device)
             dv = torch.empty_strided(v.shape, v.stride(), dtype=v.dtype, device=v.device)
-        if ctx.tc:
+        if ctx.tc == 3:
+            if dz.stride(0) % 8 or dz.stride(1) % 8 or dz.data_ptr() % 16:
+                dz = dz.contiguous()
+            RF.attention_fused_bwd(q, k, v, z, dz, lse, n_heads, hs, scale, dq, dk, dv, mask, p_drop, seed, offset)
+        elif ctx.tc:
             if dz.stride(0) % 8 or dz.stride(1) % 8 or dz.data_ptr() % 16:
                 dz = dz.contiguous()
             bwd = RF.attention_tc_bwd if ctx.tc == 1 else RF.attention_f32_tc_bwd
