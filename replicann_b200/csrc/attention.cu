@@ -42,8 +42,10 @@ constexpr int MAXD = 4;    // head size <= 32 * MAXD = 128
 static __device__ unsigned long long g_rng_epoch_attn = 0ull;
 __global__ void rng_advance_attn_kernel(unsigned long long inc) { g_rng_epoch_attn += inc; }
 
-// Philox-4x32-10: one call yields four 32-bit words.  Attention-weight element `idx` uses word (idx & 3) of the
-// block with counter (idx >> 2), so a kernel that walks four consecutive elements pays for one call.
+// Philox-4x32-10: one call yields four 32-bit words = EIGHT 16-bit keep decisions.  Attention-weight element `idx`
+// uses half (idx & 1) of word ((idx >> 1) & 3) of the block with counter (idx >> 3), so a kernel that walks eight
+// consecutive elements pays for one call (the generator, not the exponential, is what the dropout path of the
+// fused kernels spends its ALU time on).  A 16-bit decision resolves p to 1.5e-5.
 __device__ __forceinline__ uint4 philox4(unsigned long long seed, unsigned long long offset, unsigned long long ctr) {
   const uint32_t M0 = 0xD2511F53u, M1 = 0xCD9E8D57u, W0 = 0x9E3779B9u, W1 = 0xBB67AE85u;
   uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
@@ -58,18 +60,22 @@ __device__ __forceinline__ uint4 philox4(unsigned long long seed, unsigned long 
   }
   return make_uint4(c0, c1, c2, c3);
 }
-__device__ __forceinline__ uint32_t philox_word(unsigned long long seed, unsigned long long offset,
+// 16-bit random value of attention-weight element `idx`
+__device__ __forceinline__ uint32_t philox_half(unsigned long long seed, unsigned long long offset,
                                                 unsigned long long idx) {
-  const uint4 r = philox4(seed, offset, idx >> 2);
-  const int w = (int)(idx & 3);
-  return w == 0 ? r.x : w == 1 ? r.y : w == 2 ? r.z : r.w;
+  const uint4 r = philox4(seed, offset, idx >> 3);
+  const int w = (int)((idx >> 1) & 3);
+  const uint32_t word = w == 0 ? r.x : w == 1 ? r.y : w == 2 ? r.z : r.w;
+  return (idx & 1) ? (word >> 16) : (word & 0xFFFFu);
 }
+// keep threshold on the 16-bit scale: an element is kept when its value is >= the threshold
+__device__ __forceinline__ uint32_t keep_thresh16(float p_drop) { return (uint32_t)(p_drop * 65536.0f); }
 
 __device__ __forceinline__ float keep_scale(const AttnParams& p, int bh, int i, int j) {
   if (p.p_drop <= 0.f) return 1.f;
   const unsigned long long idx = ((unsigned long long)bh * p.T + i) * p.Tk + j;
-  const uint32_t r = philox_word(p.seed, p.offset, idx);
-  return r >= (uint32_t)(p.p_drop * 4294967296.0) ? 1.f / (1.f - p.p_drop) : 0.f;
+  const uint32_t r = philox_half(p.seed, p.offset, idx);
+  return r >= keep_thresh16(p.p_drop) ? 1.f / (1.f - p.p_drop) : 0.f;
 }
 
 __device__ __forceinline__ float masked_score(const AttnParams& p, float s, int b, int i, int j) {
@@ -489,8 +495,8 @@ attn_softmax_fwd_kernel(const float* __restrict__ S, TP* __restrict__ P, TP* __r
   l = warp_sum(l);
   const float inv = 1.f / l;
   const float keep = 1.f / (1.f - p.p_drop);
-  const uint32_t thresh = (uint32_t)(p.p_drop * 4294967296.0);
-  const unsigned long long row_idx = ((unsigned long long)bh * p.T + i) * p.Tk;   // multiple of 4
+  const uint32_t thresh = keep_thresh16(p.p_drop);
+  const unsigned long long row_idx = ((unsigned long long)bh * p.T + i) * p.Tk;   // multiple of 8
   for (int j4 = lane; j4 < n4; j4 += 32) {
     float s[4], pv[4];
     score4(j4, s);
@@ -498,9 +504,11 @@ attn_softmax_fwd_kernel(const float* __restrict__ S, TP* __restrict__ P, TP* __r
     for (int e = 0; e < 4; ++e) pv[e] = __expf(s[e] - m) * inv;
     store4(P + r * p.Tk + 4 * j4, pv);
     if (Pd != P) {
-      const uint4 rnd = philox4(p.seed, p.offset, (row_idx >> 2) + j4);
-      const float pk[4] = {rnd.x >= thresh ? pv[0] * keep : 0.f, rnd.y >= thresh ? pv[1] * keep : 0.f,
-                           rnd.z >= thresh ? pv[2] * keep : 0.f, rnd.w >= thresh ? pv[3] * keep : 0.f};
+      // elements 4*j4 .. 4*j4+3 of the row: words (x, y) or (z, w) of the 8-element block they fall into
+      const uint4 rnd = philox4(p.seed, p.offset, (row_idx >> 3) + (j4 >> 1));
+      const uint32_t w0 = (j4 & 1) ? rnd.z : rnd.x, w1 = (j4 & 1) ? rnd.w : rnd.y;
+      const float pk[4] = {(w0 & 0xFFFFu) >= thresh ? pv[0] * keep : 0.f, (w0 >> 16) >= thresh ? pv[1] * keep : 0.f,
+                           (w1 & 0xFFFFu) >= thresh ? pv[2] * keep : 0.f, (w1 >> 16) >= thresh ? pv[3] * keep : 0.f};
       store4(Pd + r * p.Tk + 4 * j4, pk);
     }
   }

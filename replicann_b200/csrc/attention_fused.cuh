@@ -97,13 +97,17 @@ __device__ __forceinline__ void scores32(const Params& p, const uint32_t* raw, f
 // dropout keep factors (0 or 1/(1-p)) of 32 consecutive keys of row (bh, i): the Philox words of keep_scale()
 __device__ __forceinline__ void keep32(const Params& p, float* kf, int bh, int i, int j0) {
   const float keep = 1.f / (1.f - p.p_drop);
-  const uint32_t thresh = (uint32_t)(p.p_drop * 4294967296.0);
-  const unsigned long long idx0 = ((unsigned long long)bh * p.T + i) * p.Tk + j0;   // multiple of 4 (Tk % 8 == 0)
+  const uint32_t thresh = keep_thresh16(p.p_drop);
+  const unsigned long long idx0 = ((unsigned long long)bh * p.T + i) * p.Tk + j0;   // multiple of 8 (Tk % 8 == 0)
 #pragma unroll
-  for (int e4 = 0; e4 < 8; ++e4) {
-    const uint4 r = philox4(p.seed, p.offset, (idx0 >> 2) + e4);
-    kf[4 * e4 + 0] = r.x >= thresh ? keep : 0.f; kf[4 * e4 + 1] = r.y >= thresh ? keep : 0.f;
-    kf[4 * e4 + 2] = r.z >= thresh ? keep : 0.f; kf[4 * e4 + 3] = r.w >= thresh ? keep : 0.f;
+  for (int e8 = 0; e8 < 4; ++e8) {   // one Philox call = eight 16-bit decisions (see philox_half)
+    const uint4 r = philox4(p.seed, p.offset, (idx0 >> 3) + e8);
+    const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      kf[8 * e8 + 2 * k] = (w[k] & 0xFFFFu) >= thresh ? keep : 0.f;
+      kf[8 * e8 + 2 * k + 1] = (w[k] >> 16) >= thresh ? keep : 0.f;
+    }
   }
 }
 
