@@ -205,30 +205,48 @@ def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
 
 # ------------------------------------------------------------------------------------------ Linear
 class LinearFn(Function):
+    """y = [relu](x W^T + b).  The bf16 tensor-core GEMM stores 16-byte pieces of output rows, so it wants
+    out_features % 8 == 0; a layer that is not (a 10- or 100-class head) runs with its weight, bias and output
+    gradient zero-padded to the next multiple of 8 -- a few KB of copies on a layer that small -- and the
+    padding columns are dropped again."""
+
     @staticmethod
     def forward(ctx, x, weight, bias, relu):
         x2 = x.reshape(-1, x.shape[-1])
         if not x2.is_contiguous():
             x2 = x2.contiguous()
+        N = weight.shape[0]
+        npad = (-N) % 8 if weight.dtype == torch.bfloat16 else 0
+        w = weight.detach()
+        b = bias.detach() if bias is not None else None
+        if npad:
+            w = torch.cat([w, w.new_zeros((npad, w.shape[1]))], dim=0)
+            b = torch.cat([b, b.new_zeros(npad)]) if b is not None else None
         if weight.dtype == torch.float32:
-            y = RF.gemm_f32(x2, weight.detach(), bias=bias.detach() if bias is not None else None, relu=relu)
+            y = RF.gemm_f32(x2, w, bias=b, relu=relu)
         else:
-            y = RF.gemm(x2, weight.detach(), bias=_bias_f32(bias), relu=relu)
-        ctx.relu = relu
+            y = RF.gemm(x2, w, bias=_bias_f32(b), relu=relu)
+        ctx.relu, ctx.npad = relu, npad
         ctx.xshape = x.shape
-        ctx.save_for_backward(x2, weight, bias, y if relu else None)
-        return y.reshape(*x.shape[:-1], weight.shape[0])
+        ctx.save_for_backward(x2, weight, bias, y if relu else None, w if npad else None)
+        if npad:
+            y = y[:, :N].contiguous()
+        return y.reshape(*x.shape[:-1], N)
 
     @staticmethod
     def backward(ctx, dy):
-        x2, weight, bias, y = ctx.saved_tensors
-        dy2 = dy.reshape(-1, weight.shape[0])
+        x2, weight, bias, y, wpad = ctx.saved_tensors
+        N, npad = weight.shape[0], ctx.npad
+        dy2 = dy.reshape(-1, N)
+        if npad:
+            dy2 = torch.cat([dy2, dy2.new_zeros((dy2.shape[0], npad))], dim=1)
         if not dy2.is_contiguous():
             dy2 = dy2.contiguous()
         f32 = weight.dtype == torch.float32
+        wmat = wpad if npad else weight.detach()
         dw = db = dx = None
         want_db = bias is not None and ctx.needs_input_grad[2]
-        if ctx.relu and want_db and bias.is_leaf:
+        if ctx.relu and want_db and bias.is_leaf and not npad:
             box = []
             _write_param_grad(bias, lambda out, acc: box.append(RF.relu_bwd_colsum(dy2, y, out=out, accumulate=acc)))
             dy2 = box[0]
@@ -237,7 +255,10 @@ class LinearFn(Function):
             dy2 = RF.relu_bwd(dy2, y)
         if ctx.needs_input_grad[1]:
             def wg(out, acc):
-                if f32:
+                if npad:   # padded rows of the gradient are dropped
+                    g = RF.gemm(dy2, x2, a_mn=True, b_mn=True)[:N]
+                    (out.add_ if acc else out.copy_)(g)
+                elif f32:
                     RF.gemm_f32(dy2, x2, a_mn=True, b_mn=True, out=out, accumulate=acc)
                 elif not acc:
                     RF.gemm(dy2, x2, a_mn=True, b_mn=True, out=out)
@@ -246,12 +267,18 @@ class LinearFn(Function):
                     RF.add(out, g, out=out)
             dw = _write_param_grad(weight, wg)
         if want_db:
-            db = _write_param_grad(bias, lambda out, acc: RF.colsum(dy2, out=out, accumulate=acc))
+            def bg(out, acc):
+                if npad:
+                    g = RF.colsum(dy2)[:N]
+                    (out.add_ if acc else out.copy_)(g)
+                else:
+                    RF.colsum(dy2, out=out, accumulate=acc)
+            db = _write_param_grad(bias, bg)
         if ctx.needs_input_grad[0]:
             if f32:
-                dx = RF.gemm_f32(dy2, weight.detach(), b_mn=True)
+                dx = RF.gemm_f32(dy2, wmat, b_mn=True)
             else:
-                dx = RF.gemm(dy2, weight.detach(), b_mn=True)
+                dx = RF.gemm(dy2, wmat, b_mn=True)
             dx = dx.reshape(ctx.xshape)
         return dx, dw, db, None
 

@@ -416,3 +416,27 @@ def test_colsum_and_fused_relu_bwd_colsum(M, C, dt):
     assert torch.equal(dx.float().cpu(), dx_ref)                      # a select: exact
     ref2 = dx_ref.sum(0) + prev.float()
     assert ((out.float().cpu() - ref2).abs().max() / ref2.abs().max()).item() < tol
+
+
+@pytest.mark.parametrize("n_out,relu", [(10, False), (100, True), (13, False)])
+def test_bf16_linear_with_out_features_not_a_multiple_of_8(n_out, relu):
+    """A 10- / 100-class head: the tensor-core GEMM stores 16-byte row pieces, so the layer runs zero-padded to the
+    next multiple of 8; outputs and all three gradients must match torch on the unpadded shapes."""
+    from replicann_b200.nn.layers import Linear
+    torch.manual_seed(0)
+    lin = Linear(64, n_out, relu=relu).cuda().to(torch.bfloat16)
+    x = rnd((24, 64), 3, torch.bfloat16)
+    dy = rnd((24, n_out), 4, torch.bfloat16)
+    xr = x.float().requires_grad_(True)
+    wr = lin.weight.detach().float().cpu().requires_grad_(True)
+    br = lin.bias.detach().float().cpu().requires_grad_(True)
+    yr = F.linear(xr, wr, br)
+    yr = F.relu(yr) if relu else yr
+    yr.backward(dy.float())
+    xg = x.cuda().requires_grad_(True)
+    y = lin(xg)
+    assert tuple(y.shape) == (24, n_out)
+    y.backward(dy.cuda())
+    assert rel_err(y, yr) < 1e-2
+    assert rel_err(xg.grad, xr.grad) < 1e-2
+    assert rel_err(lin.weight.grad, wr.grad) < 1e-2 and rel_err(lin.bias.grad, br.grad) < 1e-2

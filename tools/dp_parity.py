@@ -204,7 +204,7 @@ def main() -> int:
     dev = torch.device("cuda", local)
     dist.init_process_group("nccl", device_id=dev)
     say(f"# dp_parity: {world} ranks x {PER_RANK} images, {torch.cuda.get_device_name(dev)}, NCCL {torch.cuda.nccl.version()}")
-    ok = run_case("alexnet", lambda: AlexNet(n_classes=100, p_dropout=0.0), lambda: R.RefAlexNet(100), (3, 224, 224), 100,
+    ok = run_case("alexnet", lambda: AlexNet(n_classes=96, p_dropout=0.0), lambda: R.RefAlexNet(96), (3, 224, 224), 96,
                   True, world, rank, dev)
     ok &= run_case("resnet-bottleneck-1111", lambda: ResNet((1, 1, 1, 1), bottleneck=True, n_classes=16),
                    lambda: R.RefResNet((1, 1, 1, 1), True, 16), (3, 64, 64), 16, False, world, rank, dev)
