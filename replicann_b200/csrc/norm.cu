@@ -20,11 +20,13 @@ namespace {
 // Thread layout for an [M, C] bf16 matrix: each thread owns one 8-channel vector column (cg) and
 // walks rows r0, r0 + rows_per_pass, ...   blockDim.x = 256; cgs = C/8 column groups.
 template <bool BWD>
-__global__ void __launch_bounds__(256)
-bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
-                 const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
-                 float* __restrict__ partials /* [gridDim.y][2][C] */, const float* __restrict__ fscale = nullptr,
-                 const float* __restrict__ fshift = nullptr, const unsigned char* __restrict__ bitmask = nullptr) {
+__device__ __forceinline__ void bn_reduce_body(const bf16* __restrict__ x, const bf16* __restrict__ dy,
+                                               const bf16* __restrict__ yout, const float* __restrict__ mean,
+                                               const float* __restrict__ invstd, long long M, int C,
+                                               float* __restrict__ partials /* [nby][2][C] */,
+                                               const float* __restrict__ fscale, const float* __restrict__ fshift,
+                                               const unsigned char* __restrict__ bitmask, const int bx, const int by,
+                                               const int nby) {
   // grid.x tiles the column groups (when C/8 > 256), grid.y tiles rows.  Each thread owns one 8-channel
   // vector column and walks its rows four at a time so that 4 (x streams) independent 16-byte loads are
   // in flight per thread.  In the backward flavour the ReLU mask comes from the saved output `yout`, or is
@@ -33,7 +35,7 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
   const int cgs = C >> 3;
   const int tpr = cgs < 256 ? cgs : 256;          // threads per row
   const int rpp = 256 / tpr;                      // rows per pass
-  const int cg = blockIdx.x * tpr + (threadIdx.x % tpr);
+  const int cg = bx * tpr + (threadIdx.x % tpr);
   const int rlocal = threadIdx.x / tpr;
   float s0[8], s1[8];
 #pragma unroll
@@ -75,8 +77,8 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
     }
   };
   if (active) {
-    const long long stride = (long long)gridDim.y * rpp;
-    long long r = (long long)blockIdx.y * rpp + rlocal;
+    const long long stride = (long long)nby * rpp;
+    long long r = (long long)by * rpp + rlocal;
     const uint4 z = make_uint4(0, 0, 0, 0);
     for (; r + (U - 1) * stride < M; r += U * stride) {
       uint4 ux[U], ug[U], uo[U];
@@ -109,10 +111,20 @@ bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const 
 #pragma unroll
       for (int e = 0; e < 8; ++e) { s0[e] += sm[t * 16 + e]; s1[e] += sm[t * 16 + 8 + e]; }
     }
-    float* p = partials + (long long)blockIdx.y * 2 * C;
+    float* p = partials + (long long)by * 2 * C;
 #pragma unroll
     for (int e = 0; e < 8; ++e) { p[cg * 8 + e] = s0[e]; p[C + cg * 8 + e] = s1[e]; }
   }
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+bn_reduce_kernel(const bf16* __restrict__ x, const bf16* __restrict__ dy, const bf16* __restrict__ yout,
+                 const float* __restrict__ mean, const float* __restrict__ invstd, long long M, int C,
+                 float* __restrict__ partials /* [gridDim.y][2][C] */, const float* __restrict__ fscale = nullptr,
+                 const float* __restrict__ fshift = nullptr, const unsigned char* __restrict__ bitmask = nullptr) {
+  bn_reduce_body<BWD>(x, dy, yout, mean, invstd, M, C, partials, fscale, fshift, bitmask, blockIdx.x, blockIdx.y,
+                      gridDim.y);
 }
 
 // Sum the per-block partials.  A 1024-thread block owns 32 channels: warp w walks partial rows w, w+32, ... with
@@ -291,13 +303,15 @@ bn_apply_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, con
   }
 }
 
-__global__ void __launch_bounds__(256)
-bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
-                    const float* __restrict__ coef /* [3][C]: A, B, D */, bf16* __restrict__ dx,
-                    bf16* __restrict__ dres, long long nvec, int cgs, const float* __restrict__ fscale,
-                    const float* __restrict__ fshift, const unsigned char* __restrict__ bitmask) {
+template <int U>
+__device__ __forceinline__ void bn_bwd_apply_body(const bf16* __restrict__ dy, const bf16* __restrict__ x,
+                                                  const bf16* __restrict__ yout,
+                                                  const float* __restrict__ coef /* [3][C]: A, B, D */,
+                                                  bf16* __restrict__ dx, bf16* __restrict__ dres, long long nvec, int cgs,
+                                                  const float* __restrict__ fscale, const float* __restrict__ fshift,
+                                                  const unsigned char* __restrict__ bitmask, const int bx, const int nbx) {
   const int C = cgs * 8;
-  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long stride = (long long)nbx * blockDim.x;
   const uint4 z = make_uint4(0, 0, 0, 0);
   auto finish = [&](long long i, int cg, const uint4& ug, const uint4& ux, const uint4& uo, unsigned mbits) {
     const int c0 = cg * 8;
@@ -333,8 +347,7 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
     for (int e = 0; e < 8; ++e) r[e] = fmaf(a[e], g[e], fmaf(b[e], v[e], d[e]));
     st_stream(dx + i * 8, pack8(r));
   };
-  constexpr int U = APPLY_UNROLL;
-  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long i0 = (long long)bx * blockDim.x + threadIdx.x;
   int cg = (int)(i0 % cgs);
   const int dcg = (int)(stride % cgs);
   for (long long i = i0; i < nvec; i += U * stride) {
@@ -358,6 +371,163 @@ bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, con
   }
 }
 
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
+                    const float* __restrict__ coef, bf16* __restrict__ dx, bf16* __restrict__ dres, long long nvec,
+                    int cgs, const float* __restrict__ fscale, const float* __restrict__ fshift,
+                    const unsigned char* __restrict__ bitmask) {
+  bn_bwd_apply_body<APPLY_UNROLL>(dy, x, yout, coef, dx, dres, nvec, cgs, fscale, fshift, bitmask, blockIdx.x,
+                                  gridDim.x);
+}
+
+// ---- apply kernels with the per-channel constants in registers ------------------------------------------------------
+// ncu on the kernels above (round 1 / round 2) showed L1, not DRAM, as their busiest unit (l1tex 62 %, DRAM 24-60 %):
+// every 16-byte vector of payload came with 4 (forward) or 10 (backward) 16-byte loads of per-channel constants, and
+// the asymptotic rate stayed at 4.0-4.8 TB/s.  When the grid stride is a multiple of the number of channel groups
+// (it is for every power-of-two channel count) a thread sees ONE channel group for its whole life, so the constants
+// are loaded once into registers and the loop touches only the tensors.  One wave of blocks (grid = SMs x resident
+// blocks), four vectors per stream in flight per thread.
+constexpr int HOIST_U = 4;
+
+__global__ void __launch_bounds__(256, 2)
+bn_apply_hoisted_kernel(const bf16* __restrict__ x, const float* __restrict__ scale, const float* __restrict__ shift,
+                        const bf16* __restrict__ residual, int relu, bf16* __restrict__ y, long long nvec, int cgs,
+                        unsigned char* __restrict__ relu_mask) {
+  constexpr int U = HOIST_U;
+  const long long stride = (long long)gridDim.x * blockDim.x;      // multiple of cgs (checked by the launcher)
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int cg = (int)(i0 % cgs);
+  float sc[8], sh[8];
+  *reinterpret_cast<float4*>(sc) = __ldg(reinterpret_cast<const float4*>(scale + cg * 8));
+  *reinterpret_cast<float4*>(sc + 4) = __ldg(reinterpret_cast<const float4*>(scale + cg * 8 + 4));
+  *reinterpret_cast<float4*>(sh) = __ldg(reinterpret_cast<const float4*>(shift + cg * 8));
+  *reinterpret_cast<float4*>(sh + 4) = __ldg(reinterpret_cast<const float4*>(shift + cg * 8 + 4));
+  const uint4 z = make_uint4(0, 0, 0, 0);
+  for (long long i = i0; i < nvec; i += U * stride) {
+    uint4 xs[U], rs[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      xs[u] = j < nvec ? ld_stream(x + j * 8) : z;
+      rs[u] = (j < nvec && residual) ? ld_stream(residual + j * 8) : z;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j >= nvec) break;
+      float v[8];
+      unpack8(xs[u], v);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) v[e] = fmaf(v[e], sc[e], sh[e]);
+      if (residual) {
+        float r[8];
+        unpack8(rs[u], r);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] += r[e];
+      }
+      if (relu) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
+      }
+      const uint4 packed = pack8(v);
+      st_stream(y + j * 8, packed);
+      if (relu_mask) {
+        float o[8];
+        unpack8(packed, o);
+        unsigned m = 0;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) m |= (o[e] > 0.f ? 1u : 0u) << e;
+        relu_mask[j] = (unsigned char)m;
+      }
+    }
+  }
+}
+
+// MASK: 0 none, 1 recompute from x with the forward's scale / shift, 2 bit mask, 3 saved output
+template <int MASK>
+__global__ void __launch_bounds__(256, 2)
+bn_bwd_apply_hoisted_kernel(const bf16* __restrict__ dy, const bf16* __restrict__ x, const bf16* __restrict__ yout,
+                            const float* __restrict__ coef /* [3][C]: A, B, D */, bf16* __restrict__ dx,
+                            bf16* __restrict__ dres, long long nvec, int cgs, const float* __restrict__ fscale,
+                            const float* __restrict__ fshift, const unsigned char* __restrict__ bitmask) {
+  constexpr int U = HOIST_U;
+  const int C = cgs * 8;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = (int)(i0 % cgs) * 8;
+  float a[8], b[8], d[8], fs[8], fb[8];
+  *reinterpret_cast<float4*>(a) = __ldg(reinterpret_cast<const float4*>(coef + c0));
+  *reinterpret_cast<float4*>(a + 4) = __ldg(reinterpret_cast<const float4*>(coef + c0 + 4));
+  *reinterpret_cast<float4*>(b) = __ldg(reinterpret_cast<const float4*>(coef + C + c0));
+  *reinterpret_cast<float4*>(b + 4) = __ldg(reinterpret_cast<const float4*>(coef + C + c0 + 4));
+  *reinterpret_cast<float4*>(d) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0));
+  *reinterpret_cast<float4*>(d + 4) = __ldg(reinterpret_cast<const float4*>(coef + 2 * C + c0 + 4));
+  if (MASK == 1) {
+    *reinterpret_cast<float4*>(fs) = __ldg(reinterpret_cast<const float4*>(fscale + c0));
+    *reinterpret_cast<float4*>(fs + 4) = __ldg(reinterpret_cast<const float4*>(fscale + c0 + 4));
+    *reinterpret_cast<float4*>(fb) = __ldg(reinterpret_cast<const float4*>(fshift + c0));
+    *reinterpret_cast<float4*>(fb + 4) = __ldg(reinterpret_cast<const float4*>(fshift + c0 + 4));
+  }
+  const uint4 z = make_uint4(0, 0, 0, 0);
+  for (long long i = i0; i < nvec; i += U * stride) {
+    uint4 gs[U], xs[U], os[MASK == 3 ? U : 1];
+    unsigned ms[MASK == 2 ? U : 1];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      const bool ok = j < nvec;
+      gs[u] = ok ? ld_stream(dy + j * 8) : z;
+      xs[u] = ok ? ld_stream(x + j * 8) : z;
+      if (MASK == 3) os[u] = ok ? ld_stream(yout + j * 8) : z;
+      if (MASK == 2) ms[u] = ok ? bitmask[j] : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long j = i + u * stride;
+      if (j >= nvec) break;
+      float g[8], v[8], r[8];
+      unpack8(gs[u], g);
+      unpack8(xs[u], v);
+      if (MASK == 3) {
+        float o[8];
+        unpack8(os[u], o);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = o[e] > 0.f ? g[e] : 0.f;
+      } else if (MASK == 1) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = fmaf(v[e], fs[e], fb[e]) > 0.f ? g[e] : 0.f;
+      } else if (MASK == 2) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) g[e] = ((ms[u] >> e) & 1u) ? g[e] : 0.f;
+      }
+      if (dres) st_stream(dres + j * 8, pack8(g));
+#pragma unroll
+      for (int e = 0; e < 8; ++e) r[e] = fmaf(a[e], g[e], fmaf(b[e], v[e], d[e]));
+      st_stream(dx + j * 8, pack8(r));
+    }
+  }
+}
+
+// grid of the hoisted kernels: one wave, and a stride that is a multiple of the channel groups (0 = not applicable)
+template <typename K>
+int hoisted_grid(K kernel, long long nvec, int cgs) {
+  if (256 % cgs != 0 && cgs % 256 != 0) return 0;
+  static int per_sm_cache = 0;
+  if (per_sm_cache == 0) {
+    int v = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&v, kernel, 256, 0) != cudaSuccess || v < 1) v = 2;
+    per_sm_cache = v;
+  }
+  long long blocks = (nvec + 256ll * HOIST_U - 1) / (256ll * HOIST_U);
+  const long long cap = (long long)rnn_num_sms() * per_sm_cache;
+  if (blocks > cap) blocks = cap;
+  if (cgs > 256) {   // the stride (blocks * 256) must be a multiple of cgs
+    const int m = cgs / 256;
+    blocks = blocks / m * m;
+  }
+  return blocks < 1 ? 0 : (int)blocks;
+}
+
 // CTAs per SM of the streaming apply kernels (grid-stride loops).  Experiments: RNN_BN_APPLY_CTAS.
 int apply_ctas_per_sm() {
   static const int v = [] {
@@ -368,14 +538,30 @@ int apply_ctas_per_sm() {
   return v;
 }
 
+// RNN_BN_HOIST=0: the apply kernels that reload their constants per vector (A/B timing; any channel count)
+bool apply_hoist_enabled() {
+  static const bool v = [] {
+    const char* e = getenv("RNN_BN_HOIST");
+    return e == nullptr || atoi(e) != 0;
+  }();
+  return v;
+}
+
 int bn_row_blocks(long long M, int C) {
   const int cgs = C >> 3;
   const int tpr = cgs < 256 ? cgs : 256;
   const int rpp = 256 / tpr;
   const int gx = (cgs + tpr - 1) / tpr;
-  // every thread should see >= 4 rows (one unrolled batch); at most ~4 resident blocks per SM in total
+  // every thread should see >= 4 rows (one unrolled batch)
   long long gy = (M + (long long)rpp * 4 - 1) / ((long long)rpp * 4);
-  long long cap = (long long)rnn_num_sms() * 4 / gx;
+  static const int per_sm = [] {
+    const char* e = getenv("RNN_BN_REDUCE_CTAS");
+    const int n = e ? atoi(e) : 0;
+    return n > 0 ? n : 2;
+  }();
+  // 124 registers per thread: two blocks are resident per SM, so 2 per SM is ONE wave.  A second wave cost 4 us on
+  // every tensor size (bench_bn_bwd.py, round 2): the kernel is a single latency-bound sweep per thread.
+  long long cap = (long long)rnn_num_sms() * per_sm / gx;
   if (cap < 1) cap = 1;
   if (gy > cap) gy = cap;
   if (gy < 1) gy = 1;
@@ -737,6 +923,12 @@ int rnn_bn_apply_bf16(const void* x, const float* scale, const float* shift, con
                       unsigned char* relu_mask, long long M, int C, cudaStream_t stream) {
   RNN_REQUIRE(M > 0 && C > 0 && C % 8 == 0, RNN_ERR_SHAPE);
   const long long nvec = M * (C / 8);
+  if (const int hg = apply_hoist_enabled() ? hoisted_grid(bn_apply_hoisted_kernel, nvec, C / 8) : 0) {
+    bn_apply_hoisted_kernel<<<hg, 256, 0, stream>>>((const bf16*)x, scale, shift, (const bf16*)residual, relu, (bf16*)y,
+                                                    nvec, C / 8, relu ? relu_mask : nullptr);
+    RNN_CHECK_LAUNCH();
+    return RNN_OK;
+  }
   long long blocks = (nvec + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * apply_ctas_per_sm();
   if (blocks > cap) blocks = cap;
@@ -761,14 +953,38 @@ int rnn_bn_bwd_bf16(const void* dy, const void* x, const void* y_out /* nullable
   const int gy = bn_row_blocks(M, C);
   RNN_REQUIRE(ws != nullptr && ws_bytes >= (size_t)gy * 2 * C * sizeof(float), RNN_ERR_WORKSPACE);
   const int cgs = C >> 3, tpr = cgs < 256 ? cgs : 256, gx = (cgs + tpr - 1) / tpr;
-  bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
-                                                          invstd, M, C, (float*)ws, fwd_scale, fwd_shift, relu_mask);
-  RNN_CHECK_LAUNCH();
-  bn_bwd_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
-                                                                dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
-                                                                1.f / (float)M, coef);
-  RNN_CHECK_LAUNCH();
+  {
+    RnnTimedScope timed("bn_bwd_reduce", stream);
+    bn_reduce_kernel<true><<<dim3(gx, gy), 256, 0, stream>>>((const bf16*)x, (const bf16*)dy, (const bf16*)y_out, mean,
+                                                            invstd, M, C, (float*)ws, fwd_scale, fwd_shift, relu_mask);
+    RNN_CHECK_LAUNCH();
+  }
+  {
+    RnnTimedScope timed("bn_bwd_finalize", stream);
+    bn_bwd_finalize_kernel<<<ceil_div_i(C, FIN_CH), FIN_THREADS, 0, stream>>>((const float*)ws, gy, C, sum_dy, sum_dy_xhat, dgamma,
+                                                                  dbeta, grads_f32, accumulate_grads, mean, invstd, gamma,
+                                                                  1.f / (float)M, coef);
+    RNN_CHECK_LAUNCH();
+  }
+  RnnTimedScope timed_apply("bn_bwd_apply", stream);
   const long long nvec = M * (C / 8);
+  if (apply_hoist_enabled()) {
+    const bf16 *a_dy = (const bf16*)dy, *a_x = (const bf16*)x, *a_y = (const bf16*)y_out;
+    int hg = 0;
+#define RNN_BWD_HOISTED(MASK)                                                                                        \
+  if ((hg = hoisted_grid(bn_bwd_apply_hoisted_kernel<MASK>, nvec, C / 8)) > 0)                                        \
+    bn_bwd_apply_hoisted_kernel<MASK><<<hg, 256, 0, stream>>>(a_dy, a_x, a_y, coef, (bf16*)dx, (bf16*)dres, nvec, C / 8, \
+                                                              fwd_scale, fwd_shift, relu_mask)
+    if (y_out != nullptr) { RNN_BWD_HOISTED(3); }
+    else if (fwd_scale != nullptr) { RNN_BWD_HOISTED(1); }
+    else if (relu_mask != nullptr) { RNN_BWD_HOISTED(2); }
+    else { RNN_BWD_HOISTED(0); }
+#undef RNN_BWD_HOISTED
+    if (hg > 0) {
+      RNN_CHECK_LAUNCH();
+      return RNN_OK;
+    }
+  }
   long long blocks = (nvec + 255) / 256;
   const long long cap = (long long)rnn_num_sms() * apply_ctas_per_sm();
   if (blocks > cap) blocks = cap;

@@ -440,3 +440,4 @@ def test_bf16_linear_with_out_features_not_a_multiple_of_8(n_out, relu):
     assert rel_err(y, yr) < 1e-2
     assert rel_err(xg.grad, xr.grad) < 1e-2
     assert rel_err(lin.weight.grad, wr.grad) < 1e-2 and rel_err(lin.bias.grad, br.grad) < 1e-2
+
