@@ -62,6 +62,10 @@ struct TcParams {
   int stat_rows;        // = gridDim.x / n_nblk
   int force_grid;       // launch exactly this many CTAs (STATS needs gridDim.x % n_nblk == 0)
   int cg;               // host only: 2 = launch as CTA pairs (cta_group::2), else single CTAs
+  // CONV, single CTAs: the whole B operand (filter) of this CTA's n-block stays in shared memory for the life of the
+  // CTA and the ring carries A tiles only (ring_stages stages of A_BYTES).  Needs a constant n-block per CTA
+  // (gridDim.x % n_nblk == 0) and splits == 1.
+  int b_resident, ring_stages;
   // BGEMM: `splits` independent problems z = b * bg_heads + h, each with the full K range.  Operand X lives in a
   // 3-D tensor; its slab index is b (x_zdiv = 1: heads of a batch share rows, head h starts x_hoff * h elements
   // into the inner dimension) or z (x_zdiv = 0).
@@ -112,10 +116,17 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 
   uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
-  uint64_t* empty_bar = full_bar + C::STAGES;
-  uint64_t* tfull_bar = empty_bar + C::STAGES;
+  constexpr int MAXS = 8;   // barrier slots: the resident-filter form may run more ring stages than C::STAGES
+  uint64_t* empty_bar = full_bar + MAXS;
+  uint64_t* tfull_bar = empty_bar + MAXS;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* bres_bar = tempty_bar + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
+  // resident-B form (see TcParams::b_resident): B sits at the end of the ring area, the ring strides by A_BYTES
+  const bool bres = KIND == KIND_CONV && CG == 1 && p.b_resident != 0;
+  const int nstages = bres ? p.ring_stages : C::STAGES;
+  const uint32_t stage_bytes = bres ? (uint32_t)A_BYTES : (uint32_t)C::STAGE_BYTES;
+  const uint32_t bres_off = (uint32_t)(C::STAGES * C::STAGE_BYTES - p.k_iters * C::B_BYTES);
 
   // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role loops' state
   // (stage counters, barrier addresses, TMA coordinates, MMA descriptors) in uniform registers
@@ -127,7 +138,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
     tc::prefetch_tmap(&tmA);
     tc::prefetch_tmap(&tmB);
     if (p.tma_store) tc::prefetch_tmap(&tmD);
-    for (int s = 0; s < C::STAGES; ++s) {
+    for (int s = 0; s < MAXS; ++s) {
       tc::mbar_init(&full_bar[s], 1);
       tc::mbar_init(&empty_bar[s], 1);
     }
@@ -135,6 +146,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       tc::mbar_init(&tfull_bar[a], 1);
       tc::mbar_init(&tempty_bar[a], 4 * CG);  // one arrive per epilogue warp (of every CTA of the pair)
     }
+    tc::mbar_init(bres_bar, 1);
     tc::fence_barrier_init();
   }
   if (warp == 1) {
@@ -160,6 +172,24 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       uint32_t phase = 0;
       constexpr int NB_LOCAL = BN / 64 / CG;   // 64-wide B blocks staged by this CTA (MN-major B)
       const int jb0 = cta_rank * NB_LOCAL;     // first 64-wide B block this CTA stages
+      if (KIND == KIND_CONV && bres) {
+        // every tile of this CTA has n-block (cluster_id % n_nblk): fetch its whole filter slice once
+        const int n0r = (cluster_id % p.n_nblk) * BN;
+        const uint32_t rb = tc::smem_u32(bres_bar);
+        tc::mbar_expect_tx(rb, (uint32_t)(p.k_iters * C::B_BYTES));
+        int tap = 0, cc = 0;
+        for (int it = 0; it < p.k_iters; ++it) {
+          const TapDesc td = p.taps[tap];
+          const uint32_t dB = smem_a0 + bres_off + (uint32_t)(it * C::B_BYTES);
+          if (!B_MN) {
+            tc::tma_ld2<1>(dB, &tmB, rb, td.bcol + cc * BK, n0r);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) tc::tma_ld2<1>(dB + j * 8192, &tmB, rb, td.bcol + n0r + j * 64, cc * BK);
+          }
+          if (++cc == p.cchunks) { cc = 0; ++tap; }
+        }
+      }
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int t = tile;
         const int nblk = t % p.n_nblk; t /= p.n_nblk;
@@ -207,7 +237,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         }
         // loads of a pair credit the even CTA's barrier; it alone announces the bytes of BOTH CTAs
         const uint32_t tx_bytes = KIND == KIND_WGRAD ? (uint32_t)(CG * A_BYTES + nsb_valid * 8192)
-                                                     : (uint32_t)(CG * C::STAGE_BYTES);
+                                                     : (bres ? (uint32_t)A_BYTES : (uint32_t)(CG * C::STAGE_BYTES));
         // CONV: (tap, channel chunk) of the K step, advanced without divisions
         int tap = 0, cc = 0;
         TapDesc td = p.taps[0];
@@ -228,7 +258,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         }
         for (int it = k_lo; it < k_hi; ++it) {
           const uint32_t fb = full0 + stage * 8;
-          const uint32_t sA = smem_a0 + stage * C::STAGE_BYTES;
+          const uint32_t sA = smem_a0 + stage * stage_bytes;
           const uint32_t sB = sA + A_BYTES;
           tc::mbar_wait(empty0 + stage * 8, phase ^ 1u);
           if (cta_rank == 0) tc::mbar_expect_tx(fb, tx_bytes);
@@ -262,7 +292,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             }
           } else if (KIND == KIND_CONV) {
             tc::tma_ldi<CG>(sA, &tmA, fb, cc * BK, w0, h0, img0, (uint16_t)td.ow, (uint16_t)td.oh);
-            if (!B_MN) {
+            if (bres) {
+              // B is resident (loaded once below, before the first tile)
+            } else if (!B_MN) {
               tc::tma_ld2<CG>(sB, &tmB, fb, td.bcol + cc * BK, n0 + cta_rank * (BN / CG));
             } else {
 #pragma unroll
@@ -288,7 +320,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
             wg_j += BK;
             while (wg_j >= p.Wo) { wg_j -= p.Wo; if (++wg_i == wg_ho) { wg_i = 0; ++wg_img; } }
           }
-          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+          if (++stage == nstages) { stage = 0; phase ^= 1u; }
         }
       }
     }
@@ -307,6 +339,12 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
+      const uint64_t bdesc_res = B_MN ? tc::make_smem_desc(smem_a0 + bres_off, 8192, 1024)
+                                      : tc::make_smem_desc(smem_a0 + bres_off, 16, 1024);
+      if (bres) {
+        tc::mbar_wait(tc::smem_u32(bres_bar), 0);
+        tc::tc_fence_after();
+      }
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         const int split = tile / (p.n_nblk * n_pm);
         const int k_lo = KIND == KIND_BGEMM ? 0 : (int)(((long long)p.k_iters * split) / p.splits);
@@ -318,8 +356,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         for (int it = k_lo; it < k_hi; ++it) {
           tc::mbar_wait(full0 + stage * 8, phase);
           tc::tc_fence_after();
-          const uint64_t ad = adesc0 + (uint64_t)(stage * (C::STAGE_BYTES >> 4));
-          const uint64_t bd = bdesc0 + (uint64_t)(stage * (C::STAGE_BYTES >> 4));
+          const uint64_t ad = adesc0 + (uint64_t)(stage * (stage_bytes >> 4));
+          const uint64_t bd = bres ? bdesc_res + (uint64_t)(it * (C::B_BYTES >> 4))
+                                   : bdesc0 + (uint64_t)(stage * (C::STAGE_BYTES >> 4));
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
             if (CG == 2) tc::umma_bf16_pair(d_tmem, ad + k * A_KADV, bd + k * B_KADV, idesc, accumulate);
@@ -328,7 +367,7 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           }
           // frees the smem slot (in both CTAs of a pair) once these MMAs retire
           tc::umma_commit_u32<CG>(empty0 + stage * 8);
-          if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
+          if (++stage == nstages) { stage = 0; phase ^= 1u; }
         }
         // accumulator complete -> epilogue warps (of both CTAs)
         tc::umma_commit_u32<CG>(tfull0 + acc * 8);
@@ -778,6 +817,16 @@ int pick_cg(int BN, int n_mblk, int k_iters) {
   return (mode == 2 || k_iters >= 8) ? 2 : 1;
 }
 
+// RNN_TC_BRES=0 switches the resident-filter form off, =2 forces it wherever the shape allows, however few tiles a
+// CTA walks (A/B timing; tests of both forms on small cases)
+int b_resident_mode() {
+  static const int v = [] {
+    const char* e = getenv("RNN_TC_BRES");
+    return e == nullptr ? 1 : atoi(e);
+  }();
+  return v;
+}
+
 // STATS launches: every CTA (pair) keeps one n-block for all of its tiles, so the number of CTAs (pairs) is a
 // multiple of n_nblk.  Partial-sum rows: one per CTA.
 void plan_stats_grid(TcParams* p) {
@@ -808,6 +857,23 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   const int tiles = ceil_div_i(p.n_mblk, CG) * p.n_nblk * p.splits;
   int grid = (tiles < units ? tiles : units) * CG;
   if (p.force_grid > 0) grid = p.force_grid;
+  // Resident filter (TcParams::b_resident): convolutions whose whole B slice fits beside an A-only ring of at least
+  // four stages, on single CTAs, when every CTA walks several tiles (otherwise there is nothing to re-use).  These
+  // are the narrow layers that run at the L2 -> SM throughput cap: a 128 x 64 tile of the C64 3x3 layers pulled
+  // 144 KB of A and 72 KB of filter through L2; the filter share disappears.
+  p.b_resident = 0;
+  if constexpr (KIND == KIND_CONV && CG == 1) {
+    using C = Cfg<BN, CG, KIND>;
+    const int need = p.k_iters * C::B_BYTES;
+    const int ring = (C::STAGES * C::STAGE_BYTES - need) / A_BYTES;
+    const int g2 = p.force_grid > 0 ? grid : (units / p.n_nblk) * p.n_nblk;
+    if (b_resident_mode() != 0 && p.splits == 1 && need > 0 && ring >= 4 && g2 > 0 && g2 % p.n_nblk == 0 &&
+        (tiles >= 3 * g2 || b_resident_mode() == 2)) {
+      p.b_resident = 1;
+      p.ring_stages = ring > 8 ? 8 : ring;
+      grid = g2;
+    }
+  }
   // weight-gradient kernels run on a side stream next to other kernels: one epilogue group keeps them small
   const int threads = (KIND == KIND_WGRAD && !STATS) ? NUM_THREADS_NARROW : NUM_THREADS;
   RnnTimedScope timed("tc_kernel", stream);

@@ -20,3 +20,16 @@ def test_tc_parity_under_forced_launch_form(mode):
                         "-x", "--timeout", "600", "-p", "no:cacheprovider"],
                        cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+
+
+@pytest.mark.gpu
+def test_conv_parity_with_the_filter_resident_form_forced():
+    """Convolutions whose filter slice fits in shared memory keep it there for the life of the CTA and stream only A
+    tiles (the library picks this when a CTA walks many tiles: the batch-256 shapes of tests/test_tc_real_shapes.py).
+    RNN_TC_BRES=2 forces the form on the small parity cases too, RNN_TC_BRES=0 switches it off."""
+    for mode in ("2", "0"):
+        env = dict(os.environ, RNN_TC_BRES=mode)
+        r = subprocess.run([sys.executable, "-m", "pytest", str(ROOT / "tests" / "test_tc_kernels.py"), "-m", "gpu", "-q",
+                            "-x", "-k", "conv", "--timeout", "600", "-p", "no:cacheprovider"],
+                           cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, f"RNN_TC_BRES={mode}\n" + r.stdout[-3000:] + r.stderr[-2000:]
