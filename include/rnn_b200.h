@@ -225,6 +225,12 @@ int rnn_layernorm_bwd(const void* dy, const void* xin, const void* gamma, const 
  * a 1-byte position inside the window (r*S+s), the compact form the backward pass reads; pass either to bwd. */
 int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
                       int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream);
+/* relu(BatchNorm-apply(x)) followed by the max pool, in one pass: pools relu(x * scale + shift) (rounded to the
+ * storage type first, so values and argmax ties equal rnn_bn_apply_bf16 + rnn_maxpool2d_fwd) without writing the
+ * normalised tensor -- the stem of the ResNets the north star names (torch: F.max_pool2d(F.relu(bn(x)))). */
+int rnn_bn_relu_maxpool2d_fwd(const void* x, const float* scale, const float* shift, void* y, int* indices,
+                              unsigned char* window_idx, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph,
+                              int pw, int is_f32, cudaStream_t stream);
 int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
                       int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream);
 /* torch.nn.AvgPool2d (count_include_pad=True, ceil_mode=False). */

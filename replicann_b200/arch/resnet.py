@@ -9,7 +9,7 @@ import torch
 import torch.nn as nn
 from torch import Tensor
 
-from ..nn._functions import BottleneckFn
+from ..nn._functions import BnReluMaxPoolFn, BottleneckFn
 from ..nn.layers import AdaptiveAvgPool2d, BatchNorm2d, Conv2d, Linear, MaxPool2d
 from ._stem import prepare_input
 
@@ -107,6 +107,7 @@ class ResNet(nn.Module):
         self._avgpool = AdaptiveAvgPool2d((1, 1))
         self._fc = Linear(ch, n_classes)
         self._n_features = ch
+        self._fused_stem = True
         for m in self.modules():
             if isinstance(m, Conv2d):
                 nn.init.kaiming_normal_(m.weight, mode="fan_out", nonlinearity="relu")
@@ -119,10 +120,20 @@ class ResNet(nn.Module):
     def n_features(self) -> int:
         return self._n_features
 
+    def _stem_tail(self, y: Tensor) -> Tensor:
+        """BatchNorm + ReLU + max-pool after the first convolution; one pooling kernel applies the normalisation on
+        the fly for bf16 CUDA tensors (same values and gradients as the two modules, see BnReluMaxPoolFn)."""
+        bn, mp = self._bn1, self._maxpool
+        if self._fused_stem and y.is_cuda and y.dtype == torch.bfloat16 and not mp._return_indices:
+            if self.training:
+                bn._batches_pending += 1
+            return BnReluMaxPoolFn.apply(y, bn.weight, bn.bias, bn.running_mean, bn.running_var, self.training,
+                                         bn.momentum, bn.eps, mp._k, mp._s, mp._p)
+        return mp(bn(y))
+
     def forward(self, x: Tensor, /) -> Tensor:
         x = prepare_input(x, self._conv1.weight.dtype)
-        x = self._bn1(self._conv1(x))
-        x = self._maxpool(x)
+        x = self._stem_tail(self._conv1(x))
         for stage in self._stages:
             x = stage(x)
         x = self._avgpool(x)

@@ -83,7 +83,8 @@ template <> struct WIdx<8> {
 template <typename T, bool VEC, int FX>
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__ idx,
-                   unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift) {
+                   unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift,
+                   const float* __restrict__ scale = nullptr, const float* __restrict__ shift = nullptr) {
   constexpr int VW = PV<T, VEC>::W;
   // FX != 0: the window geometry is a compile-time constant (1: 3x3 stride 2 pad 1, 2: 2x2 stride 2, 3: 3x3 stride 2
   // pad 0 -- the pools of ResNet, VGG and AlexNet), which turns the divisions below into shifts
@@ -103,11 +104,27 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
   const int he = min(h0 + gR, g.H), we = min(w0 + gS, g.W);
 #pragma unroll
   for (int e2 = 0; e2 < VW; ++e2) { best[e2] = -INFINITY; bl[e2] = (hs - h0) * gS + (ws - w0); }
+  // scale != nullptr: the input is a pre-BatchNorm activation and the pooled quantity is relu(x * scale + shift)
+  // rounded to the storage type first -- exactly what a separate BatchNorm-apply kernel would have stored, so values
+  // AND argmax ties are those of the unfused pair (the ResNet stem: saves writing and re-reading that tensor)
+  float sc[VW], sf[VW];
+  if (scale != nullptr) {
+#pragma unroll
+    for (int e2 = 0; e2 < VW; ++e2) { sc[e2] = scale[cg * VW + e2]; sf[e2] = shift[cg * VW + e2]; }
+  }
   const T* xn = x + (long long)n * g.H * g.W * g.C + cg * VW;
   for (int h = hs; h < he; ++h)
     for (int w = ws; w < we; ++w) {
       float v[VW];
       PV<T, VEC>::load(xn + ((long long)h * g.W + w) * g.C, v);
+      if (scale != nullptr) {
+        float t[VW];
+#pragma unroll
+        for (int e2 = 0; e2 < VW; ++e2) t[e2] = fmaxf(fmaf(v[e2], sc[e2], sf[e2]), 0.f);
+        __align__(16) T tmp[VW];
+        PV<T, VEC>::store(tmp, t);      // round to the storage type
+        PV<T, VEC>::load(tmp, v);
+      }
       const int local = (h - h0) * gS + (w - w0);
 #pragma unroll
       for (int e2 = 0; e2 < VW; ++e2)
@@ -418,8 +435,9 @@ int make_geom(PoolGeom* g, int N, int H, int W, int C, int R, int S, int sh, int
 
 extern "C" {
 
-int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
-                      int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+static int maxpool_fwd_impl(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
+                            int R, int S, int sh, int sw, int ph, int pw, int is_f32, const float* scale,
+                            const float* shift, cudaStream_t stream) {
   RNN_REQUIRE(R * S <= 255, RNN_ERR_SHAPE);
   PoolGeom g;
   const int vw = is_f32 ? 4 : 8;
@@ -432,20 +450,30 @@ int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* windo
   const dim3 grid(ceil_div_i((long long)g.Q * cgs, 256), g.P, N);
   const int fx = fixed_geometry(g);
   if (is_f32) {
-    if (vec) maxpool_fwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
-    else maxpool_fwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_);
+    if (vec) maxpool_fwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_, scale, shift);
+    else maxpool_fwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)x, (float*)y, indices, window_idx, g, sh_, scale, shift);
   } else if (!vec) {
-    maxpool_fwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
+    maxpool_fwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
   } else {
     switch (fx) {
-      case 1: maxpool_fwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
-      case 2: maxpool_fwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
-      case 3: maxpool_fwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_); break;
-      default: maxpool_fwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_);
+      case 1: maxpool_fwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift); break;
+      case 2: maxpool_fwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift); break;
+      case 3: maxpool_fwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift); break;
+      default: maxpool_fwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
     }
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
+}
+int rnn_maxpool2d_fwd(const void* x, void* y, int* indices, unsigned char* window_idx, int N, int H, int W, int C,
+                      int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+  return maxpool_fwd_impl(x, y, indices, window_idx, N, H, W, C, R, S, sh, sw, ph, pw, is_f32, nullptr, nullptr, stream);
+}
+int rnn_bn_relu_maxpool2d_fwd(const void* x, const float* scale, const float* shift, void* y, int* indices,
+                              unsigned char* window_idx, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph,
+                              int pw, int is_f32, cudaStream_t stream) {
+  RNN_REQUIRE(scale != nullptr && shift != nullptr, RNN_ERR_SHAPE);
+  return maxpool_fwd_impl(x, y, indices, window_idx, N, H, W, C, R, S, sh, sw, ph, pw, is_f32, scale, shift, stream);
 }
 int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
                       int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {

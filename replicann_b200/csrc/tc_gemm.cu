@@ -66,6 +66,7 @@ struct TcParams {
   // CTA and the ring carries A tiles only (ring_stages stages of A_BYTES).  Needs a constant n-block per CTA
   // (gridDim.x % n_nblk == 0) and splits == 1.
   int b_resident, ring_stages;
+  int no_b_resident;    // host only: never take the resident form (the packed-pixel first layer measured slower with it)
   // BGEMM: `splits` independent problems z = b * bg_heads + h, each with the full K range.  Operand X lives in a
   // 3-D tensor; its slab index is b (x_zdiv = 1: heads of a batch share rows, head h starts x_hoff * h elements
   // into the inner dimension) or z (x_zdiv = 0).
@@ -867,7 +868,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     const int need = p.k_iters * C::B_BYTES;
     const int ring = (C::STAGES * C::STAGE_BYTES - need) / A_BYTES;
     const int g2 = p.force_grid > 0 ? grid : (units / p.n_nblk) * p.n_nblk;
-    if (b_resident_mode() != 0 && p.splits == 1 && need > 0 && ring >= 4 && g2 > 0 && g2 % p.n_nblk == 0 &&
+    if (b_resident_mode() != 0 && !p.no_b_resident && p.splits == 1 && need > 0 && ring >= 4 && g2 > 0 && g2 % p.n_nblk == 0 &&
         (tiles >= 3 * g2 || b_resident_mode() == 2)) {
       p.b_resident = 1;
       p.ring_stages = ring > 8 ? 8 : ring;
@@ -1512,6 +1513,7 @@ int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, co
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = 0; p.lo_h = 0;
   p.ldd = d->K;
   p.D = y; p.scale = scale; p.shift = shift; p.relu = relu;
+  p.no_b_resident = 1;   // 338 -> 362 us in-step with the filter resident: the 7 K steps of a tile are epilogue-bound
   first_taps(d, g, &p);
   return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);
 }

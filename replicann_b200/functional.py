@@ -646,6 +646,19 @@ def maxpool2d_fwd(x, k, s, p, return_indices=True, return_window_idx=False):
     return y, idx, widx
 
 
+def bn_relu_maxpool2d_fwd(x, scale, shift, k, s, p):
+    """relu(x * scale + shift) pooled in one pass (x: pre-BatchNorm activation, NHWC); returns (y, window_idx)."""
+    lib = _lib.load(); _cuda(x); _contig(x, "x")
+    _req(scale, torch.float32, "scale"); _req(shift, torch.float32, "shift")
+    N, H, W, Cn, kh, kw, sh, sw, ph, pw, P, Q = _pool_args(x, k, s, p)
+    y = torch.empty((N, P, Q, Cn), dtype=x.dtype, device=x.device)
+    widx = torch.empty((N, P, Q, Cn), dtype=torch.uint8, device=x.device)
+    with _span('maxpool', float(x.numel() + y.numel()) * x.element_size() + y.numel(), f"bn+relu+fwd {tuple(x.shape)} k{kh} s{sh}"):
+        check(lib.rnn_bn_relu_maxpool2d_fwd(ptr(x), ptr(scale), ptr(shift), ptr(y), None, ptr(widx), N, H, W, Cn, kh, kw,
+                                            sh, sw, ph, pw, _is_f32(x), cur_stream()), "rnn_bn_relu_maxpool2d_fwd")
+    return y, widx
+
+
 def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None):
     lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
     N, H, W, Cn = x_shape

@@ -545,6 +545,48 @@ class MaxPool2dFn(Function):
         return nchw(RF.maxpool2d_bwd(nhwc(dy), None, shape, k, s, p, window_idx=widx)), None, None, None, None
 
 
+class BnReluMaxPoolFn(Function):
+    """max_pool(relu(BatchNorm(x))) -- the stem of the ResNets -- with the BatchNorm-apply + ReLU folded into the
+    pooling kernel: the normalised 112 x 112 activation (411 MB at batch 256) is neither written nor re-read.
+    Values, argmax ties and all gradients are those of BatchNorm2d(relu=True) followed by MaxPool2d: the pooled
+    values are rounded to bf16 before they are compared, and backward is the same two kernels (pool backward by
+    window index, BatchNorm backward with the ReLU mask recomputed from x)."""
+
+    @staticmethod
+    def forward(ctx, x, gamma, beta, running_mean, running_var, training, momentum, eps, k, s, p):
+        xh = nhwc(x)
+        Cn = xh.shape[-1]
+        x2 = xh.reshape(-1, Cn)
+        g, b = gamma.detach(), beta.detach()
+        if training:
+            mean, invstd, scale, shift = RF.bn_stats(x2, g, b, eps, momentum, running_mean, running_var)
+        else:
+            scale, shift = RF.bn_eval_prepare(g, b, running_mean, running_var, eps)
+            mean, invstd = running_mean, torch.rsqrt(running_var + eps)
+        y, widx = RF.bn_relu_maxpool2d_fwd(xh, scale, shift, k, s, p)
+        ctx.training, ctx.cfg = training, (tuple(xh.shape), k, s, p)
+        ctx.save_for_backward(x2, widx, mean, invstd, gamma, beta, scale, shift)
+        return nchw(y)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, widx, mean, invstd, gamma, beta, scale, shift = ctx.saved_tensors
+        if not ctx.training:
+            raise RuntimeError("BatchNorm2d backward in eval mode is not supported by replicann_b200")
+        shape, k, s, p = ctx.cfg
+        dz = RF.maxpool2d_bwd(nhwc(dy), None, shape, k, s, p, window_idx=widx)
+        dg, acc = grad_target(gamma)
+        db, acc_b = grad_target(beta)
+        if acc != acc_b:
+            raise RuntimeError("BatchNorm weight/bias gradient state out of sync")
+        dx2, _ = RF.bn_bwd(dz.reshape(-1, shape[-1]), x2, None, mean, invstd, gamma.detach(), want_dres=False, dgamma=dg,
+                           dbeta=db, accumulate=acc, fwd_scale=scale, fwd_shift=shift)
+        _notify(gamma)
+        _notify(beta)
+        dx = nchw(dx2.reshape(shape)) if ctx.needs_input_grad[0] else None
+        return (dx,) + (None,) * 10
+
+
 class AvgPool2dFn(Function):
     @staticmethod
     def forward(ctx, x, k, s, p):

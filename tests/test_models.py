@@ -256,3 +256,27 @@ def test_side_stream_weight_gradients_are_bitwise_the_same(monkeypatch):
     for a, b in zip(res[True], res[False]):
         for n in a:
             assert torch.equal(a[n], b[n]), n
+
+
+def test_fused_stem_pool_is_bit_identical_to_the_two_modules():
+    """ResNet stem: max_pool(relu(bn(conv))) with the BatchNorm-apply + ReLU folded into the pooling kernel against
+    BatchNorm2d(relu=True) + MaxPool2d: same kernels otherwise, so logits, running statistics and every gradient
+    must agree bit for bit."""
+    from replicann_b200.arch.resnet import ResNet
+    g = torch.Generator().manual_seed(21)
+    x = torch.randn(8, 3, 96, 96, generator=g).cuda()
+    y = torch.randint(0, 16, (8,), generator=g).cuda()
+    res = {}
+    for fused in (True, False):
+        torch.manual_seed(5)
+        m = ResNet((1, 1), bottleneck=True, n_classes=16).cuda().to(torch.bfloat16)
+        m._fused_stem = fused
+        logits = m(x)
+        F.cross_entropy(logits.float(), y).backward()
+        res[fused] = (logits.detach(), {n: p.grad.clone() for n, p in m.named_parameters()},
+                      {k: v.clone() for k, v in m.state_dict().items() if "running" in k or "num_batches" in k})
+    assert torch.equal(res[True][0], res[False][0])
+    for k in res[True][2]:
+        assert torch.equal(res[True][2][k], res[False][2][k]), k
+    for n in res[True][1]:
+        assert torch.equal(res[True][1][n], res[False][1][n]), n
