@@ -31,9 +31,13 @@ class _Bucket:
         self.pending, self.handle, self.launched = n_params, None, False
 
 
-def plan_buckets(sizes: list[int], itemsize: int, bucket_bytes: int) -> list[tuple[int, int]]:
+def plan_buckets(sizes: list[int], itemsize: int, bucket_bytes: int, tail_bytes: int = 0) -> list[tuple[int, int]]:
     """Greedy contiguous partition of parameter sizes (elements) into buckets of ~bucket_bytes.
-    Returns [(first_param, last_param_exclusive)]."""
+    Returns [(first_param, last_param_exclusive)].
+
+    `tail_bytes` > 0: the LAST bucket (the parameters whose gradients are produced last: nothing is left to overlap
+    its all-reduce with) is split so that its final part is at most ~tail_bytes; only that small part's exchange is
+    exposed after backward ends."""
     out, start, acc = [], 0, 0
     for i, n in enumerate(sizes):
         acc += n * itemsize
@@ -42,6 +46,16 @@ def plan_buckets(sizes: list[int], itemsize: int, bucket_bytes: int) -> list[tup
             start, acc = i + 1, 0
     if start < len(sizes):
         out.append((start, len(sizes)))
+    if tail_bytes > 0 and out:
+        a, b = out[-1]
+        acc, cut = 0, b
+        for i in range(b - 1, a, -1):       # walk back from the end while the tail stays within tail_bytes
+            if acc + sizes[i] * itemsize > tail_bytes:
+                break
+            acc += sizes[i] * itemsize
+            cut = i
+        if a < cut < b:
+            out[-1:] = [(a, cut), (cut, b)]
     return out
 
 
@@ -51,8 +65,13 @@ class DataParallel:
     Usage per step: `dp.begin_step()`, forward, `loss.backward()`, `dp.finish()`, `optimizer.step()`.
     """
 
-    def __init__(self, model: torch.nn.Module, optimizer, *, process_group=None, bucket_bytes: int = 25 << 20,
-                 broadcast_parameters: bool = True) -> None:
+    def __init__(self, model: torch.nn.Module, optimizer, *, process_group=None, bucket_bytes: int | None = None,
+                 tail_bytes: int | None = None, broadcast_parameters: bool = True) -> None:
+        import os
+        if bucket_bytes is None:   # RNN_DP_BUCKET_MB / RNN_DP_TAIL_MB: tuning without touching the caller
+            bucket_bytes = int(float(os.environ.get("RNN_DP_BUCKET_MB", "25")) * (1 << 20))
+        if tail_bytes is None:
+            tail_bytes = int(float(os.environ.get("RNN_DP_TAIL_MB", "4")) * (1 << 20))
         if not dist.is_initialized():
             raise RuntimeError("torch.distributed must be initialised before building DataParallel")
         self.model, self.optimizer, self.group = model, optimizer, process_group
@@ -65,7 +84,7 @@ class DataParallel:
         self._param_bucket: dict[int, _Bucket] = {}
         for g in optimizer.groups:
             sizes = [o2 - o1 for o1, o2 in zip(g.offsets, g.offsets[1:] + [g.numel])]
-            for a, b in plan_buckets(sizes, g.grad.element_size(), bucket_bytes):
+            for a, b in plan_buckets(sizes, g.grad.element_size(), bucket_bytes, tail_bytes):
                 lo = g.offsets[a]
                 hi = g.offsets[b] if b < len(g.offsets) else g.numel
                 bk = _Bucket(g.grad[lo:hi], b - a)

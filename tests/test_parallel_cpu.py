@@ -15,6 +15,10 @@ def test_plan_buckets():
     assert plan_buckets([100], 2, 40) == [(0, 1)]
     assert plan_buckets([1, 1, 1], 4, 1 << 20) == [(0, 3)]
     assert plan_buckets([], 2, 8) == []
+    # the last bucket is split so that only a small tail is exchanged after backward has ended
+    assert plan_buckets([10, 10, 10, 10, 3, 2], 2, 1 << 20, tail_bytes=12) == [(0, 4), (4, 6)]
+    assert plan_buckets([10, 10, 10], 2, 40, tail_bytes=4) == [(0, 2), (2, 3)]      # nothing small enough to split off
+    assert plan_buckets([5], 2, 40, tail_bytes=4) == [(0, 1)]
 
 
 def _free_port():
