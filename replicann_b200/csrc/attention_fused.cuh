@@ -14,9 +14,11 @@
 // (rnn_attention_tc_*) never reach HBM; the backward kernels below recompute the probabilities from the saved
 // log-sum-exp and regenerate the dropout mask from the same Philox counters.
 //
-// Roles (192 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..5 = softmax /
-// epilogue (thread = one query row = one TMEM lane).  Two S buffers in TMEM, two P buffers in shared memory: the
-// S product of tile j+1 overlaps the softmax of tile j, which overlaps the P V product of tile j-1.
+// Roles (320 threads): warp 0 = TMA producer, warp 1 = MMA issuer (one elected thread), warps 2..9 = softmax /
+// epilogue: a query row (= TMEM lane) is shared by two threads, one per 64-key half of every tile (the softmax,
+// mask and Philox arithmetic of these warps, not the tensor pipe, is what bounds the kernel; partial row maxima and
+// sums are combined through shared memory once per sweep).  Two S buffers in TMEM, two P buffers in shared memory:
+// the S product of tile j+1 overlaps the softmax of tile j, which overlaps the P V product of tile j-1.
 //
 // Included by attention.cu inside its anonymous namespace (shares philox4 / the dropout epoch with the other
 // attention kernels, so all paths draw the same keep mask for the same seed / offset).
@@ -27,8 +29,10 @@ namespace fa {
 constexpr int BQ = 128;    // query rows per CTA = TMEM lanes
 constexpr int BKV = 128;   // keys per tile
 constexpr int TILE64 = 16384;   // a [128 rows x 64 bf16] SWIZZLE_128B block
-constexpr int NTHREADS = 192;
+constexpr int NTHREADS = 320;   // producer warp, MMA warp, 8 softmax / epilogue warps (two threads per query row)
 constexpr float kLog2e = 1.4426950408889634f;
+constexpr int kMaskScratch = 8 * 4096;   // 4 KB per softmax warp (see scores32)
+constexpr int kMaxSmem = 232448;         // 227 KB of dynamic shared memory per CTA
 
 struct Params {
   int B, H, T, Tk;
@@ -54,10 +58,37 @@ struct Cfg {
 
 // ---- score of one element: s * scale + mask, in the log2 domain ---------------------------------------------------
 // 32 consecutive keys of one query row.  `ok` = the row exists (i < T).  Keys at or beyond Tk get -inf.
-__device__ __forceinline__ void scores32(const Params& p, const uint32_t* raw, float* s, int b, int i, int j0, bool ok) {
+// `mscr`: 4 KB of shared memory owned by the calling warp, or nullptr.  With it, an additive float mask is fetched by
+// the warp as a whole -- four fully used 128-byte lines per load instruction -- and transposed through the scratch
+// (XOR-swizzled, conflict-free both ways); without it every thread walks its own mask row and each load instruction
+// touches 32 different lines, which made the masked kernels L1-bound (the reference's decoder blocks always pass
+// such a mask, arch/transformer.py:148).  Must be called by all 32 lanes of the warp (rows i - lane .. i - lane + 31).
+__device__ __forceinline__ void scores32(const Params& p, const uint32_t* raw, float* s, int b, int i, int j0, bool ok,
+                                         float* mscr = nullptr, int lane = 0) {
   const float c = p.scale * kLog2e;
 #pragma unroll
   for (int e = 0; e < 32; ++e) s[e] = __uint_as_float(raw[e]) * c;
+  if (p.mask_kind == 2 && mscr != nullptr && p.mask_vec && j0 + 32 <= p.Tk) {
+    const float* mb = reinterpret_cast<const float*>(p.mask) + b * p.mask_bs + j0;
+    const int i_base = i - lane;
+#pragma unroll
+    for (int it = 0; it < 8; ++it) {
+      const int row_l = it * 4 + (lane >> 3), piece = lane & 7;
+      const int row = i_base + row_l;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < p.T) v = __ldg(reinterpret_cast<const float4*>(mb + (long long)row * p.mask_rs) + piece);
+      *reinterpret_cast<float4*>(mscr + row_l * 32 + ((piece ^ (row_l & 7)) << 2)) = v;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int e4 = 0; e4 < 8; ++e4) {
+      const float4 m = *reinterpret_cast<const float4*>(mscr + lane * 32 + ((e4 ^ (lane & 7)) << 2));
+      s[4 * e4 + 0] = fmaf(m.x, kLog2e, s[4 * e4 + 0]); s[4 * e4 + 1] = fmaf(m.y, kLog2e, s[4 * e4 + 1]);
+      s[4 * e4 + 2] = fmaf(m.z, kLog2e, s[4 * e4 + 2]); s[4 * e4 + 3] = fmaf(m.w, kLog2e, s[4 * e4 + 3]);
+    }
+    __syncwarp();
+    return;   // j0 + 32 <= Tk: no key of this chunk is out of range
+  }
   if (p.mask_kind == 1 && ok) {
     const uint8_t* mrow = reinterpret_cast<const uint8_t*>(p.mask) + b * p.mask_bs + i * p.mask_rs + j0;
     if (p.mask_vec && j0 + 32 <= p.Tk) {
@@ -216,7 +247,9 @@ __device__ __forceinline__ void mma_tn(uint32_t d_tmem, uint32_t sA, uint32_t sB
 template <int HS>
 struct FwdCfg : Cfg<HS> {
   static constexpr int STAGES = HS == 64 ? 3 : 2;                      // (K_j, V_j) ring
-  static constexpr int SMEM = Cfg<HS>::TILE * (1 + 2 * STAGES) + 2 * Cfg<HS>::PBYTES + 1024 + 256;
+  static constexpr int BASE = Cfg<HS>::TILE * (1 + 2 * STAGES) + 2 * Cfg<HS>::PBYTES + 1024 + 256 + 1024;
+  static constexpr bool MSCR = BASE + kMaskScratch <= kMaxSmem;    // room for the per-warp mask scratch?
+  static constexpr int SMEM = BASE + (MSCR ? kMaskScratch : 0);
 };
 
 template <int HS>
@@ -241,6 +274,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
   uint64_t* p_empty = p_full + 2;                       // [2]
   uint64_t* o_full = p_empty + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(o_full + 1);
+  float* xchg = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [2 halves][128 rows]
+  float* mscr_base = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256 + 1024);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -252,8 +287,8 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
     tc::mbar_init(q_full, 1);
     for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&kv_full[s], 1); tc::mbar_init(&kv_empty[s], 1); }
     for (int i = 0; i < 2; ++i) {
-      tc::mbar_init(&s_full[i], 1); tc::mbar_init(&s_empty[i], 4);
-      tc::mbar_init(&p_full[i], 4); tc::mbar_init(&p_empty[i], 1);
+      tc::mbar_init(&s_full[i], 1); tc::mbar_init(&s_empty[i], 8);
+      tc::mbar_init(&p_full[i], 8); tc::mbar_init(&p_empty[i], 1);
     }
     tc::mbar_init(o_full, 1);
     tc::fence_barrier_init();
@@ -332,23 +367,26 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
   } else {
     // ------------------------------------------------------------------------------------------ softmax / epilogue
     const int qd = warp & 3;                     // TMEM lane quarter this warp may read
+    const int half = (warp - 2) >> 2;            // which 64 keys of every 128-key tile this thread owns
     const int r = qd * 32 + lane;                // row inside the tile
     const int i = q0 + r;
     const bool row_ok = i < p.T;
     const int bh = b * p.H + h;
     const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
+    float* mscr = C::MSCR ? mscr_base + (warp - 2) * 1024 : nullptr;
     float m = -INFINITY;
     int t = 0;
     for (int j = 0; j < nkv; ++j, ++t) {
       tc::mbar_wait(&s_full[t & 1], ((uint32_t)t >> 1) & 1u);
       tc::tc_fence_after();
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int ch = half * 2 + cc;
         uint32_t raw[32];
         float s[32];
         tc::tmem_ld32(tS + lane_off + (uint32_t)((t & 1) * 128 + ch * 32), raw);
         tc::tmem_ld_wait();
-        scores32(p, raw, s, b, i, j * BKV + ch * 32, row_ok);
+        scores32(p, raw, s, b, i, j * BKV + ch * 32, row_ok, mscr, lane);
 #pragma unroll
         for (int e = 0; e < 32; ++e) m = fmaxf(m, s[e]);
       }
@@ -356,6 +394,11 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
       __syncwarp();
       if (lane == 0) tc::mbar_arrive(&s_empty[t & 1]);
     }
+    // row maximum over both halves
+    xchg[half * 128 + r] = m;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    m = fmaxf(m, xchg[(half ^ 1) * 128 + r]);
+    asm volatile("bar.sync 1, 256;" ::: "memory");   // xchg is reused for the row sums below
     float l = 0.f;
     for (int j = 0; j < nkv; ++j, ++t) {
       tc::mbar_wait(&s_full[t & 1], ((uint32_t)t >> 1) & 1u);
@@ -363,12 +406,13 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
       tc::tc_fence_after();
       uint8_t* pt = sP + (j & 1) * C::PBYTES;
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int ch = half * 2 + cc;
         uint32_t raw[32];
         float s[32];
         tc::tmem_ld32(tS + lane_off + (uint32_t)((t & 1) * 128 + ch * 32), raw);
         tc::tmem_ld_wait();
-        scores32(p, raw, s, b, i, j * BKV + ch * 32, row_ok);
+        scores32(p, raw, s, b, i, j * BKV + ch * 32, row_ok, mscr, lane);
 #pragma unroll
         for (int e = 0; e < 32; ++e) { s[e] = exp2f(s[e] - m); l += s[e]; }
         if (p.p_drop > 0.f) {
@@ -384,12 +428,19 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
       __syncwarp();
       if (lane == 0) { tc::mbar_arrive(&s_empty[t & 1]); tc::mbar_arrive(&p_full[j & 1]); }
     }
+    // row sum over both halves, in a fixed order (half 0 + half 1) so that both threads hold the same value
+    xchg[half * 128 + r] = l;
+    asm volatile("bar.sync 1, 256;" ::: "memory");
+    l = xchg[r] + xchg[128 + r];
     // epilogue: O / l -> z, log-sum-exp (natural log) for the backward pass
     tc::mbar_wait(o_full, 0);
     tc::tc_fence_after();
-    if (row_ok && p.lse != nullptr) p.lse[(long long)bh * p.T + i] = (m + log2f(l)) * 0.6931471805599453f;
-    // every P V product has retired: the first P buffer is free and serves as the store staging area
-    store_acc_rows<HS / 64>(tO + lane_off, 1.f / l, sP + (warp - 2) * 4096, &tmZ, h * HS, q0 + qd * 32, b, lane);
+    if (half == 0 && row_ok && p.lse != nullptr) p.lse[(long long)bh * p.T + i] = (m + log2f(l)) * 0.6931471805599453f;
+    // every P V product has retired: the first P buffer is free and serves as the store staging area.  The 64-column
+    // chunks of O are dealt out to the two halves (head size 64: one chunk, half 0 stores it).
+    if (half < HS / 64)
+      store_acc_rows<1>(tO + lane_off + (uint32_t)(half * 64), 1.f / l, sP + (warp - 2) * 4096, &tmZ, h * HS + half * 64,
+                        q0 + qd * 32, b, lane);
   }
 
   tc::tc_fence_before();
@@ -412,9 +463,10 @@ fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUte
 
 // p (normalised probability) and dS of 32 keys of one row; `raw_s`, `raw_dp` = S and dPd accumulator words
 __device__ __forceinline__ void bwd_row32(const Params& p, const uint32_t* raw_s, const uint32_t* raw_dp, float* pd, float* ds,
-                                          int b, int bh, int i, int j0, bool ok, float lse2, float delta) {
+                                          int b, int bh, int i, int j0, bool ok, float lse2, float delta,
+                                          float* mscr = nullptr, int lane = 0) {
   float s[32];
-  scores32(p, raw_s, s, b, i, j0, ok);
+  scores32(p, raw_s, s, b, i, j0, ok, mscr, lane);
   float kf[32];
   if (p.p_drop > 0.f) keep32(p, kf, bh, i, j0);
 #pragma unroll
@@ -429,7 +481,9 @@ __device__ __forceinline__ void bwd_row32(const Params& p, const uint32_t* raw_s
 template <int HS>
 struct DqCfg : Cfg<HS> {
   static constexpr int STAGES = 2;                                     // (K_j, V_j) ring
-  static constexpr int SMEM = Cfg<HS>::TILE * (2 + 2 * STAGES) + Cfg<HS>::PBYTES + 1024 + 256;
+  static constexpr int BASE = Cfg<HS>::TILE * (2 + 2 * STAGES) + Cfg<HS>::PBYTES + 1024 + 256;
+  static constexpr bool MSCR = BASE + kMaskScratch <= kMaxSmem;
+  static constexpr int SMEM = BASE + (MSCR ? kMaskScratch : 0);
 };
 
 template <int HS>
@@ -455,6 +509,7 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
   uint64_t* ds_empty = ds_full + 1;
   uint64_t* dq_full = ds_empty + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(dq_full + 1);
+  float* mscr_base = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -466,8 +521,8 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
     tc::prefetch_tmap(&tmDQ);
     tc::mbar_init(qdo_full, 1);
     for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&kv_full[s], 1); tc::mbar_init(&kv_empty[s], 1); }
-    tc::mbar_init(sd_full, 1); tc::mbar_init(sd_empty, 4);
-    tc::mbar_init(ds_full, 4); tc::mbar_init(ds_empty, 1);
+    tc::mbar_init(sd_full, 1); tc::mbar_init(sd_empty, 8);
+    tc::mbar_init(ds_full, 8); tc::mbar_init(ds_empty, 1);
     tc::mbar_init(dq_full, 1);
     tc::fence_barrier_init();
   }
@@ -523,12 +578,14 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
     __syncwarp();
   } else {
     const int qd = warp & 3;
+    const int half = (warp - 2) >> 2;            // which 64 keys of every tile this thread owns
     const int r = qd * 32 + lane;
     const int i = q0 + r;
     const bool row_ok = i < p.T;
     const int bh = b * p.H + h;
     const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
-    // delta_i = dO_i . z_i over this head's columns (fp32), kept for the dK / dV kernel
+    // delta_i = dO_i . z_i over this head's columns (fp32; both threads of a row compute it, one keeps it for the
+    // dK / dV kernel)
     float delta = 0.f, lse2 = 0.f;
     if (row_ok) {
       const bf16* zr = p.z + (long long)b * p.z_bs + (long long)i * p.z_rs + h * HS;
@@ -541,7 +598,7 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
 #pragma unroll
         for (int e = 0; e < 8; ++e) delta = fmaf(a[e], g[e], delta);
       }
-      p.delta[(long long)bh * p.T + i] = delta;
+      if (half == 0) p.delta[(long long)bh * p.T + i] = delta;
       lse2 = p.lse[(long long)bh * p.T + i] * kLog2e;
     }
     for (int j = 0; j < nkv; ++j) {
@@ -549,13 +606,15 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
       tc::mbar_wait(ds_empty, ((uint32_t)j & 1u) ^ 1u);
       tc::tc_fence_after();
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int ch = half * 2 + cc;
         uint32_t rs[32], rp[32];
         float pd[32], ds[32];
         tc::tmem_ld32(tS + lane_off + (uint32_t)(ch * 32), rs);
         tc::tmem_ld32(tDP + lane_off + (uint32_t)(ch * 32), rp);
         tc::tmem_ld_wait();
-        bwd_row32(p, rs, rp, pd, ds, b, bh, i, j * BKV + ch * 32, row_ok, lse2, delta);
+        bwd_row32(p, rs, rp, pd, ds, b, bh, i, j * BKV + ch * 32, row_ok, lse2, delta,
+                  C::MSCR ? mscr_base + (warp - 2) * 1024 : nullptr, lane);
         store_tile_row32(sDS, r, ch * 32, ds);
       }
       tc::tc_fence_before();
@@ -565,7 +624,9 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
     }
     tc::mbar_wait(dq_full, 0);
     tc::tc_fence_after();
-    store_acc_rows<HS / 64>(tDQ + lane_off, 1.f, sDS + (warp - 2) * 4096, &tmDQ, h * HS, q0 + qd * 32, b, lane);
+    if (half < HS / 64)
+      store_acc_rows<1>(tDQ + lane_off + (uint32_t)(half * 64), 1.f, sDS + (warp - 2) * 4096, &tmDQ, h * HS + half * 64,
+                        q0 + qd * 32, b, lane);
   }
 
   tc::tc_fence_before();
@@ -579,7 +640,9 @@ dq_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUten
 template <int HS>
 struct DkvCfg : Cfg<HS> {
   static constexpr int STAGES = HS == 64 ? 2 : 1;                      // (Q_i, dO_i) ring
-  static constexpr int SMEM = Cfg<HS>::TILE * (2 + 2 * STAGES) + 2 * Cfg<HS>::PBYTES + 1024 + 256;
+  static constexpr int BASE = Cfg<HS>::TILE * (2 + 2 * STAGES) + 2 * Cfg<HS>::PBYTES + 1024 + 256;
+  static constexpr bool MSCR = BASE + kMaskScratch <= kMaxSmem;
+  static constexpr int SMEM = BASE + (MSCR ? kMaskScratch : 0);
 };
 
 template <int HS>
@@ -607,6 +670,7 @@ dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   uint64_t* pds_empty = pds_full + 1;
   uint64_t* out_full = pds_empty + 1;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(out_full + 1);
+  float* mscr_base = reinterpret_cast<float*>(reinterpret_cast<uint8_t*>(bars) + 256);
 
   const int warp = __shfl_sync(0xffffffffu, (int)(threadIdx.x >> 5), 0);
   const int lane = threadIdx.x & 31;
@@ -618,8 +682,8 @@ dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     tc::prefetch_tmap(&tmDK); tc::prefetch_tmap(&tmDV);
     tc::mbar_init(kv_full, 1);
     for (int s = 0; s < C::STAGES; ++s) { tc::mbar_init(&qd_full[s], 1); tc::mbar_init(&qd_empty[s], 1); }
-    tc::mbar_init(sd_full, 1); tc::mbar_init(sd_empty, 4);
-    tc::mbar_init(pds_full, 4); tc::mbar_init(pds_empty, 1);
+    tc::mbar_init(sd_full, 1); tc::mbar_init(sd_empty, 8);
+    tc::mbar_init(pds_full, 8); tc::mbar_init(pds_empty, 1);
     tc::mbar_init(out_full, 1);
     tc::fence_barrier_init();
   }
@@ -676,6 +740,7 @@ dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     __syncwarp();
   } else {
     const int qd = warp & 3;
+    const int half = (warp - 2) >> 2;            // which 64 keys of the tile this thread owns
     const int r = qd * 32 + lane;
     const int bh = b * p.H + h;
     const uint32_t lane_off = (uint32_t)(qd * 32) << 16;
@@ -688,13 +753,15 @@ dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       tc::mbar_wait(pds_empty, ((uint32_t)it & 1u) ^ 1u);
       tc::tc_fence_after();
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int cc = 0; cc < 2; ++cc) {
+        const int ch = half * 2 + cc;
         uint32_t rs[32], rp[32];
         float pd[32], ds[32];
         tc::tmem_ld32(tS + lane_off + (uint32_t)(ch * 32), rs);
         tc::tmem_ld32(tDP + lane_off + (uint32_t)(ch * 32), rp);
         tc::tmem_ld_wait();
-        bwd_row32(p, rs, rp, pd, ds, b, bh, i, k0 + ch * 32, row_ok, lse2, delta);
+        bwd_row32(p, rs, rp, pd, ds, b, bh, i, k0 + ch * 32, row_ok, lse2, delta,
+                  C::MSCR ? mscr_base + (warp - 2) * 1024 : nullptr, lane);
         if (!row_ok) {
 #pragma unroll
           for (int e = 0; e < 32; ++e) ds[e] = 0.f;     // rows past T must not reach dK / dV
@@ -709,9 +776,11 @@ dkdv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     }
     tc::mbar_wait(out_full, 0);
     tc::tc_fence_after();
-    // rows of the accumulators are keys here
-    store_acc_rows<HS / 64>(tDV + lane_off, 1.f, sPD + (warp - 2) * 4096, &tmDV, h * HS, k0 + qd * 32, b, lane);
-    store_acc_rows<HS / 64>(tDK + lane_off, 1.f, sPD + (warp - 2) * 4096, &tmDK, h * HS, k0 + qd * 32, b, lane);
+    // rows of the accumulators are keys here; one half of the warps stores dV, the other dK
+    if (half == 0)
+      store_acc_rows<HS / 64>(tDV + lane_off, 1.f, sPD + (warp - 2) * 4096, &tmDV, h * HS, k0 + qd * 32, b, lane);
+    else
+      store_acc_rows<HS / 64>(tDK + lane_off, 1.f, sPD + (warp - 2) * 4096, &tmDK, h * HS, k0 + qd * 32, b, lane);
   }
 
   tc::tc_fence_before();

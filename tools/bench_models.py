@@ -61,10 +61,11 @@ def main():
         for dt in (torch.bfloat16, torch.float32):
             enc = TransformerEncoder(H, E).cuda().to(dt).train()
             xx = torch.randn(B, T, E, device="cuda", dtype=dt, requires_grad=True)
+            from replicann_b200.optim import AdamW
+            opt_ = AdamW(enc.parameters(), lr=1e-4)   # flat buckets: packed q/k/v projections, gradients in place
 
-            def step():
-                for p in enc.parameters():
-                    p.grad = None
+            def step(opt_=opt_, enc=enc, xx=xx):
+                opt_.zero_grad()
                 enc(xx).float().sum().backward()
             ms = timed(step, 3, 5)
             out.write(f"TransformerEncoder {tag} B{B} T{T} E{E} H{H} fwd+bwd {str(dt)[6:]}\teager\t{ms:.3f}\t{B * T / ms * 1e3:.0f}\ttokens/s\n")
