@@ -141,6 +141,31 @@ def test_maxpool_indices_bit_exact(dtype, N, H, W, C, k, s, p):
     assert torch.equal(dx2, dx)
 
 
+@pytest.mark.parametrize("N,H,W,C", [(2, 30, 18, 64), (3, 13, 11, 16), (1, 8, 8, 8), (2, 21, 112, 64)])
+def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, monkeypatch):
+    """The marching forward / backward kernels of the 3x3 / stride 2 / pad 1 pool (rows carried in registers) against
+    the one-row-per-CTA kernels: values, both index forms and dx bit for bit -- with ties, -inf, NaN, and the
+    BatchNorm+ReLU-fused forward; and against torch for the NaN-free part."""
+    f = RF()
+    x = (rnd((N, H, W, C), 5, torch.bfloat16) * 2).round() / 2
+    x[0, 2, 3, 1] = float("nan"); x[0, 3, 3, 1] = float("nan"); x[-1, H - 1, W - 1, 0] = float("nan")
+    x[0, :5, :5, 2] = float("-inf")
+    scale = (torch.rand(C) + 0.5).cuda(); shift = (torch.randn(C) * 0.3).cuda()
+    dy = rnd((N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, C), 6, torch.bfloat16).cuda()
+    out = {}
+    for mode in ("0", "1"):
+        monkeypatch.setenv("RNN_POOL_MARCH", mode)
+        y, idx, widx = f.maxpool2d_fwd(x.cuda(), 3, 2, 1, return_window_idx=True)
+        yb, wb = f.bn_relu_maxpool2d_fwd(x.cuda(), scale, shift, 3, 2, 1)
+        dx = f.maxpool2d_bwd(dy, None, tuple(x.shape), 3, 2, 1, window_idx=widx)
+        out[mode] = (y, idx, widx, yb, wb, dx)
+    for a, b in zip(out["0"], out["1"]):
+        assert torch.equal(a.view(torch.uint8) if a.dtype == torch.bfloat16 else a,
+                           b.view(torch.uint8) if b.dtype == torch.bfloat16 else b)
+    ref, ridx = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1, return_indices=True)
+    assert torch.equal(out["1"][1].cpu().long(), ridx.permute(0, 2, 3, 1))
+
+
 def test_maxpool_nan_propagates():
     f = RF()
     x = rnd((1, 4, 4, 8), 1)
