@@ -285,12 +285,24 @@ maxpool_bwd_3x3s2_kernel(const T* __restrict__ dy, const unsigned char* __restri
 //             and column; "first maximum, NaN wins" composes over rows) is carried, so a window costs 6 loads (and 6
 //             BatchNorm+ReLU evaluations in the fused form) instead of 9;
 //   backward: window row p+1 serves the input quads of rows p and p+1 -- 2 window loads per quad instead of 4.
-// Measured on [256,112,112,64] (tools/bench_pool.py): backward 255 -> 134 us (4.2 TB/s); fused forward 285 -> 257 us.
+// Measured on [256,112,112,64] (tools/bench_pool.py): backward 255 -> 134 us (4.2 TB/s), forward 211 -> 134 us,
+// BatchNorm+ReLU-fused forward 285 -> 189 us.
 constexpr int MROWS = 4;
 
+// The forward kernel compares in packed bf16x2 (the values ARE bf16, so the packed compare is exact): one HSET2 pair
+// + three LOP3 per two channels and window position instead of ~12 scalar instructions -- the scalar form ran at 123
+// registers and 780 instructions per output vector (ncu), i.e. instruction-bound at 2 TB/s.
+__device__ __forceinline__ unsigned pool_take_mask(unsigned v, unsigned best) {   // v > best || isnan(v), per half
+  const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(&v);
+  const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(&best);
+  return __hgt2_mask(a, b) | __hneu2_mask(a, a);
+}
+__device__ __forceinline__ unsigned pool_sel(unsigned m, unsigned a, unsigned b) { return (a & m) | (b & ~m); }
+
+// 3-wide maximum of one input row for 8 channels: rv[4] packed values, rc[4] the column (0..2) in each 16-bit half
 template <bool BN>
 __device__ __forceinline__ void pool_row_max(const bf16* __restrict__ xrow, int w0, int W, int C, const float* sc,
-                                             const float* sf, float* rv, int* rc) {
+                                             const float* sf, unsigned* rv, unsigned* rc) {
   uint4 raw[3];
   bool in[3];
 #pragma unroll
@@ -299,27 +311,33 @@ __device__ __forceinline__ void pool_row_max(const bf16* __restrict__ xrow, int 
     in[s] = w >= 0 && w < W;
     if (in[s]) raw[s] = *reinterpret_cast<const uint4*>(xrow + (long long)w * C);
   }
-  const int first = w0 < 0 ? -w0 : 0;
+  const unsigned first = w0 < 0 ? 0x00010001u : 0u;
 #pragma unroll
-  for (int e2 = 0; e2 < 8; ++e2) { rv[e2] = -INFINITY; rc[e2] = first; }
+  for (int k = 0; k < 4; ++k) { rv[k] = 0xff80ff80u; rc[k] = first; }   // -inf, first column inside the image
 #pragma unroll
   for (int s = 0; s < 3; ++s) {
     if (!in[s]) continue;
-    float v[8];
-    unpack8(raw[s], v);
+    unsigned v[4] = {raw[s].x, raw[s].y, raw[s].z, raw[s].w};
     if (BN) {
 #pragma unroll
-      for (int e2 = 0; e2 < 8; ++e2)   // what a separate BatchNorm-apply kernel would have stored (rounded to bf16)
-        v[e2] = __bfloat162float(__float2bfloat16(fmaxf(fmaf(v[e2], sc[e2], sf[e2]), 0.f)));
+      for (int k = 0; k < 4; ++k) {   // what a separate BatchNorm-apply kernel would have stored (rounded to bf16)
+        const float lo = fmaxf(fmaf(__uint_as_float(v[k] << 16), sc[2 * k], sf[2 * k]), 0.f);
+        const float hi = fmaxf(fmaf(__uint_as_float(v[k] & 0xffff0000u), sc[2 * k + 1], sf[2 * k + 1]), 0.f);
+        const __nv_bfloat162 t = __floats2bfloat162_rn(lo, hi);
+        v[k] = *reinterpret_cast<const unsigned*>(&t);
+      }
     }
 #pragma unroll
-    for (int e2 = 0; e2 < 8; ++e2)
-      if (v[e2] > rv[e2] || v[e2] != v[e2]) { rv[e2] = v[e2]; rc[e2] = s; }
+    for (int k = 0; k < 4; ++k) {
+      const unsigned m = pool_take_mask(v[k], rv[k]);
+      rv[k] = pool_sel(m, v[k], rv[k]);
+      rc[k] = pool_sel(m, (unsigned)s * 0x00010001u, rc[k]);
+    }
   }
 }
 
 template <bool BN>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, BN ? 3 : 4)   // measured: fused 189 us at 3 (235 at 4: spills), plain 134 us at 4
 maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int* __restrict__ idx,
                                unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift,
                                const float* __restrict__ scale, const float* __restrict__ shift) {
@@ -338,45 +356,53 @@ maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
   }
   const bf16* xn = x + (long long)n * g.H * g.W * g.C + cg * 8;
   const long long rowb = (long long)g.W * g.C;
-  float cv[8];
-  int cc[8];
+  unsigned cv[4], cc[4];
   bool have = p0 > 0;                       // window p0's top row 2*p0 - 1 exists
   if (have) pool_row_max<BN>(xn + (long long)(2 * p0 - 1) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
   for (int p = p0; p < p1; ++p) {
     const int h0 = 2 * p - 1;
-    float best[8];
-    int bl[8];
-    const int first = (h0 < 0 ? 3 : 0) + (w0 < 0 ? 1 : 0);
+    unsigned best[4], bl[4];                // bl: position inside the 3x3 window, per 16-bit half
+    const unsigned first = (unsigned)((h0 < 0 ? 3 : 0) + (w0 < 0 ? 1 : 0)) * 0x00010001u;
 #pragma unroll
-    for (int e2 = 0; e2 < 8; ++e2) { best[e2] = -INFINITY; bl[e2] = first; }
+    for (int k = 0; k < 4; ++k) { best[k] = 0xff80ff80u; bl[k] = first; }
     if (have) {
 #pragma unroll
-      for (int e2 = 0; e2 < 8; ++e2)
-        if (cv[e2] > best[e2] || cv[e2] != cv[e2]) { best[e2] = cv[e2]; bl[e2] = cc[e2]; }
+      for (int k = 0; k < 4; ++k) {
+        const unsigned m = pool_take_mask(cv[k], best[k]);
+        best[k] = pool_sel(m, cv[k], best[k]);
+        bl[k] = pool_sel(m, cc[k], bl[k]);
+      }
     }
-    float rv[8];
-    int rc[8];
+    unsigned rv[4], rc[4];
     pool_row_max<BN>(xn + (long long)(h0 + 1) * rowb, w0, g.W, g.C, sc, sf, rv, rc);   // row 2p: always inside
-#pragma unroll
-    for (int e2 = 0; e2 < 8; ++e2)
-      if (rv[e2] > best[e2] || rv[e2] != rv[e2]) { best[e2] = rv[e2]; bl[e2] = 3 + rc[e2]; }
     have = h0 + 2 < g.H;
-    if (have) {
-      pool_row_max<BN>(xn + (long long)(h0 + 2) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
+    if (have) pool_row_max<BN>(xn + (long long)(h0 + 2) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
 #pragma unroll
-      for (int e2 = 0; e2 < 8; ++e2)
-        if (cv[e2] > best[e2] || cv[e2] != cv[e2]) { best[e2] = cv[e2]; bl[e2] = 6 + cc[e2]; }
+    for (int k = 0; k < 4; ++k) {
+      const unsigned m = pool_take_mask(rv[k], best[k]);
+      best[k] = pool_sel(m, rv[k], best[k]);
+      bl[k] = pool_sel(m, rc[k] + 0x00030003u, bl[k]);
+    }
+    if (have) {
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const unsigned m = pool_take_mask(cv[k], best[k]);
+        best[k] = pool_sel(m, cv[k], best[k]);
+        bl[k] = pool_sel(m, cc[k] + 0x00060006u, bl[k]);
+      }
     }
     const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * 8;
-    *reinterpret_cast<uint4*>(y + o) = pack8(best);
+    *reinterpret_cast<uint4*>(y + o) = make_uint4(best[0], best[1], best[2], best[3]);
     if (idx) {
 #pragma unroll
       for (int e2 = 0; e2 < 8; ++e2) {
-        const int lh = bl[e2] / 3, lw = bl[e2] - lh * 3;
+        const int l = (int)((bl[e2 >> 1] >> (16 * (e2 & 1))) & 0xffu);
+        const int lh = l / 3, lw = l - lh * 3;
         idx[o + e2] = (h0 + lh) * g.W + (w0 + lw);
       }
     }
-    if (widx) WIdx<8>::store(widx + o, bl);
+    if (widx)   // bytes 0 and 2 of each position word -> one byte per channel
+      *reinterpret_cast<uint2*>(widx + o) = make_uint2(__byte_perm(bl[0], bl[1], 0x6420), __byte_perm(bl[2], bl[3], 0x6420));
   }
 }
 
@@ -626,11 +652,12 @@ static int maxpool_fwd_impl(const void* x, void* y, int* indices, unsigned char*
   } else if (!vec) {
     maxpool_fwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
   } else {
-    // marching forward only in the BatchNorm+ReLU-fused form (measured at the stem shape: 285 -> 257 us fused, where
-    // the saved work is 3 of 9 BatchNorm evaluations; 211 -> 225 us unfused, where the row kernel stays)
-    if (fx == 1 && scale != nullptr && pool_march_enabled()) {
+    if (fx == 1 && pool_march_enabled()) {
       const dim3 mg(grid.x, ceil_div_i(g.P, MROWS), N);
-      maxpool_fwd_3x3s2_march_kernel<true><<<mg, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
+      if (scale != nullptr)
+        maxpool_fwd_3x3s2_march_kernel<true><<<mg, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
+      else
+        maxpool_fwd_3x3s2_march_kernel<false><<<mg, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
       RNN_CHECK_LAUNCH();
       return RNN_OK;
     }
