@@ -336,7 +336,7 @@ __device__ __forceinline__ void pool_row_max(const bf16* __restrict__ xrow, int 
   }
 }
 
-template <bool BN>
+template <bool BN, int PAD>
 __global__ void __launch_bounds__(256, BN ? 3 : 4)   // measured: fused 189 us at 3 (235 at 4: spills), plain 134 us at 4
 maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y, int* __restrict__ idx,
                                unsigned char* __restrict__ widx, PoolGeom g, int cgs_shift,
@@ -348,7 +348,7 @@ maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
   const int cg = e - q * cgs;
   const int n = blockIdx.z, p0 = blockIdx.y * MROWS;
   const int p1 = min(p0 + MROWS, g.P);
-  const int w0 = 2 * q - 1;
+  const int w0 = 2 * q - PAD;
   float sc[8], sf[8];
   if (BN) {
 #pragma unroll
@@ -357,10 +357,10 @@ maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
   const bf16* xn = x + (long long)n * g.H * g.W * g.C + cg * 8;
   const long long rowb = (long long)g.W * g.C;
   unsigned cv[4], cc[4];
-  bool have = p0 > 0;                       // window p0's top row 2*p0 - 1 exists
-  if (have) pool_row_max<BN>(xn + (long long)(2 * p0 - 1) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
+  bool have = PAD == 0 || p0 > 0;           // window p0's top row 2*p0 - PAD exists
+  if (have) pool_row_max<BN>(xn + (long long)(2 * p0 - PAD) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
   for (int p = p0; p < p1; ++p) {
-    const int h0 = 2 * p - 1;
+    const int h0 = 2 * p - PAD;
     unsigned best[4], bl[4];                // bl: position inside the 3x3 window, per 16-bit half
     const unsigned first = (unsigned)((h0 < 0 ? 3 : 0) + (w0 < 0 ? 1 : 0)) * 0x00010001u;
 #pragma unroll
@@ -374,7 +374,7 @@ maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
       }
     }
     unsigned rv[4], rc[4];
-    pool_row_max<BN>(xn + (long long)(h0 + 1) * rowb, w0, g.W, g.C, sc, sf, rv, rc);   // row 2p: always inside
+    pool_row_max<BN>(xn + (long long)(h0 + 1) * rowb, w0, g.W, g.C, sc, sf, rv, rc);   // middle row: always inside
     have = h0 + 2 < g.H;
     if (have) pool_row_max<BN>(xn + (long long)(h0 + 2) * rowb, w0, g.W, g.C, sc, sf, cv, cc);
 #pragma unroll
@@ -406,17 +406,25 @@ maxpool_fwd_3x3s2_march_kernel(const bf16* __restrict__ x, bf16* __restrict__ y,
   }
 }
 
+// Quads for padding PAD: quad (p, q) holds the inputs (2p+a+OFF, 2q+b+OFF), OFF = 1 - PAD, a, b in {0, 1}; it is
+// covered by the windows (p..p+1, q..q+1) at row a+1-2*wa, column b+1-2*wb.  With PAD = 0 the quads start at -1
+// (row / column 0 is the second element of quad -1).
+__host__ __device__ inline int pool_quads(int extent, int pad) { return (extent - 1 - (1 - pad)) / 2 + (1 - pad) + 1; }
+
+template <int PAD>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_3x3s2_march_kernel(const bf16* __restrict__ dy, const unsigned char* __restrict__ widx,
                                bf16* __restrict__ dx, PoolGeom g, int cgs_shift) {
+  constexpr int OFF = 1 - PAD;
   const int cgs = g.C >> 3;
-  const int Qx = (g.W + 1) / 2, Px = (g.H + 1) / 2;
+  const int Qx = pool_quads(g.W, PAD), Px = pool_quads(g.H, PAD);
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= Qx * cgs) return;
-  const int q = cgs_shift >= 0 ? (e >> cgs_shift) : (int)((unsigned)e / (unsigned)cgs);
-  const int cg = e - q * cgs;
-  const int n = blockIdx.z, p0 = blockIdx.y * MROWS;
-  const int p1 = min(p0 + MROWS, Px);
+  const int qi = cgs_shift >= 0 ? (e >> cgs_shift) : (int)((unsigned)e / (unsigned)cgs);
+  const int cg = e - qi * cgs;
+  const int q = qi - OFF;
+  const int n = blockIdx.z, p0 = blockIdx.y * MROWS - OFF;
+  const int p1 = min(p0 + MROWS, Px - OFF);
   // window row r, columns q and q+1: output gradients (packed bf16) and argmax positions (8 bytes)
   uint4 d0[2], d1[2];
   uint2 l0[2], l1[2];
@@ -424,7 +432,7 @@ maxpool_bwd_3x3s2_march_kernel(const bf16* __restrict__ dy, const unsigned char*
   auto load_row = [&](int r, uint4* d, uint2* l, bool* ok) {
 #pragma unroll
     for (int b = 0; b < 2; ++b) {
-      ok[b] = r < g.P && (q + b) < g.Q;
+      ok[b] = r >= 0 && r < g.P && (q + b) >= 0 && (q + b) < g.Q;
       if (ok[b]) {
         const long long o = (((long long)n * g.P + r) * g.Q + (q + b)) * g.C + cg * 8;
         d[b] = *reinterpret_cast<const uint4*>(dy + o);
@@ -435,13 +443,13 @@ maxpool_bwd_3x3s2_march_kernel(const bf16* __restrict__ dy, const unsigned char*
   load_row(p0, d0, l0, ok0);
   for (int p = p0; p < p1; ++p) {
     load_row(p + 1, d1, l1, ok1);
-    // input (2p+a, 2q+b) sits at row a+1-2*wa, column b+1-2*wb of window (p+wa, q+wb); sums in (wa, wb) order
+    // sums in (wa, wb) order: ascending window index, as the generic kernel
 #pragma unroll
     for (int a = 0; a < 2; ++a)
 #pragma unroll
       for (int b = 0; b < 2; ++b) {
-        const int h = 2 * p + a, w = 2 * q + b;
-        if (h >= g.H || w >= g.W) continue;
+        const int h = 2 * p + a + OFF, w = 2 * q + b + OFF;
+        if (h < 0 || w < 0 || h >= g.H || w >= g.W) continue;
         float acc[8];
 #pragma unroll
         for (int e2 = 0; e2 < 8; ++e2) acc[e2] = 0.f;
@@ -652,12 +660,18 @@ static int maxpool_fwd_impl(const void* x, void* y, int* indices, unsigned char*
   } else if (!vec) {
     maxpool_fwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
   } else {
-    if (fx == 1 && pool_march_enabled()) {
+    if ((fx == 1 || fx == 3) && pool_march_enabled()) {   // 3x3 stride 2, pad 1 (ResNet stem) or 0 (AlexNet)
       const dim3 mg(grid.x, ceil_div_i(g.P, MROWS), N);
-      if (scale != nullptr)
-        maxpool_fwd_3x3s2_march_kernel<true><<<mg, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
+      const bf16* xi = (const bf16*)x;
+      bf16* yo = (bf16*)y;
+      if (fx == 1 && scale != nullptr)
+        maxpool_fwd_3x3s2_march_kernel<true, 1><<<mg, 256, 0, stream>>>(xi, yo, indices, window_idx, g, sh_, scale, shift);
+      else if (fx == 1)
+        maxpool_fwd_3x3s2_march_kernel<false, 1><<<mg, 256, 0, stream>>>(xi, yo, indices, window_idx, g, sh_, scale, shift);
+      else if (scale != nullptr)
+        maxpool_fwd_3x3s2_march_kernel<true, 0><<<mg, 256, 0, stream>>>(xi, yo, indices, window_idx, g, sh_, scale, shift);
       else
-        maxpool_fwd_3x3s2_march_kernel<false><<<mg, 256, 0, stream>>>((const bf16*)x, (bf16*)y, indices, window_idx, g, sh_, scale, shift);
+        maxpool_fwd_3x3s2_march_kernel<false, 0><<<mg, 256, 0, stream>>>(xi, yo, indices, window_idx, g, sh_, scale, shift);
       RNN_CHECK_LAUNCH();
       return RNN_OK;
     }
@@ -700,14 +714,17 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
     RNN_CHECK_LAUNCH();
     return RNN_OK;
   }
+  if (!is_f32 && vec && window_idx != nullptr && (fx == 1 || fx == 3) && pool_march_enabled()) {
+    // 3x3 stride 2, pad 1 (ResNet stem) or pad 0 (AlexNet): marching 2x2 input quads
+    const int pad = fx == 1 ? 1 : 0;
+    const dim3 mg(ceil_div_i((long long)pool_quads(W, pad) * cgs, 256), ceil_div_i(pool_quads(H, pad), MROWS), N);
+    if (pad) maxpool_bwd_3x3s2_march_kernel<1><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    else maxpool_bwd_3x3s2_march_kernel<0><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    RNN_CHECK_LAUNCH();
+    return RNN_OK;
+  }
   if (!is_f32 && vec && window_idx != nullptr && fx == 1) {   // 3x3 stride 2 pad 1: one thread per 2x2 input quad
     const dim3 tg(ceil_div_i((long long)((W + 1) / 2) * cgs, 256), (H + 1) / 2, N);
-    if (pool_march_enabled()) {
-      const dim3 mg(tg.x, ceil_div_i((H + 1) / 2, MROWS), N);
-      maxpool_bwd_3x3s2_march_kernel<<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
-      RNN_CHECK_LAUNCH();
-      return RNN_OK;
-    }
     maxpool_bwd_3x3s2_kernel<bf16><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
     RNN_CHECK_LAUNCH();
     return RNN_OK;

@@ -141,8 +141,10 @@ def test_maxpool_indices_bit_exact(dtype, N, H, W, C, k, s, p):
     assert torch.equal(dx2, dx)
 
 
-@pytest.mark.parametrize("N,H,W,C", [(2, 30, 18, 64), (3, 13, 11, 16), (1, 8, 8, 8), (2, 21, 112, 64)])
-def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, monkeypatch):
+@pytest.mark.parametrize("pad", [1, 0])
+@pytest.mark.parametrize("N,H,W,C", [(2, 30, 18, 64), (3, 13, 11, 16), (1, 8, 8, 8), (2, 21, 112, 64), (2, 55, 55, 64),
+                                     (2, 14, 27, 192)])
+def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, pad, monkeypatch):
     """The marching forward / backward kernels of the 3x3 / stride 2 / pad 1 pool (rows carried in registers) against
     the one-row-per-CTA kernels: values, both index forms and dx bit for bit -- with ties, -inf, NaN, and the
     BatchNorm+ReLU-fused forward; and against torch for the NaN-free part."""
@@ -151,13 +153,13 @@ def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, monkey
     x[0, 2, 3, 1] = float("nan"); x[0, 3, 3, 1] = float("nan"); x[-1, H - 1, W - 1, 0] = float("nan")
     x[0, :5, :5, 2] = float("-inf")
     scale = (torch.rand(C) + 0.5).cuda(); shift = (torch.randn(C) * 0.3).cuda()
-    dy = rnd((N, (H - 1) // 2 + 1, (W - 1) // 2 + 1, C), 6, torch.bfloat16).cuda()
+    dy = rnd((N, (H + 2 * pad - 3) // 2 + 1, (W + 2 * pad - 3) // 2 + 1, C), 6, torch.bfloat16).cuda()
     out = {}
     for mode in ("0", "1"):
         monkeypatch.setenv("RNN_POOL_MARCH", mode)
-        y, idx, widx = f.maxpool2d_fwd(x.cuda(), 3, 2, 1, return_window_idx=True)
-        yb, wb = f.bn_relu_maxpool2d_fwd(x.cuda(), scale, shift, 3, 2, 1)
-        dx = f.maxpool2d_bwd(dy, None, tuple(x.shape), 3, 2, 1, window_idx=widx)
+        y, idx, widx = f.maxpool2d_fwd(x.cuda(), 3, 2, pad, return_window_idx=True)
+        yb, wb = f.bn_relu_maxpool2d_fwd(x.cuda(), scale, shift, 3, 2, pad)
+        dx = f.maxpool2d_bwd(dy, None, tuple(x.shape), 3, 2, pad, window_idx=widx)
         out[mode] = (y, idx, widx, yb, wb, dx)
     for name, a, b in zip(("y", "idx", "widx", "y_bn", "widx_bn", "dx"), out["0"], out["1"]):
         if a.dtype == torch.bfloat16:   # bit for bit, except that a NaN may carry a different payload
@@ -165,7 +167,7 @@ def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, monkey
             a, b = torch.nan_to_num(a.float(), nan=0.0), torch.nan_to_num(b.float(), nan=0.0)
             a, b = a.view(torch.int32), b.view(torch.int32)
         assert torch.equal(a, b), name
-    ref, ridx = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, 1, return_indices=True)
+    ref, ridx = F.max_pool2d(x.float().permute(0, 3, 1, 2), 3, 2, pad, return_indices=True)
     assert torch.equal(out["1"][1].cpu().long(), ridx.permute(0, 2, 3, 1))
 
 
