@@ -93,6 +93,16 @@ int rnn_conv2d_fprop_bn_stats_bf16(const rnn_conv_desc* d, const void* x, const 
 /* autograd of Conv2d w.r.t. its input.  accumulate != 0: dx += result. */
 int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
                           cudaStream_t stream);
+/* F.relu(Conv2d(x)) with the ReLU's backward moved into the CONSUMER's dgrad (a chain conv -> relu -> conv, as in
+ * VGG / AlexNet; torch.nn.Conv2d + F.relu semantics, no counterpart kernel in the reference):
+ *   fprop_relu_mask: y = relu(conv(x, w) + shift) and mask[N,P,Q,K/8] (bit k&7 of byte k>>3 = y > 0); K % 64 == 0.
+ *   dgrad_masked   : dx = conv_transpose(dy, w) where the mask bit of that element is set, else 0 (mask: [N,H,W,C/8]
+ *                    of the tensor this convolution consumed); unit stride, C % 64 == 0.
+ * The producer's backward then needs no pass over its output (its incoming gradient is already masked). */
+int rnn_conv2d_fprop_relu_mask_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* shift,
+                                    unsigned char* mask_out, cudaStream_t stream);
+int rnn_conv2d_dgrad_masked_bf16(const rnn_conv_desc* d, const void* dy, const void* w, const unsigned char* mask,
+                                 void* dx, cudaStream_t stream);
 /* autograd of Conv2d w.r.t. its weight; dw is bf16 [K,R,S,C] (fp32 when dw_f32 != 0). */
 size_t rnn_conv2d_wgrad_workspace(const rnn_conv_desc* d);
 int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy, void* dw, int dw_f32,
@@ -107,6 +117,9 @@ int rnn_conv2d_wgrad_bf16(const rnn_conv_desc* d, const void* x, const void* dy,
 int rnn_conv2d_first_geometry(const rnn_conv_desc* d, int* Hp, int* Wp, int* SG);
 int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
                                 const float* scale, const float* shift, int relu, cudaStream_t stream);
+/* first layer + 1-bit ReLU mask, as rnn_conv2d_fprop_relu_mask_bf16 (K % 64 == 0) */
+int rnn_conv2d_first_fprop_relu_mask_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                                          const float* shift, unsigned char* mask_out, cudaStream_t stream);
 size_t rnn_conv2d_first_wgrad_workspace(const rnn_conv_desc* d);
 int rnn_conv2d_first_wgrad_bf16(const rnn_conv_desc* d, const void* x_packed, const void* dy, void* dw_packed,
                                 int dw_f32, void* ws, size_t ws_bytes, cudaStream_t stream);
@@ -233,6 +246,12 @@ int rnn_bn_relu_maxpool2d_fwd(const void* x, const float* scale, const float* sh
                               int pw, int is_f32, cudaStream_t stream);
 int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
                       int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream);
+/* max_pool2d backward through a ReLU in front of the pool (autograd of max_pool2d(relu(.)) w.r.t. the ReLU's input,
+ * given the POOLED output y): a window's gradient lands on its argmax element, whose value is the pooled value, so
+ * the ReLU mask is (y > 0) per window -- dx = scatter(dy * (y > 0)).  Same index arguments as rnn_maxpool2d_bwd. */
+int rnn_maxpool2d_relu_bwd(const void* dy, const void* y, const int* indices, const unsigned char* window_idx, void* dx,
+                           int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32,
+                           cudaStream_t stream);
 /* torch.nn.AvgPool2d (count_include_pad=True, ceil_mode=False). */
 int rnn_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
                       int is_f32, cudaStream_t stream);

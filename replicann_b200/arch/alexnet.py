@@ -6,7 +6,7 @@ from __future__ import annotations
 import torch.nn as nn
 from torch import Tensor
 
-from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d
+from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d, fuse_relu_conv, fuse_relu_pool
 from ._stem import prepare_input
 
 
@@ -23,6 +23,10 @@ class AlexNet(nn.Module):
         self._conv4 = Conv2d(384, 256, 3, 1, 1, relu=True)
         self._conv5 = Conv2d(256, 256, 3, 1, 1, relu=True)
         self._pool5 = MaxPool2d(3, 2)
+        for conv, pool in ((self._conv1, self._pool1), (self._conv2, self._pool2), (self._conv5, self._pool5)):
+            fuse_relu_pool(conv, pool)                     # ReLU backward on the pooled-size gradient
+        fuse_relu_conv(self._conv3, self._conv4)           # ReLU backward in the next layer's dgrad epilogue
+        fuse_relu_conv(self._conv4, self._conv5)
         self._avgpool = AdaptiveAvgPool2d((6, 6))
         self._flatten = Flatten()
         self._drop1 = Dropout(p_dropout)

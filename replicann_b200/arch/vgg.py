@@ -5,7 +5,7 @@ from __future__ import annotations
 import torch.nn as nn
 from torch import Tensor
 
-from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d
+from ..nn.layers import AdaptiveAvgPool2d, Conv2d, Dropout, Flatten, Linear, MaxPool2d, fuse_relu_conv, fuse_relu_pool
 from ._stem import prepare_input
 
 _CFG_D = (64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M")
@@ -20,8 +20,12 @@ class VGG(nn.Module):
         for v in cfg:
             if v == "M":
                 feats.append(MaxPool2d(2, 2))
+                if len(feats) > 1 and isinstance(feats[-2], Conv2d):
+                    fuse_relu_pool(feats[-2], feats[-1])   # ReLU backward on the pooled-size gradient
             else:
                 feats.append(Conv2d(ch, v, 3, 1, 1, relu=True))
+                if len(feats) > 1 and isinstance(feats[-2], Conv2d):
+                    fuse_relu_conv(feats[-2], feats[-1])   # ReLU backward in the next layer's dgrad epilogue
                 ch = v
         self._features = nn.ModuleList(feats)
         if input_mean is not None:   # per-channel image normalisation, fused into the input layout kernel

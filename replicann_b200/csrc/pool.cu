@@ -146,7 +146,7 @@ maxpool_fwd_kernel(const T* __restrict__ x, T* __restrict__ y, int* __restrict__
 template <typename T, bool VEC, int FX>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const unsigned char* __restrict__ widx,
-                   T* __restrict__ dx, PoolGeom g, int cgs_shift) {
+                   T* __restrict__ dx, PoolGeom g, int cgs_shift, const T* __restrict__ ypool = nullptr) {
   constexpr int VW = PV<T, VEC>::W;
   // FX != 0: the window geometry is a compile-time constant (1: 3x3 stride 2 pad 1, 2: 2x2 stride 2, 3: 3x3 stride 2
   // pad 0 -- the pools of ResNet, VGG and AlexNet), which turns the divisions below into shifts
@@ -173,6 +173,12 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
       const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
       float d[VW];
       PV<T, VEC>::load(dy + o, d);
+      if (ypool) {   // ReLU backward of the pooled tensor's producer: the gradient passes where the pooled value > 0
+        float yv[VW];
+        PV<T, VEC>::load(ypool + o, yv);
+#pragma unroll
+        for (int e2 = 0; e2 < VW; ++e2) d[e2] = yv[e2] > 0.f ? d[e2] : 0.f;
+      }
       if (widx) {
         const int local = (h - (p * gsh - gph)) * gS + (w - (q * gsw - gpw));
         int l[VW];
@@ -195,7 +201,7 @@ maxpool_bwd_kernel(const T* __restrict__ dy, const int* __restrict__ idx, const 
 template <typename T, int K>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_tiled_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ widx, T* __restrict__ dx,
-                         PoolGeom g, int cgs_shift) {
+                         PoolGeom g, int cgs_shift, const T* __restrict__ ypool = nullptr) {
   constexpr int VW = PV<T, true>::W;
   const int cgs = g.C / VW;
   const int Qx = (g.W + K - 1) / K;                 // windows per row including a partial last one
@@ -211,6 +217,12 @@ maxpool_bwd_tiled_kernel(const T* __restrict__ dy, const unsigned char* __restri
     const long long o = (((long long)n * g.P + p) * g.Q + q) * g.C + cg * VW;
     PV<T, true>::load(dy + o, d);
     WIdx<VW>::load(widx + o, l);
+    if (ypool) {
+      float yv[VW];
+      PV<T, true>::load(ypool + o, yv);
+#pragma unroll
+      for (int e2 = 0; e2 < VW; ++e2) d[e2] = yv[e2] > 0.f ? d[e2] : 0.f;
+    }
   }
 #pragma unroll
   for (int r = 0; r < K; ++r)
@@ -231,7 +243,7 @@ maxpool_bwd_tiled_kernel(const T* __restrict__ dy, const unsigned char* __restri
 template <typename T>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_3x3s2_kernel(const T* __restrict__ dy, const unsigned char* __restrict__ widx, T* __restrict__ dx,
-                         PoolGeom g, int cgs_shift) {
+                         PoolGeom g, int cgs_shift, const T* __restrict__ ypool = nullptr) {
   constexpr int VW = PV<T, true>::W;
   const int cgs = g.C / VW;
   const int Qx = (g.W + 1) / 2;
@@ -252,6 +264,12 @@ maxpool_bwd_3x3s2_kernel(const T* __restrict__ dy, const unsigned char* __restri
         const long long o = (((long long)n * g.P + (p + a)) * g.Q + (q + b)) * g.C + cg * VW;
         PV<T, true>::load(dy + o, d[a][b]);
         WIdx<VW>::load(widx + o, l[a][b]);
+        if (ypool) {
+          float yv[VW];
+          PV<T, true>::load(ypool + o, yv);
+#pragma unroll
+          for (int e2 = 0; e2 < VW; ++e2) d[a][b][e2] = yv[e2] > 0.f ? d[a][b][e2] : 0.f;
+        }
       }
     }
   // position of input (2p+a, 2q+b) inside window (p+wa, q+wb): row a+1-2*wa, column b+1-2*wb (only 0..2 is inside)
@@ -414,7 +432,8 @@ __host__ __device__ inline int pool_quads(int extent, int pad) { return (extent 
 template <int PAD>
 __global__ void __launch_bounds__(256)
 maxpool_bwd_3x3s2_march_kernel(const bf16* __restrict__ dy, const unsigned char* __restrict__ widx,
-                               bf16* __restrict__ dx, PoolGeom g, int cgs_shift) {
+                               bf16* __restrict__ dx, PoolGeom g, int cgs_shift,
+                               const bf16* __restrict__ ypool = nullptr) {
   constexpr int OFF = 1 - PAD;
   const int cgs = g.C >> 3;
   const int Qx = pool_quads(g.W, PAD), Px = pool_quads(g.H, PAD);
@@ -437,6 +456,14 @@ maxpool_bwd_3x3s2_march_kernel(const bf16* __restrict__ dy, const unsigned char*
         const long long o = (((long long)n * g.P + r) * g.Q + (q + b)) * g.C + cg * 8;
         d[b] = *reinterpret_cast<const uint4*>(dy + o);
         l[b] = *reinterpret_cast<const uint2*>(widx + o);
+        if (ypool) {   // ReLU backward of the pooled tensor's producer, packed: keep the halves whose pooled value > 0
+          const uint4 yv = *reinterpret_cast<const uint4*>(ypool + o);
+          const __nv_bfloat162 z = __floats2bfloat162_rn(0.f, 0.f);
+          d[b].x &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&yv.x), z);
+          d[b].y &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&yv.y), z);
+          d[b].z &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&yv.z), z);
+          d[b].w &= __hgt2_mask(*reinterpret_cast<const __nv_bfloat162*>(&yv.w), z);
+        }
       }
     }
   };
@@ -695,8 +722,9 @@ int rnn_bn_relu_maxpool2d_fwd(const void* x, const float* scale, const float* sh
   RNN_REQUIRE(scale != nullptr && shift != nullptr, RNN_ERR_SHAPE);
   return maxpool_fwd_impl(x, y, indices, window_idx, N, H, W, C, R, S, sh, sw, ph, pw, is_f32, scale, shift, stream);
 }
-int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
-                      int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+static int maxpool_bwd_impl(const void* dy, const void* ypool, const int* indices, const unsigned char* window_idx,
+                            void* dx, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
+                            int is_f32, cudaStream_t stream) {
   RNN_REQUIRE((indices != nullptr) != (window_idx != nullptr), RNN_ERR_SHAPE);  // exactly one index source
   PoolGeom g;
   const int vw = is_f32 ? 4 : 8;
@@ -710,7 +738,7 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
   const int fx = fixed_geometry(g);
   if (!is_f32 && vec && window_idx != nullptr && fx == 2) {   // 2x2 stride 2, no padding: non-overlapping windows
     const dim3 tg(ceil_div_i((long long)((W + 1) / 2) * cgs, 256), (H + 1) / 2, N);
-    maxpool_bwd_tiled_kernel<bf16, 2><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    maxpool_bwd_tiled_kernel<bf16, 2><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
     RNN_CHECK_LAUNCH();
     return RNN_OK;
   }
@@ -718,32 +746,42 @@ int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* w
     // 3x3 stride 2, pad 1 (ResNet stem) or pad 0 (AlexNet): marching 2x2 input quads
     const int pad = fx == 1 ? 1 : 0;
     const dim3 mg(ceil_div_i((long long)pool_quads(W, pad) * cgs, 256), ceil_div_i(pool_quads(H, pad), MROWS), N);
-    if (pad) maxpool_bwd_3x3s2_march_kernel<1><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
-    else maxpool_bwd_3x3s2_march_kernel<0><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    if (pad) maxpool_bwd_3x3s2_march_kernel<1><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
+    else maxpool_bwd_3x3s2_march_kernel<0><<<mg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
     RNN_CHECK_LAUNCH();
     return RNN_OK;
   }
   if (!is_f32 && vec && window_idx != nullptr && fx == 1) {   // 3x3 stride 2 pad 1: one thread per 2x2 input quad
     const dim3 tg(ceil_div_i((long long)((W + 1) / 2) * cgs, 256), (H + 1) / 2, N);
-    maxpool_bwd_3x3s2_kernel<bf16><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_);
+    maxpool_bwd_3x3s2_kernel<bf16><<<tg, 256, 0, stream>>>((const bf16*)dy, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
     RNN_CHECK_LAUNCH();
     return RNN_OK;
   }
   if (is_f32) {
-    if (vec) maxpool_bwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
-    else maxpool_bwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_);
+    if (vec) maxpool_bwd_kernel<float, true, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_, (const float*)ypool);
+    else maxpool_bwd_kernel<float, false, 0><<<grid, 256, 0, stream>>>((const float*)dy, indices, window_idx, (float*)dx, g, sh_, (const float*)ypool);
   } else if (!vec) {
-    maxpool_bwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
+    maxpool_bwd_kernel<bf16, false, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
   } else {
     switch (fx) {
-      case 1: maxpool_bwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
-      case 2: maxpool_bwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
-      case 3: maxpool_bwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_); break;
-      default: maxpool_bwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_);
+      case 1: maxpool_bwd_kernel<bf16, true, 1><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool); break;
+      case 2: maxpool_bwd_kernel<bf16, true, 2><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool); break;
+      case 3: maxpool_bwd_kernel<bf16, true, 3><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool); break;
+      default: maxpool_bwd_kernel<bf16, true, 0><<<grid, 256, 0, stream>>>((const bf16*)dy, indices, window_idx, (bf16*)dx, g, sh_, (const bf16*)ypool);
     }
   }
   RNN_CHECK_LAUNCH();
   return RNN_OK;
+}
+int rnn_maxpool2d_bwd(const void* dy, const int* indices, const unsigned char* window_idx, void* dx, int N, int H,
+                      int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32, cudaStream_t stream) {
+  return maxpool_bwd_impl(dy, nullptr, indices, window_idx, dx, N, H, W, C, R, S, sh, sw, ph, pw, is_f32, stream);
+}
+int rnn_maxpool2d_relu_bwd(const void* dy, const void* y, const int* indices, const unsigned char* window_idx, void* dx,
+                           int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw, int is_f32,
+                           cudaStream_t stream) {
+  RNN_REQUIRE(y != nullptr, RNN_ERR_SHAPE);
+  return maxpool_bwd_impl(dy, y, indices, window_idx, dx, N, H, W, C, R, S, sh, sw, ph, pw, is_f32, stream);
 }
 int rnn_avgpool2d_fwd(const void* x, void* y, int N, int H, int W, int C, int R, int S, int sh, int sw, int ph, int pw,
                       int is_f32, cudaStream_t stream) {

@@ -55,6 +55,8 @@ struct TcParams {
   const float* scale;   // per-column scale (nullable)
   const float* shift;   // per-column shift / bias (nullable)
   const bf16* residual; // added before ReLU (nullable), same indexing as D
+  unsigned char* mask_out;       // FUSED: bit c&7 of byte [row][c>>3] = (stored value > 0)  (1-bit ReLU mask, nullable)
+  const unsigned char* mask_in;  // FUSED: D = bit ? acc : 0 -- the backward of that ReLU (nullable); N % 64 == 0
   int relu;
   int tma_store;        // epilogue writes through the third tensor map (dense row mapping only)
   int reduce_add;       // TMA stores add into D instead of overwriting it (gradient accumulation)
@@ -482,6 +484,11 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
           uint4 out[8];
           const int c_first = col_base + chunk * 64;
           const bf16* res = (FUSED && p.residual && row_ok) ? p.residual + out_row * p.ldd + c_first : nullptr;
+          // 1-bit ReLU masks: 8 bytes per row and 64-column chunk
+          uint2 mbits = make_uint2(0xffffffffu, 0xffffffffu), obits = make_uint2(0u, 0u);
+          const bool chunk_in = chunk * 64 < col_lim_local;
+          if (FUSED && p.mask_in && row_ok && chunk_in)
+            mbits = *reinterpret_cast<const uint2*>(p.mask_in + out_row * (p.ldd >> 3) + (c_first >> 3));
 #pragma unroll
           for (int g = 0; g < 8; ++g) {
             float v[8];
@@ -511,9 +518,22 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
 #pragma unroll
                 for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
               }
+              if (p.mask_in) {
+                const unsigned byte = ((g < 4 ? mbits.x : mbits.y) >> (8 * (g & 3))) & 0xffu;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) v[e] = ((byte >> e) & 1u) ? v[e] : 0.f;
+              }
+              if (p.mask_out) {
+                unsigned byte = 0;
+#pragma unroll
+                for (int e = 0; e < 8; ++e) byte |= (v[e] > 0.f ? 1u : 0u) << e;
+                if (g < 4) obits.x |= byte << (8 * g); else obits.y |= byte << (8 * (g - 4));
+              }
             }
             out[g] = pack8(v);
           }
+          if (FUSED && p.mask_out && row_ok && chunk_in)
+            *reinterpret_cast<uint2*>(p.mask_out + out_row * (p.ldd >> 3) + (c_first >> 3)) = obits;
           int valid16 = (col_lim_local - chunk * 64) / 8;
           valid16 = valid16 < 0 ? 0 : (valid16 > 8 ? 8 : valid16);
           if (p.tma_store) flush_tma(out, c_first, mblk * BM + q * 32);
@@ -905,7 +925,7 @@ int launch_inst(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p,
   }
   // wgrad and the MN-major-A GEMM (Linear wgrad) never carry a fused epilogue
   if constexpr (KIND != KIND_WGRAD && !A_MN) {
-    if (p.ws == nullptr && (p.scale || p.shift || p.residual || p.relu))
+    if (p.ws == nullptr && (p.scale || p.shift || p.residual || p.relu || p.mask_in || p.mask_out))
       return launch_inst2<BN, KIND, A_MN, B_MN, true, false, CG>(ta, tb, p, stream);
   }
   return launch_inst2<BN, KIND, A_MN, B_MN, false, false, CG>(ta, tb, p, stream);
@@ -1215,7 +1235,7 @@ static int check_conv_desc(const rnn_conv_desc* d) {
 
 static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* scale,
                            const float* shift, const void* residual, int relu, float* stat_partials, int* stat_rows,
-                           cudaStream_t stream) {
+                           cudaStream_t stream, unsigned char* mask_out = nullptr) {
   int rc = check_conv_desc(d);
   if (rc != RNN_OK) return rc;
   rc = load_driver_entry_points();
@@ -1247,6 +1267,7 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = -d->pad_w; p.lo_h = -d->pad_h;
   p.ldd = d->K;
   p.D = y; p.scale = scale; p.shift = shift; p.residual = reinterpret_cast<const bf16*>(residual); p.relu = relu;
+  p.mask_out = mask_out;
   if (stat_partials != nullptr) {
     RNN_REQUIRE(d->K % BN == 0, RNN_ERR_SHAPE);  // statistics need whole N tiles
     RNN_REQUIRE(p.n_nblk <= rnn_num_sms() / 2, RNN_ERR_SHAPE);
@@ -1260,6 +1281,14 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
       t.ow = (int16_t)s; t.oh = (int16_t)r; t.bcol = (r * d->S + s) * d->C;
     }
   return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);
+}
+
+// y = relu(conv(x, w) + shift) and the 1-bit mask (y > 0) the backward pass needs: [N,P,Q,K/8] bytes, bit k&7 of byte
+// k>>3.  The consumer's dgrad applies it (rnn_conv2d_dgrad_masked_bf16) in place of a ReLU backward pass over y.
+int rnn_conv2d_fprop_relu_mask_bf16(const rnn_conv_desc* d, const void* x, const void* w, void* y, const float* shift,
+                                    unsigned char* mask_out, cudaStream_t stream) {
+  RNN_REQUIRE(d != nullptr && mask_out != nullptr && d->K % 64 == 0, RNN_ERR_SHAPE);
+  return conv_fprop_impl(d, x, w, y, nullptr, shift, nullptr, 1, nullptr, nullptr, stream, mask_out);
 }
 
 // y[N,P,Q,K] = conv(x[N,H,W,C], w[K,R,S,C]); optional per-channel scale/shift, residual add, ReLU.
@@ -1299,8 +1328,22 @@ int rnn_conv2d_fprop_bn_stats_bf16(const rnn_conv_desc* d, const void* x, const 
 // dx[N,H,W,C] = conv_transpose(dy[N,P,Q,K], w[K,R,S,C]).  Strided convolutions are decomposed
 // into stride_h*stride_w parity classes, each a unit-stride gather over dy with a subset of taps.
 // `accumulate` != 0 adds into the existing dx (gradient of a tensor consumed by two branches).
+static int conv_dgrad_impl(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
+                           const void* relu_mask, cudaStream_t stream);
 int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
                           cudaStream_t stream) {
+  return conv_dgrad_impl(d, dy, w, dx, accumulate, nullptr, stream);
+}
+// dx = conv_transpose(dy, w) masked by the 1-bit ReLU mask of the tensor x this convolution consumed ([N,H,W,C/8]
+// bytes, from rnn_conv2d_fprop_relu_mask_bf16 of the producing layer): the producer's ReLU backward in this epilogue
+// instead of a separate pass that reads dx and x and writes dx.  Unit stride, C % 64 == 0.
+int rnn_conv2d_dgrad_masked_bf16(const rnn_conv_desc* d, const void* dy, const void* w, const unsigned char* mask,
+                                 void* dx, cudaStream_t stream) {
+  RNN_REQUIRE(d != nullptr && mask != nullptr && d->stride_h == 1 && d->stride_w == 1 && d->C % 64 == 0, RNN_ERR_SHAPE);
+  return conv_dgrad_impl(d, dy, w, dx, 0, mask, stream);
+}
+static int conv_dgrad_impl(const rnn_conv_desc* d, const void* dy, const void* w, void* dx, int accumulate,
+                           const void* relu_mask, cudaStream_t stream) {
   int rc = check_conv_desc(d);
   if (rc != RNN_OK) return rc;
   RNN_REQUIRE(d->K % 64 == 0 && d->C % 8 == 0, RNN_ERR_SHAPE);
@@ -1367,7 +1410,8 @@ int rnn_conv2d_dgrad_bf16(const rnn_conv_desc* d, const void* dy, const void* w,
       p.D = dx;
       // accumulation: dense outputs add through the TMA reduce-store (bf16 add at the destination, the same
       // rounding as adding two bf16 gradient tensors); scattered (strided) outputs read-modify-write per thread
-      if (accumulate && !p.pix_map) p.reduce_add = 1;
+      if (relu_mask != nullptr) p.mask_in = reinterpret_cast<const unsigned char*>(relu_mask);
+      else if (accumulate && !p.pix_map) p.reduce_add = 1;
       else p.residual = accumulate ? reinterpret_cast<const bf16*>(dx) : nullptr;
       for (int i = 0; i < nh; ++i)
         for (int j = 0; j < nw; ++j) {
@@ -1487,8 +1531,22 @@ int rnn_conv2d_first_geometry(const rnn_conv_desc* d, int* Hp, int* Wp, int* SG)
   return RNN_OK;
 }
 
+static int first_fprop_impl(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                            const float* scale, const float* shift, int relu, unsigned char* mask_out,
+                            cudaStream_t stream);
 int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
                                 const float* scale, const float* shift, int relu, cudaStream_t stream) {
+  return first_fprop_impl(d, x_packed, w_packed, y, scale, shift, relu, nullptr, stream);
+}
+// first layer with the 1-bit ReLU mask as in rnn_conv2d_fprop_relu_mask_bf16
+int rnn_conv2d_first_fprop_relu_mask_bf16(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                                          const float* shift, unsigned char* mask_out, cudaStream_t stream) {
+  RNN_REQUIRE(d != nullptr && mask_out != nullptr && d->K % 64 == 0, RNN_ERR_SHAPE);
+  return first_fprop_impl(d, x_packed, w_packed, y, nullptr, shift, 1, mask_out, stream);
+}
+static int first_fprop_impl(const rnn_conv_desc* d, const void* x_packed, const void* w_packed, void* y,
+                            const float* scale, const float* shift, int relu, unsigned char* mask_out,
+                            cudaStream_t stream) {
   FirstGeom g;
   int rc = first_geom(d, &g);
   if (rc != RNN_OK) return rc;
@@ -1512,7 +1570,7 @@ int rnn_conv2d_first_fprop_bf16(const rnn_conv_desc* d, const void* x_packed, co
   p.Wo = d->Q; p.HoWo = d->P * d->Q;
   p.ts_w = d->stride_w; p.ts_h = d->stride_h; p.lo_w = 0; p.lo_h = 0;
   p.ldd = d->K;
-  p.D = y; p.scale = scale; p.shift = shift; p.relu = relu;
+  p.D = y; p.scale = scale; p.shift = shift; p.relu = relu; p.mask_out = mask_out;
   p.no_b_resident = 1;   // 338 -> 362 us in-step with the filter resident: the 7 K steps of a tile are epilogue-bound
   first_taps(d, g, &p);
   return launch_bn<KIND_CONV, false, false>(BN, ta, tb, p, stream);

@@ -238,6 +238,21 @@ def conv2d_fprop(x, w, *, stride=1, pad=0, scale=None, shift=None, residual=None
     return y
 
 
+def conv2d_fprop_relu_mask(x, w, *, stride=1, pad=0, shift=None):
+    """y = relu(conv(x, w) + shift) and the 1-bit mask (y > 0), [N,P,Q,K/8] uint8, that the consumer's
+    conv2d_dgrad(relu_mask=...) applies in place of a ReLU backward pass.  K % 64 == 0."""
+    lib = _lib.load()
+    _req(x, torch.bfloat16, "x")
+    _req(w, torch.bfloat16, "w")
+    d = _cdesc(x.shape, w.shape, stride, pad)
+    y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x.device)
+    mask = torch.empty((d.N, d.P, d.Q, d.K // 8), dtype=torch.uint8, device=x.device)
+    with _span("tc_conv_fprop", _conv_flops(d), _conv_tag(d)):
+        check(lib.rnn_conv2d_fprop_relu_mask_bf16(d, ptr(x), ptr(w), ptr(y), ptr(shift), ptr(mask), cur_stream()),
+              "rnn_conv2d_fprop_relu_mask_bf16")
+    return y, mask
+
+
 def conv2d_fprop_bn_stats(x, w, gamma, beta, eps, momentum, running_mean, running_var, *, stride=1, pad=0):
     """Convolution whose epilogue also produces the BatchNorm batch statistics of its output.
     Returns (y, mean, invstd, scale, shift); updates the running statistics in place."""
@@ -289,10 +304,18 @@ def pack_first_input(x_nchw_f32, d, mean=None, inv_std=None):
     return y
 
 
-def first_conv_fprop(x_packed, w_packed, d, *, scale=None, shift=None, relu=False):
+def first_conv_fprop(x_packed, w_packed, d, *, scale=None, shift=None, relu=False, relu_mask=False):
+    """relu_mask=True: y = relu(conv + shift) and the 1-bit mask (see conv2d_fprop_relu_mask); returns (y, mask)."""
     lib = _lib.load()
     _req(x_packed, torch.bfloat16, "x_packed"); _req(w_packed, torch.bfloat16, "w_packed")
     y = torch.empty((d.N, d.P, d.Q, d.K), dtype=torch.bfloat16, device=x_packed.device)
+    if relu_mask:
+        mask = torch.empty((d.N, d.P, d.Q, d.K // 8), dtype=torch.uint8, device=x_packed.device)
+        with _span("tc_conv_fprop", _conv_flops(d), "first " + _conv_tag(d)):
+            check(lib.rnn_conv2d_first_fprop_relu_mask_bf16(d, ptr(x_packed), ptr(w_packed), ptr(y), ptr(shift),
+                                                            ptr(mask), cur_stream()),
+                  "rnn_conv2d_first_fprop_relu_mask_bf16")
+        return y, mask
     with _span("tc_conv_fprop", _conv_flops(d), "first " + _conv_tag(d)):
         check(lib.rnn_conv2d_first_fprop_bf16(d, ptr(x_packed), ptr(w_packed), ptr(y), ptr(scale), ptr(shift), int(relu),
                                               cur_stream()), "rnn_conv2d_first_fprop_bf16")
@@ -311,7 +334,9 @@ def first_conv_wgrad(x_packed, dy, d, sg, *, out_dtype=torch.bfloat16):
     return dw
 
 
-def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False):
+def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False, relu_mask=None):
+    """relu_mask: the 1-bit mask of the ReLU that produced this convolution's input (conv2d_fprop_relu_mask of the
+    layer before); its backward is applied in the epilogue (unit stride, no accumulation, C % 64 == 0)."""
     lib = _lib.load()
     _req(dy, torch.bfloat16, "dy")
     _req(w, torch.bfloat16, "w")
@@ -320,8 +345,15 @@ def conv2d_dgrad(dy, w, x_shape, *, stride=1, pad=0, out=None, accumulate=False)
         raise ValueError(f"dy shape {tuple(dy.shape)} != {(d.N, d.P, d.Q, d.K)}")
     dx = out if out is not None else torch.empty(tuple(x_shape), dtype=torch.bfloat16, device=dy.device)
     with _span("tc_conv_dgrad", _conv_flops(d), _conv_tag(d)):
-        check(lib.rnn_conv2d_dgrad_bf16(d, ptr(dy), ptr(w), ptr(dx), int(accumulate), cur_stream()),
-              "rnn_conv2d_dgrad_bf16")
+        if relu_mask is not None:
+            _req(relu_mask, torch.uint8, "relu_mask"); _contig(relu_mask, "relu_mask")
+            if accumulate or tuple(relu_mask.shape) != (d.N, d.H, d.W, d.C // 8):
+                raise ValueError("relu_mask: [N,H,W,C/8] of the input, no accumulation")
+            check(lib.rnn_conv2d_dgrad_masked_bf16(d, ptr(dy), ptr(w), ptr(relu_mask), ptr(dx), cur_stream()),
+                  "rnn_conv2d_dgrad_masked_bf16")
+        else:
+            check(lib.rnn_conv2d_dgrad_bf16(d, ptr(dy), ptr(w), ptr(dx), int(accumulate), cur_stream()),
+                  "rnn_conv2d_dgrad_bf16")
     return dx
 
 
@@ -659,7 +691,9 @@ def bn_relu_maxpool2d_fwd(x, scale, shift, k, s, p):
     return y, widx
 
 
-def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None):
+def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None, relu_y=None):
+    """relu_y: the pooled output when the pool's input came from a ReLU whose backward is applied here (dy is masked
+    by relu_y > 0 inside the kernel)."""
     lib = _lib.load(); _cuda(dy); _contig(dy, "dy")
     N, H, W, Cn = x_shape
     kh, kw = (k, k) if isinstance(k, int) else k
@@ -667,8 +701,16 @@ def maxpool2d_bwd(dy, idx, x_shape, k, s, p, window_idx=None):
     ph, pw = (p, p) if isinstance(p, int) else p
     dx = torch.empty(tuple(x_shape), dtype=dy.dtype, device=dy.device)
     with _span('maxpool', float(2 * dy.numel() + dx.numel()) * dy.element_size(), f"bwd {tuple(x_shape)} k{kh} s{sh}"):
-        check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx) if window_idx is None else None, ptr(window_idx), ptr(dx), N, H, W,
-                                    Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()), "rnn_maxpool2d_bwd")
+        if relu_y is not None:
+            _contig(relu_y, "relu_y")
+            if relu_y.shape != dy.shape or relu_y.dtype != dy.dtype:
+                raise ValueError("relu_y: the pooled output, same shape and dtype as dy")
+            check(lib.rnn_maxpool2d_relu_bwd(ptr(dy), ptr(relu_y), ptr(idx) if window_idx is None else None,
+                                             ptr(window_idx), ptr(dx), N, H, W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy),
+                                             cur_stream()), "rnn_maxpool2d_relu_bwd")
+        else:
+            check(lib.rnn_maxpool2d_bwd(ptr(dy), ptr(idx) if window_idx is None else None, ptr(window_idx), ptr(dx), N, H,
+                                        W, Cn, kh, kw, sh, sw, ph, pw, _is_f32(dy), cur_stream()), "rnn_maxpool2d_bwd")
     return dx
 
 

@@ -74,25 +74,41 @@ def _write_param_grad(p, compute):
 
 # ------------------------------------------------------------------------------------------ Conv2d
 class Conv2dFn(Function):
-    """y = [relu](conv2d(x, w) + bias)."""
+    """y = [relu](conv2d(x, w) + bias).
+
+    Two ways of moving the fused ReLU's backward out of this node (both declared by the model, see
+    nn.layers.fuse_relu_pool / fuse_relu_conv; without them the backward pass masks dy itself):
+      premasked: the only consumer of y is a pooling layer that masks the gradient at the pooled resolution;
+      emit_mask: the only consumer is a unit-stride convolution -- the forward also returns the 1-bit mask (y > 0),
+                 which that convolution receives as `in_mask` and applies in the epilogue of its dgrad kernel.
+    Either way this node's incoming gradient is already masked and the bias gradient is a plain column sum."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu=False):
+    def forward(ctx, x, weight, bias, stride, pad, relu=False, premasked=False, in_mask=None, emit_mask=False):
         xh = nhwc(x)
         wk = nhwc(weight)  # [K,C,R,S] channels_last -> KRSC
-        ctx.stride, ctx.pad, ctx.relu = stride, pad, relu
+        ctx.stride, ctx.pad = stride, pad
+        ctx.relu = relu and not premasked and not emit_mask
+        mask = None
         if weight.dtype == torch.float32:
+            if in_mask is not None or emit_mask:
+                raise RuntimeError("1-bit ReLU masks are a bf16-path feature")
             y = RF.conv2d_fprop_f32(xh, wk, bias.detach() if bias is not None else None, stride=stride, pad=pad)
             if relu:
                 y = RF.relu_fwd(y)
+        elif emit_mask:
+            y, mask = RF.conv2d_fprop_relu_mask(xh, wk, stride=stride, pad=pad, shift=_bias_f32(bias))
         else:
             y = RF.conv2d_fprop(xh, wk, stride=stride, pad=pad, shift=_bias_f32(bias), relu=relu)
-        ctx.save_for_backward(xh, weight, bias, y if relu else None)
+        ctx.save_for_backward(xh, weight, bias, y if ctx.relu else None, in_mask)
+        if emit_mask:
+            ctx.mark_non_differentiable(mask)
+            return nchw(y), mask
         return nchw(y)
 
     @staticmethod
-    def backward(ctx, dy):
-        xh, weight, bias, y = ctx.saved_tensors
+    def backward(ctx, dy, *_):
+        xh, weight, bias, y, in_mask = ctx.saved_tensors
         wk = nhwc(weight)
         dyh = nhwc(dy)
         stride, pad = ctx.stride, ctx.pad
@@ -122,8 +138,8 @@ class Conv2dFn(Function):
             if f32:
                 dx = nchw(RF.conv2d_dgrad_f32(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
             else:
-                dx = nchw(RF.conv2d_dgrad(dyh, wk, tuple(xh.shape), stride=stride, pad=pad))
-        return dx, dw, db, None, None, None
+                dx = nchw(RF.conv2d_dgrad(dyh, wk, tuple(xh.shape), stride=stride, pad=pad, relu_mask=in_mask))
+        return dx, dw, db, None, None, None, None, None, None
 
 
 class PadFilterFn(Function):
@@ -149,7 +165,7 @@ class FirstConv2dFn(Function):
     gradient is produced (images do not require grad)."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias, stride, pad, relu, norm=None):
+    def forward(ctx, x, weight, bias, stride, pad, relu, norm=None, premasked=False, emit_mask=False):
         from .._lib import conv_desc
         N, Cn, H, W = x.shape
         K, _, R, S = weight.shape
@@ -160,13 +176,20 @@ class FirstConv2dFn(Function):
         # filter [K,C,R,S] -> [K,R,SG*8 taps,8 ch] with zeros beyond S and C (tiny; data movement only)
         wp = torch.zeros((K, R, sg * 8, 8), dtype=weight.dtype, device=weight.device)
         wp[:, :, :S, :Cn].copy_(weight.detach().permute(0, 2, 3, 1))
-        y = RF.first_conv_fprop(xp, wp.reshape(K, R, sg, 64), d, shift=_bias_f32(bias), relu=relu)
-        ctx.d, ctx.sg, ctx.relu = d, sg, relu
-        ctx.save_for_backward(xp, weight, bias, y if relu else None)
+        mask = None
+        if emit_mask:
+            y, mask = RF.first_conv_fprop(xp, wp.reshape(K, R, sg, 64), d, shift=_bias_f32(bias), relu_mask=True)
+        else:
+            y = RF.first_conv_fprop(xp, wp.reshape(K, R, sg, 64), d, shift=_bias_f32(bias), relu=relu)
+        ctx.d, ctx.sg, ctx.relu = d, sg, relu and not premasked and not emit_mask   # see Conv2dFn
+        ctx.save_for_backward(xp, weight, bias, y if ctx.relu else None)
+        if emit_mask:
+            ctx.mark_non_differentiable(mask)
+            return nchw(y), mask
         return nchw(y)
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_):
         xp, weight, bias, y = ctx.saved_tensors
         d, sg = ctx.d, ctx.sg
         dyh = nhwc(dy)
@@ -191,7 +214,7 @@ class FirstConv2dFn(Function):
         if want_db:
             K = dyh.shape[-1]
             db = _write_param_grad(bias, lambda out, acc: RF.colsum(dyh.reshape(-1, K), out=out, accumulate=acc))
-        return None, dw, db, None, None, None, None
+        return None, dw, db, None, None, None, None, None, None
 
 
 def nhwc_param_view(g: torch.Tensor) -> torch.Tensor:
@@ -526,11 +549,14 @@ class MaxPool2dFn(Function):
     uses the 1-byte in-window argmax."""
 
     @staticmethod
-    def forward(ctx, x, k, s, p, want_indices):
+    def forward(ctx, x, k, s, p, want_indices, relu_input=False):
+        # relu_input: x is the output of a ReLU whose backward is left to this layer.  A window's gradient goes to its
+        # argmax element, whose value IS the pooled value, so "x > 0 there" == "y > 0": the ReLU mask is applied to dy
+        # at the pooled resolution (1/4 .. 1/2.25 of the elements) instead of in a pass over the full-size tensor.
         xh = nhwc(x)
         y, idx, widx = RF.maxpool2d_fwd(xh, k, s, p, return_indices=want_indices, return_window_idx=True)
         ctx.cfg = (tuple(xh.shape), k, s, p)
-        ctx.save_for_backward(widx)
+        ctx.save_for_backward(widx, y if relu_input else None)
         if idx is None:
             idx = torch.empty(0, dtype=torch.int32, device=x.device)
             ctx.mark_non_differentiable(idx)
@@ -540,9 +566,10 @@ class MaxPool2dFn(Function):
 
     @staticmethod
     def backward(ctx, dy, _didx):
-        (widx,) = ctx.saved_tensors
+        widx, y = ctx.saved_tensors
         shape, k, s, p = ctx.cfg
-        return nchw(RF.maxpool2d_bwd(nhwc(dy), None, shape, k, s, p, window_idx=widx)), None, None, None, None
+        return (nchw(RF.maxpool2d_bwd(nhwc(dy), None, shape, k, s, p, window_idx=widx, relu_y=y)),
+                None, None, None, None, None)
 
 
 class BnReluMaxPoolFn(Function):

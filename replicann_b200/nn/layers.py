@@ -10,6 +10,7 @@ options, read-only properties.
 from __future__ import annotations
 
 import math
+import os
 
 import torch
 import torch.nn as nn
@@ -36,6 +37,8 @@ class Conv2d(nn.Module):
         sh, sw = _pair(stride)
         ph, pw = _pair(padding)
         self._stride, self._padding, self._kernel, self._relu = (sh, sw), (ph, pw), (kh, kw), relu
+        self._grad_premasked = False     # see fuse_relu_pool()
+        self._emit_relu_mask = False     # see fuse_relu_conv()
         w = torch.empty((out_channels, in_channels, kh, kw), device=device, dtype=dtype)
         w = w.contiguous(memory_format=torch.channels_last)
         self.weight = nn.Parameter(w)
@@ -102,7 +105,13 @@ class Conv2d(nn.Module):
                 and x.shape[1] == self.in_channels and not x.requires_grad):
             # network input: fp32 NCHW images straight into the packed-pixel first-layer kernels
             norm = (self._in_mean, self._in_inv_std) if self._in_mean is not None else None
-            return Fn.FirstConv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu, norm)
+            emit = self._emit_relu_mask and self._relu and self.out_channels % 64 == 0
+            out = Fn.FirstConv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu, norm,
+                                         self._grad_premasked, emit)
+            if emit:
+                out[0]._relu_mask = out[1]
+                return out[0]
+            return out
         if self._in_mean is not None:
             raise RuntimeError("input normalisation is fused into the fp32-image first-layer path only; "
                                "this input does not take it (normalise it upstream)")
@@ -112,7 +121,17 @@ class Conv2d(nn.Module):
                 w = Fn.PadFilterFn.apply(w, x.shape[1])
             else:
                 raise ValueError(f"expected {self.in_channels} input channels, got {x.shape[1]}")
-        return Fn.Conv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu)
+        in_mask = getattr(x, "_relu_mask", None)      # attached by the producing layer, see fuse_relu_conv()
+        if in_mask is not None and (self._stride != (1, 1) or w.dtype != torch.bfloat16 or w is not self.weight):
+            raise RuntimeError("fuse_relu_conv: the consumer must be a unit-stride bf16 convolution")
+        emit = self._emit_relu_mask and w.dtype == torch.bfloat16 and self.out_channels % 64 == 0
+        out = Fn.Conv2dFn.apply(x, w, self.bias, self._stride, self._padding, self._relu, self._grad_premasked,
+                                in_mask, emit)
+        if emit:
+            y, mask = out
+            y._relu_mask = mask
+            return y
+        return out
 
     def extra_repr(self) -> str:
         return (f"{self.in_channels}, {self.out_channels}, kernel_size={self._kernel}, stride={self._stride}, "
@@ -292,12 +311,48 @@ class MaxPool2d(nn.Module):
         self._s = _pair(stride) if stride is not None else self._k
         self._p = _pair(padding)
         self._return_indices = return_indices
+        self._relu_input = False         # see fuse_relu_pool()
 
     def forward(self, x: Tensor, /):
-        y, idx = Fn.MaxPool2dFn.apply(x, self._k, self._s, self._p, self._return_indices)
+        y, idx = Fn.MaxPool2dFn.apply(x, self._k, self._s, self._p, self._return_indices, self._relu_input)
         if self._return_indices:
             return y, idx.long()
         return y
+
+
+# RNN_FUSE_RELU=0: fuse_relu_pool / fuse_relu_conv declarations are ignored (A/B timing, bit-identity tests)
+_FUSE_RELU = os.environ.get("RNN_FUSE_RELU", "1") != "0"
+
+
+def fuse_relu_pool(conv: "Conv2d", pool: MaxPool2d) -> None:
+    """Declare that `pool` is the ONLY consumer of `conv`'s (ReLU-fused) output.  The ReLU backward then runs inside
+    the pooling layer's backward on the pooled-size gradient (a window's gradient lands on its argmax element, whose
+    value is the pooled value, so the mask `conv_out > 0` at that element equals `pool_out > 0`), and the convolution's
+    backward skips its full-size mask pass: its bias gradient becomes a plain column sum (one read of dy instead of
+    two reads and a write).  Results are bit-identical to the unfused pair."""
+    if not isinstance(conv, Conv2d) or not isinstance(pool, MaxPool2d):
+        raise TypeError("fuse_relu_pool(Conv2d, MaxPool2d)")
+    if not conv._relu:
+        raise ValueError("the convolution has no fused ReLU")
+    if _FUSE_RELU:
+        conv._grad_premasked = True
+        pool._relu_input = True
+
+
+def fuse_relu_conv(conv: "Conv2d", nxt: "Conv2d") -> None:
+    """Declare that `nxt` (unit stride) is the ONLY consumer of `conv`'s (ReLU-fused) output and receives it directly.
+    `conv`'s forward then also writes the 1-bit mask (y > 0) from its epilogue and hands it over on the output tensor;
+    `nxt` applies it to its input gradient in the epilogue of its dgrad kernel, and `conv`'s backward skips the
+    full-size mask pass (its bias gradient becomes a plain column sum).  Bit-identical to the unfused pair.  Takes
+    effect for bf16 weights with out_channels % 64 == 0; otherwise the layers run unfused."""
+    if not isinstance(conv, Conv2d) or not isinstance(nxt, Conv2d):
+        raise TypeError("fuse_relu_conv(Conv2d, Conv2d)")
+    if not conv._relu:
+        raise ValueError("the convolution has no fused ReLU")
+    if nxt._stride != (1, 1):
+        raise ValueError("the consumer must have unit stride")
+    if _FUSE_RELU:
+        conv._emit_relu_mask = True
 
 
 class AvgPool2d(nn.Module):

@@ -171,6 +171,29 @@ def test_maxpool_3x3s2_marching_kernels_match_the_row_kernels(N, H, W, C, pad, m
     assert torch.equal(out["1"][1].cpu().long(), ridx.permute(0, 2, 3, 1))
 
 
+@pytest.mark.parametrize("march", ["1", "0"])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("N,H,W,C,k,s,p", [(2, 28, 28, 64, 2, 2, 0), (2, 27, 27, 64, 3, 2, 0), (2, 30, 18, 16, 3, 2, 1),
+                                            (1, 9, 7, 12, 2, 2, 0), (2, 12, 12, 6, 3, 1, 1)])
+def test_maxpool_backward_with_the_relu_mask_of_the_pooled_output(dtype, N, H, W, C, k, s, p, march, monkeypatch):
+    """rnn_maxpool2d_relu_bwd: max_pool2d backward with the ReLU in front of the pool folded in (mask = pooled y > 0)
+    against relu_bwd at the pooled size followed by the plain kernel -- bit for bit, every kernel variant."""
+    monkeypatch.setenv("RNN_POOL_MARCH", march)
+    f = RF()
+    x = torch.relu(rnd((N, H, W, C), 7, dtype)).cuda()           # a ReLU output: many exact zeros
+    y, _, widx = f.maxpool2d_fwd(x, k, s, p, return_indices=False, return_window_idx=True)
+    dy = rnd(tuple(y.shape), 8, dtype).cuda()
+    ref = f.maxpool2d_bwd(f.relu_bwd(dy, y), None, tuple(x.shape), k, s, p, window_idx=widx)
+    got = f.maxpool2d_bwd(dy, None, tuple(x.shape), k, s, p, window_idx=widx, relu_y=y)
+    assert torch.equal(got, ref)
+    # and it is the gradient of max_pool2d(relu(.)) at a pre-activation whose ReLU is x
+    pre = x.float().cpu().clone()
+    pre[pre == 0] = -1.0
+    pre = pre.permute(0, 3, 1, 2).requires_grad_(True)
+    F.max_pool2d(torch.relu(pre), k, s, p).backward(dy.float().cpu().permute(0, 3, 1, 2))
+    assert rel_err(got, pre.grad.permute(0, 2, 3, 1)) < (1e-6 if dtype == torch.float32 else 1e-2)
+
+
 def test_maxpool_nan_propagates():
     f = RF()
     x = rnd((1, 4, 4, 8), 1)

@@ -280,3 +280,37 @@ def test_fused_stem_pool_is_bit_identical_to_the_two_modules():
         assert torch.equal(res[True][2][k], res[False][2][k]), k
     for n in res[True][1]:
         assert torch.equal(res[True][1][n], res[False][1][n]), n
+
+
+def test_relu_backward_at_the_pooled_resolution_is_bit_identical():
+    """fuse_relu_pool(conv, pool): the convolution's ReLU backward runs inside the pooling layer's backward on the
+    pooled-size gradient and the convolution skips its full-size mask pass; fuse_relu_conv(conv, next): it runs in the
+    epilogue of the next convolution's dgrad kernel.  AlexNet (overlapping 3x3/2 windows, first
+    layer included) and a VGG (2x2/2 windows): logits and every gradient bit for bit against the unfused modules."""
+    from replicann_b200.arch.alexnet import AlexNet
+    from replicann_b200.arch.vgg import VGG
+    from replicann_b200.nn.layers import Conv2d, MaxPool2d
+    g = torch.Generator().manual_seed(31)
+    cases = [(lambda: AlexNet(n_classes=24, p_dropout=0.0), (4, 3, 224, 224)),
+             (lambda: VGG((64, 64, "M", 128, "M", 128, 128, "M"), n_classes=24, p_dropout=0.0, hidden_size=64), (4, 3, 56, 56))]
+    for make, shape in cases:
+        x = torch.randn(*shape, generator=g).cuda()
+        y = torch.randint(0, 24, (shape[0],), generator=g).cuda()
+        res = {}
+        for fused in (True, False):
+            torch.manual_seed(9)
+            m = make().cuda().to(torch.bfloat16)
+            n_fused = sum(int(c._grad_premasked) + int(c._emit_relu_mask) for c in m.modules() if isinstance(c, Conv2d))
+            assert n_fused >= 4
+            if not fused:
+                for c in m.modules():
+                    if isinstance(c, Conv2d):
+                        c._grad_premasked = c._emit_relu_mask = False
+                    if isinstance(c, MaxPool2d):
+                        c._relu_input = False
+            logits = m(x)
+            F.cross_entropy(logits.float(), y).backward()
+            res[fused] = (logits.detach(), {n: p.grad.clone() for n, p in m.named_parameters()})
+        assert torch.equal(res[True][0], res[False][0])
+        for n in res[True][1]:
+            assert torch.equal(res[True][1][n], res[False][1][n]), n
