@@ -41,10 +41,10 @@ else
   timeout 300 ncu --set full --clock-control none --import-source on -k regex:tc_kernel -s 3 -c 1 -f -o $O/r02_tc_c64 \
       python tools/prof_conv.py fprop 256 56 56 64 64 3 1 1 > $O/ncu_c64.log 2>&1
   timeout 100 python tools/bench_attention.py --once > /dev/null 2>&1 && \
-  timeout 300 ncu --set full --clock-control none --import-source on -k "regex:fwd_kernel|dq_kernel|dkdv_kernel" -s 3 -c 3 -f \
+  timeout 300 ncu --set full --clock-control none --import-source on -k "regex:^(fwd|dq|dkdv)_kernel" -c 6 -f \
       -o $O/r02_fa python tools/bench_attention.py --once > $O/ncu_fa.log 2>&1
   timeout 100 python tools/bench_pool.py > /dev/null 2>&1 && \
-  timeout 300 ncu --set full --clock-control none --import-source on -k "regex:maxpool_.*march" -s 2 -c 2 -f \
+  timeout 300 ncu --set full --clock-control none --import-source on -k "regex:maxpool_.*march" -s 6 -c 3 -f \
       -o $O/r02_pool python tools/bench_pool.py > $O/ncu_pool.log 2>&1
   ls -la $O | tail -15
 fi
