@@ -94,3 +94,37 @@ def test_gemm_f32_on_tensor_cores_is_fp32_accurate(M, N, K, a_mn, b_mn):
     got2 = RF.gemm_f32(a.cuda(), b.cuda(), a_mn=a_mn, b_mn=b_mn, bias=bias.cuda(), relu=True)
     err2 = (got2.cpu().double() - ref2).abs().max().item() / ref2.abs().max().item()
     assert err2 < 1e-5, err2
+
+
+@pytest.mark.parametrize("N,H,W,C,K,R,pad", [(4, 28, 28, 64, 64, 3, 1), (2, 30, 17, 128, 192, 3, 1), (3, 14, 14, 256, 256, 1, 0),
+                                             (2, 56, 56, 64, 128, 3, 1)])
+def test_relu_mask_from_the_fprop_epilogue_and_into_the_dgrad_epilogue(N, H, W, C, K, R, pad):
+    """rnn_conv2d_fprop_relu_mask_bf16 / rnn_conv2d_dgrad_masked_bf16: y is bit-identical to the ReLU-fused fprop, the
+    mask is exactly (y > 0) packed 8 channels per byte, and the masked dgrad equals dgrad followed by ReLU backward
+    (bit for bit) -- and the torch gradient of conv(relu(.)) within the bf16 tolerance."""
+    import torch
+    import torch.nn.functional as F
+    from replicann_b200 import functional as RF
+    g = torch.Generator().manual_seed(3)
+    x = torch.randn(N, H, W, C, generator=g).to(torch.bfloat16).cuda()
+    w = (torch.randn(K, R, R, C, generator=g) * 0.05).to(torch.bfloat16).cuda()
+    b = torch.randn(K, generator=g).cuda()
+    y_ref = RF.conv2d_fprop(x, w, stride=1, pad=pad, shift=b, relu=True)
+    y, mask = RF.conv2d_fprop_relu_mask(x, w, stride=1, pad=pad, shift=b)
+    assert torch.equal(y, y_ref)
+    bits = (y > 0).reshape(N, y.shape[1], y.shape[2], K // 8, 8).to(torch.int32)
+    packed = (bits * (1 << torch.arange(8, device="cuda", dtype=torch.int32))).sum(-1).to(torch.uint8)
+    assert torch.equal(mask, packed)
+    # consumer: a second convolution over y; its dgrad with the mask == dgrad then relu_bwd
+    w2 = (torch.randn(64, 3, 3, K, generator=g) * 0.05).to(torch.bfloat16).cuda()
+    dy2 = torch.randn(N, y.shape[1], y.shape[2], 64, generator=g).to(torch.bfloat16).cuda()
+    dx_plain = RF.conv2d_dgrad(dy2, w2, tuple(y.shape), stride=1, pad=1)
+    dx_ref = RF.relu_bwd(dx_plain, y)
+    dx = RF.conv2d_dgrad(dy2, w2, tuple(y.shape), stride=1, pad=1, relu_mask=mask)
+    assert torch.equal(dx, dx_ref)
+    pre = torch.where(y > 0, y.float(), torch.full_like(y.float(), -1.0)).cpu().permute(0, 3, 1, 2).requires_grad_(True)
+    out = F.conv2d(torch.relu(pre), w2.float().cpu().permute(0, 3, 1, 2), padding=1)
+    out.backward(dy2.float().cpu().permute(0, 3, 1, 2))
+    ref = pre.grad.permute(0, 2, 3, 1)
+    err = (dx.float().cpu() - ref).abs().max() / (ref.abs().max() + 1e-20)
+    assert err < 1e-2, err
