@@ -83,7 +83,7 @@ def _compare(go, logits_o, loss_o, logits_r, loss_r, gr):
             "low_cos": {n: round(c, 4) for n, c in sorted(cos.items(), key=lambda kv: kv[1])[:4]}}
 
 
-def _bf16_step_check(ours, ref, x, y, lr=0.05, deep_bn=False):
+def _bf16_step_check(ours, ref, x, y, lr=0.05, deep_bn=False, deep_relu=False):
     """GPU bf16 training step vs (a) the fp32 CPU reference and (b) the same reference with activations and
     activation-gradients rounded to bf16 wherever the kernels store bf16 ("bf16-storage reference").
 
@@ -124,7 +124,16 @@ def _bf16_step_check(ours, ref, x, y, lr=0.05, deep_bn=False):
     assert all(torch.isfinite(g_).all() for g_ in go.values())
     assert abs(st_32["loss_o"] - st_32["loss_r"]) < 1e-2 * max(1.0, abs(st_32["loss_r"])), st_32
     assert abs(st_q["loss_o"] - st_q["loss_r"]) < 1e-2 * max(1.0, abs(st_q["loss_r"])), st_q
-    if not deep_bn:
+    if deep_relu:
+        # 16 ReLU layers without normalisation: the two REFERENCES sit at gradient cosine 0.9972 (0.935 for the first
+        # layer's filter) from each other -- bf16 storage flips ReLU decisions whose effect grows with depth -- so the
+        # assertion is "no farther from either reference than they are from each other"; logits and loss stay strict.
+        # Strict per-layer parity at these very shapes: tests/test_tc_real_shapes.py, test_vgg_small_bf16_train_step.
+        for st in (st_q, st_32):
+            assert st["logits_rel"] < 1e-2, st
+            assert st["global_cos"] >= floor["global_cos"] - 2e-3, (st, floor)
+            assert st["min_cos"] >= floor["min_cos"] - 3e-2, (st, floor)
+    elif not deep_bn:
         for st in (st_q, st_32):
             assert st["logits_rel"] < 1e-2, st
         assert st_q["global_cos"] >= 0.999 and st_q["min_cos"] >= 0.99, st_q
@@ -187,6 +196,25 @@ def test_vgg_small_bf16_train_step():
     x = torch.randn(4, 3, 224, 224, generator=g)
     y = torch.randint(0, 96, (4,), generator=g)
     _bf16_step_check(ours, ref, x, y)
+
+
+def test_vgg16_bf16_train_step():
+    """The real VGG-16 (configuration D, 1000 classes, 4096-wide classifier: BASELINE.json configs[2]) at 224 x 224,
+    batch 2: 13 ReLU-fused convolutions with the 1-bit-mask / pooled-resolution ReLU backward, 5 pools, 3 Linear.
+    He initialisation on both sides (torch's default shrinks the signal by ~0.6 per layer, which leaves the logits of
+    a 16-layer net to the biases)."""
+    from replicann_b200.arch.vgg import VGG16
+    torch.manual_seed(0)
+    ref = R.RefVGG((64, 64, "M", 128, 128, "M", 256, 256, 256, "M", 512, 512, 512, "M", 512, 512, 512, "M"), 1000)
+    for m in ref.modules():
+        if isinstance(m, (torch.nn.Conv2d, torch.nn.Linear)):
+            torch.nn.init.kaiming_normal_(m.weight, nonlinearity="relu")
+            torch.nn.init.normal_(m.bias, std=0.05)
+    ours = VGG16(p_dropout=0.0).cuda().to(torch.bfloat16)
+    g = torch.Generator().manual_seed(1234)
+    x = torch.randn(4, 3, 224, 224, generator=g)
+    y = torch.randint(0, 1000, (4,), generator=g)
+    _bf16_step_check(ours, ref, x, y, lr=1e-3, deep_relu=True)
 
 
 def test_state_dict_roundtrip_and_eval_mode():
