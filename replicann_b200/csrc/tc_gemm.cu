@@ -68,6 +68,11 @@ struct TcParams {
   // CTA and the ring carries A tiles only (ring_stages stages of A_BYTES).  Needs a constant n-block per CTA
   // (gridDim.x % n_nblk == 0) and splits == 1.
   int b_resident, ring_stages;
+  // Two CTAs per SM (TcParams::dual): narrow tiles are paced by the two single-thread role loops of a CTA, not by
+  // memory or the tensor pipe (profiles/r02_tc_role_elimination.txt), so a second CTA with its own producer and MMA
+  // threads on the same SM doubles the step rate.  Each CTA then gets `nst` ring stages in `ring_area` bytes, one
+  // epilogue group (192 threads) and half of the SM's TMEM.
+  int dual, nst, ring_area;
   int no_b_resident;    // host only: never take the resident form (the packed-pixel first layer measured slower with it)
   // BGEMM: `splits` independent problems z = b * bg_heads + h, each with the full K range.  Operand X lives in a
   // 3-D tensor; its slab index is b (x_zdiv = 1: heads of a batch share rows, head h starts x_hoff * h elements
@@ -117,7 +122,8 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   const uint32_t raw_addr = tc::smem_u32(smem_raw);
   uint8_t* smem = smem_raw + (((raw_addr + 1023u) & ~1023u) - raw_addr);
 
-  uint8_t* staging = smem + C::STAGES * C::STAGE_BYTES;
+  const uint32_t ring_area = p.dual ? (uint32_t)p.ring_area : (uint32_t)(C::STAGES * C::STAGE_BYTES);
+  uint8_t* staging = smem + ring_area;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(staging + C::STAGING_BYTES);
   constexpr int MAXS = 8;   // barrier slots: the resident-filter form may run more ring stages than C::STAGES
   uint64_t* empty_bar = full_bar + MAXS;
@@ -127,9 +133,9 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bres_bar + 1);
   // resident-B form (see TcParams::b_resident): B sits at the end of the ring area, the ring strides by A_BYTES
   const bool bres = KIND == KIND_CONV && CG == 1 && p.b_resident != 0;
-  const int nstages = bres ? p.ring_stages : C::STAGES;
+  const int nstages = bres ? p.ring_stages : (p.dual ? p.nst : C::STAGES);
   const uint32_t stage_bytes = bres ? (uint32_t)A_BYTES : (uint32_t)C::STAGE_BYTES;
-  const uint32_t bres_off = (uint32_t)(C::STAGES * C::STAGE_BYTES - p.k_iters * C::B_BYTES);
+  const uint32_t bres_off = ring_area - (uint32_t)(p.k_iters * C::B_BYTES);
 
   // warp index through a shuffle: the compiler then knows it is warp-uniform and keeps the role loops' state
   // (stage counters, barrier addresses, TMA coordinates, MMA descriptors) in uniform registers
@@ -582,14 +588,14 @@ tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUten
         *reinterpret_cast<float2*>(mine + c * 64 + 2 * lane) = make_float2(st[c][0], st[c][1]);
         *reinterpret_cast<float2*>(mine + BN + c * 64 + 2 * lane) = make_float2(st[c][2], st[c][3]);
       }
-      asm volatile("bar.sync 1, 256;" ::: "memory");   // the 8 epilogue warps (STATS launches always have both groups)
+      const int nepi = (int)(blockDim.x >> 5) - 2;      // 8 epilogue warps, or 4 when two CTAs share the SM
+      asm volatile("bar.sync 1, %0;" ::"r"(nepi * 32) : "memory");
       const int nb = cluster_id % p.n_nblk;
       const int prow = (cluster_id / p.n_nblk) * CG + cta_rank;
       float* base = p.stat_partials + ((long long)(nb * p.stat_rows + prow) * 2) * BN;
-      for (int e = (warp - 2) * 32 + lane; e < 2 * BN; e += 256) {
+      for (int e = (warp - 2) * 32 + lane; e < 2 * BN; e += nepi * 32) {
         float a = 0.f;
-#pragma unroll
-        for (int w = 0; w < 8; ++w) a += reinterpret_cast<const float*>(staging + w * 4096)[e];
+        for (int w = 0; w < nepi; ++w) a += reinterpret_cast<const float*>(staging + w * 4096)[e];
         base[e] = a;
       }
     }
@@ -850,9 +856,23 @@ int b_resident_mode() {
 
 // STATS launches: every CTA (pair) keeps one n-block for all of its tiles, so the number of CTAs (pairs) is a
 // multiple of n_nblk.  Partial-sum rows: one per CTA.
-void plan_stats_grid(TcParams* p) {
+// RNN_TC_DUAL=1: run two CTAs per SM for the N = 64 convolution tiles (see TcParams::dual).  OFF by default: timed
+// alone the C64 layers gain 18-21 % (C64 3x3 111 -> 90 us, VGG 224^2 C64 800 -> 650 us, 1x1 C64->64 -11 %), but inside
+// a training step it LOSES (ResNet-50 19.36 -> 19.94 ms, VGG-16 15.10 -> 15.60 ms, same box): the two CTAs give up the
+// resident filter and take the whole SM's shared memory, so the kernels of the other stream no longer fit beside them.
+static int dual_mode() {
+  static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 0; }();
+  return v;
+}
+// the N = 64 convolution tiles on single CTAs with enough tiles to keep 2 x SMs CTAs busy (BN = 128 would get only two
+// ring stages per CTA and loses even alone)
+static bool want_dual(int BN, int cg, long long tiles) {
+  return dual_mode() != 0 && cg == 1 && BN == 64 && tiles >= 4ll * rnn_num_sms();
+}
+
+void plan_stats_grid(TcParams* p, bool dual) {
   const int cg = p->cg == 2 ? 2 : 1;
-  const int units = rnn_num_sms() / cg;
+  const int units = rnn_num_sms() / cg * (dual ? 2 : 1);
   p->force_grid = (units / p->n_nblk) * p->n_nblk * cg;
   p->stat_rows = p->force_grid / p->n_nblk;
 }
@@ -872,6 +892,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
   RNN_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
     RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    RNN_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   const int units = rnn_num_sms() / CG;   // CTAs, or CTA pairs
@@ -896,10 +917,30 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     }
   }
   // weight-gradient kernels run on a side stream next to other kernels: one epilogue group keeps them small
-  const int threads = (KIND == KIND_WGRAD && !STATS) ? NUM_THREADS_NARROW : NUM_THREADS;
+  int threads = (KIND == KIND_WGRAD && !STATS) ? NUM_THREADS_NARROW : NUM_THREADS;
+  int smem_launch = smem;
+  p.dual = 0;
+  if constexpr (KIND == KIND_CONV && CG == 1 && BN == 64) {
+    using C = Cfg<BN, CG, KIND>;
+    // per CTA: ring + staging + barriers must fit twice into the SM's 227 KB (1 KB per block is the driver's)
+    constexpr int kPerCta = (232448 - 2 * 1024) / 2;
+    constexpr int fixed = C::STAGING_BYTES + 1024 + 256;
+    constexpr int nst = (kPerCta - fixed) / C::STAGE_BYTES;
+    static_assert(nst >= 3, "two CTAs per SM need a ring of at least three stages each");
+    // statistics launches planned their (doubled) grid with the same predicate (conv_fprop_impl)
+    if (want_dual(BN, CG, tiles) && (p.force_grid == 0 || STATS)) {
+      p.dual = 1;
+      p.b_resident = 0;
+      p.nst = nst > 8 ? 8 : nst;
+      p.ring_area = p.nst * C::STAGE_BYTES;
+      smem_launch = p.ring_area + fixed;
+      threads = NUM_THREADS_NARROW;
+      if (p.force_grid == 0) grid = tiles < 2 * units ? tiles : 2 * units;
+    }
+  }
   RnnTimedScope timed("tc_kernel", stream);
   if (CG == 1) {
-    kern<<<grid, threads, smem, stream>>>(ta, tb, td, p);
+    kern<<<grid, threads, smem_launch, stream>>>(ta, tb, td, p);
   } else {
     cudaLaunchConfig_t cfg;
     memset(&cfg, 0, sizeof(cfg));
@@ -1271,7 +1312,7 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
   if (stat_partials != nullptr) {
     RNN_REQUIRE(d->K % BN == 0, RNN_ERR_SHAPE);  // statistics need whole N tiles
     RNN_REQUIRE(p.n_nblk <= rnn_num_sms() / 2, RNN_ERR_SHAPE);
-    plan_stats_grid(&p);
+    plan_stats_grid(&p, want_dual(BN, cg, (long long)p.n_mblk * p.n_nblk));
     p.stat_partials = stat_partials;
     *stat_rows = p.stat_rows;
   }
@@ -1306,7 +1347,7 @@ size_t rnn_conv2d_fprop_bn_stats_workspace(const rnn_conv_desc* d) {
   const int n_nblk = ceil_div_i(d->K, BN);
   const int sms = rnn_num_sms();
   if (n_nblk > sms) return 0;
-  const int grid = (sms / n_nblk) * n_nblk;
+  const int grid = (sms * (BN == 64 ? 2 : 1) / n_nblk) * n_nblk;   // N = 64 tiles may run two CTAs per SM
   return (size_t)n_nblk * (grid / n_nblk) * 2 * BN * sizeof(float);
 }
 
