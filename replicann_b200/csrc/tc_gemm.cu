@@ -858,8 +858,10 @@ int b_resident_mode() {
 // multiple of n_nblk.  Partial-sum rows: one per CTA.
 // RNN_TC_DUAL=1: run two CTAs per SM for the N = 64 convolution tiles (see TcParams::dual).  OFF by default: timed
 // alone the C64 layers gain 18-21 % (C64 3x3 111 -> 90 us, VGG 224^2 C64 800 -> 650 us, 1x1 C64->64 -11 %), but inside
-// a training step it LOSES (ResNet-50 19.36 -> 19.94 ms, VGG-16 15.10 -> 15.60 ms, same box): the two CTAs give up the
-// resident filter and take the whole SM's shared memory, so the kernels of the other stream no longer fit beside them.
+// a training step it LOSES (ResNet-50 19.36 -> 19.94 ms, VGG-16 15.10 -> 15.60 ms, same box).  ncu of the step's own
+// launches: both CTAs are resident (limit 2 by registers and shared memory, 18.6 % warps active), but the statistics
+// variant takes 162-218 us where the single CTA takes 135 -- with ONE epilogue group per CTA the heavier statistics
+// epilogue of consecutive tiles no longer overlaps; a second group per CTA would need <= 96 registers per thread.
 static int dual_mode() {
   static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 0; }();
   return v;
