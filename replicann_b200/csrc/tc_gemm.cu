@@ -73,7 +73,7 @@ struct TcParams {
   // threads on the same SM doubles the step rate.  Each CTA then gets `nst` ring stages in `ring_area` bytes, one
   // epilogue group (192 threads) and half of the SM's TMEM.
   int dual, nst, ring_area;
-  int no_b_resident;    // host only: never take the resident form (the packed-pixel first layer measured slower with it)
+  int no_b_resident;    // host only: the packed-pixel first layer -- never the resident form (measured slower with it)
   // BGEMM: `splits` independent problems z = b * bg_heads + h, each with the full K range.  Operand X lives in a
   // 3-D tensor; its slab index is b (x_zdiv = 1: heads of a batch share rows, head h starts x_hoff * h elements
   // into the inner dimension) or z (x_zdiv = 0).
@@ -862,14 +862,17 @@ int b_resident_mode() {
 // launches: both CTAs are resident (limit 2 by registers and shared memory, 18.6 % warps active), but the statistics
 // variant takes 162-218 us where the single CTA takes 135 -- with ONE epilogue group per CTA the heavier statistics
 // epilogue of consecutive tiles no longer overlaps; a second group per CTA would need <= 96 registers per thread.
-static int dual_mode() {
-  static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 0; }();
+// The packed-pixel first layer is the exception (7 K steps per tile, epilogue-bound): 394 -> 331 us (ResNet-50 stem) and
+// 546 -> 474 us (VGG-16 conv1_1) inside the step, so it takes the form unless RNN_TC_DUAL=0.
+static int dual_mode() {   // 0 never, 1 every eligible N = 64 convolution, 2 (default) the first layer only
+  static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 2; }();
   return v;
 }
 // the N = 64 convolution tiles on single CTAs with enough tiles to keep 2 x SMs CTAs busy (BN = 128 would get only two
 // ring stages per CTA and loses even alone)
-static bool want_dual(int BN, int cg, long long tiles) {
-  return dual_mode() != 0 && cg == 1 && BN == 64 && tiles >= 4ll * rnn_num_sms();
+static bool want_dual(int BN, int cg, long long tiles, bool first_layer = false) {
+  const int mode = dual_mode();
+  return (mode == 1 || (mode == 2 && first_layer)) && cg == 1 && BN == 64 && tiles >= 4ll * rnn_num_sms();
 }
 
 void plan_stats_grid(TcParams* p, bool dual) {
@@ -930,7 +933,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     constexpr int nst = (kPerCta - fixed) / C::STAGE_BYTES;
     static_assert(nst >= 3, "two CTAs per SM need a ring of at least three stages each");
     // statistics launches planned their (doubled) grid with the same predicate (conv_fprop_impl)
-    if (want_dual(BN, CG, tiles) && (p.force_grid == 0 || STATS)) {
+    if (want_dual(BN, CG, tiles, p.no_b_resident != 0) && (p.force_grid == 0 || STATS)) {
       p.dual = 1;
       p.b_resident = 0;
       p.nst = nst > 8 ? 8 : nst;
