@@ -10,11 +10,19 @@ from __future__ import annotations
 
 from typing import Iterable
 
+import os
+
 import torch
 
 from . import functional as RF
 
 _ALIGN = 8  # elements: keeps every parameter 16-byte aligned in bf16 (TMA base-address requirement)
+# Every stand-alone parameter (and the first member of a pack) starts on a 128-byte line: a filter that starts
+# mid-line makes every 128-byte row of every TMA box of it straddle two lines -- invisible to kernels that load the
+# filter once (resident form), a doubling of the B-operand traffic of those that stream it every K step.  Measured
+# through the one kernel form that streams narrow filters (RNN_TC_DUAL=1): 685 us with a torch-allocated filter,
+# 1168 us with the same filter at a 16-byte-aligned offset of the flat buffer.
+_ALIGN_BASE = int(os.environ.get("RNN_PARAM_ALIGN", "64"))
 
 
 class ParamPack:
@@ -67,13 +75,15 @@ class _FlatGroup:
     """One dtype's parameters flattened: work (param dtype), grad (param dtype), master/state (fp32)."""
 
     def __init__(self, params: list[torch.nn.Parameter]):
-        params = self._pack_order(params)
+        params, continued = self._pack_order(params)
         self.params = params
         dev, dt = params[0].device, params[0].dtype
         self.dtype = dt
         self.offsets = []
         off = 0
         for p in params:
+            if id(p) not in continued:      # pack members after the first stay back to back
+                off = (off + _ALIGN_BASE - 1) // _ALIGN_BASE * _ALIGN_BASE
             self.offsets.append(off)
             off += (p.numel() + _ALIGN - 1) // _ALIGN * _ALIGN
         self.numel = off
@@ -91,12 +101,12 @@ class _FlatGroup:
         self.state: dict[str, torch.Tensor] = {}
 
     @staticmethod
-    def _pack_order(params: list) -> list:
+    def _pack_order(params: list):
         """Layout order: the given order, except that the members of a declared ParamPack sit back to back (in
         pack order) where the first of them would have been.  A pack is honoured only when all of its members
         are in this group and need no alignment padding between them."""
         ids = {id(p) for p in params}
-        out, done = [], set()
+        out, done, continued = [], set(), set()
         for p in params:
             pk = getattr(p, "_rnn_pack", None)
             if pk is None or not all(id(m) in ids and m.numel() % _ALIGN == 0 and m.numel() == pk.members[0].numel()
@@ -107,10 +117,12 @@ class _FlatGroup:
                 continue
             if id(p) in done:
                 continue
-            for m in pk.members:
+            for i, m in enumerate(pk.members):
                 out.append(m)
                 done.add(id(m))
-        return out
+                if i > 0:
+                    continued.add(id(m))
+        return out, continued
 
     @staticmethod
     def _view(flat: torch.Tensor, p: torch.Tensor, off: int) -> torch.Tensor:
