@@ -856,23 +856,24 @@ int b_resident_mode() {
 
 // STATS launches: every CTA (pair) keeps one n-block for all of its tiles, so the number of CTAs (pairs) is a
 // multiple of n_nblk.  Partial-sum rows: one per CTA.
-// RNN_TC_DUAL=1: run two CTAs per SM for the N = 64 convolution tiles (see TcParams::dual).  OFF by default: timed
-// alone the C64 layers gain 18-21 % (C64 3x3 111 -> 90 us, VGG 224^2 C64 800 -> 650 us, 1x1 C64->64 -11 %), but inside
-// a training step it LOSES (ResNet-50 19.36 -> 19.94 ms, VGG-16 15.10 -> 15.60 ms, same box).  ncu of the step's own
-// launches: both CTAs are resident (limit 2 by registers and shared memory, 18.6 % warps active), but the statistics
-// variant takes 162-218 us where the single CTA takes 135 -- with ONE epilogue group per CTA the heavier statistics
-// epilogue of consecutive tiles no longer overlaps; a second group per CTA would need <= 96 registers per thread.
-// The packed-pixel first layer is the exception (7 K steps per tile, epilogue-bound): 394 -> 331 us (ResNet-50 stem) and
-// 546 -> 474 us (VGG-16 conv1_1) inside the step, so it takes the form unless RNN_TC_DUAL=0.
-static int dual_mode() {   // 0 never, 1 every eligible N = 64 convolution, 2 (default) the first layer only
-  static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 2; }();
+// RNN_TC_DUAL: two CTAs per SM for the N = 64 convolution tiles (see TcParams::dual).
+//   0 never   1 every eligible launch   2 the packed-pixel first layer only   3 (default) every eligible launch except
+//   those with the statistics epilogue.
+// Timed alone the C64 layers gain 18-21 % (C64 3x3 111 -> 90 us, VGG 224^2 C64 800 -> 650 us, 1x1 C64->64 -11 %).  Inside
+// a step (with 128-byte-aligned filters, see optim.py -- before that fix the filter-streaming dual form lost badly):
+// mode 3 vs mode 2: VGG-16 13.66 -> 13.25 ms, AlexNet 2.32 -> 2.23 ms, ResNet-50 18.60 -> 18.59 ms.  The statistics
+// variant stays on one CTA: with ONE epilogue group per CTA its heavier epilogue does not overlap across tiles
+// (ncu: 162-218 us against 135 us); a second group per CTA would need <= 96 registers per thread.
+static int dual_mode() {
+  static const int v = [] { const char* e = getenv("RNN_TC_DUAL"); return e != nullptr ? atoi(e) : 3; }();
   return v;
 }
 // the N = 64 convolution tiles on single CTAs with enough tiles to keep 2 x SMs CTAs busy (BN = 128 would get only two
 // ring stages per CTA and loses even alone)
-static bool want_dual(int BN, int cg, long long tiles, bool first_layer = false) {
-  const int mode = dual_mode();
-  return (mode == 1 || (mode == 2 && first_layer)) && cg == 1 && BN == 64 && tiles >= 4ll * rnn_num_sms();
+static bool want_dual(int BN, int cg, long long tiles, bool first_layer = false, bool stats = false) {
+  const int mode = dual_mode();   // 3: every N = 64 convolution except the statistics-epilogue launches
+  return (mode == 1 || (mode == 2 && first_layer) || (mode == 3 && !stats)) && cg == 1 && BN == 64 &&
+         tiles >= 4ll * rnn_num_sms();
 }
 
 void plan_stats_grid(TcParams* p, bool dual) {
@@ -933,7 +934,7 @@ int launch_inst2(const CUtensorMap& ta, const CUtensorMap& tb, const TcParams& p
     constexpr int nst = (kPerCta - fixed) / C::STAGE_BYTES;
     static_assert(nst >= 3, "two CTAs per SM need a ring of at least three stages each");
     // statistics launches planned their (doubled) grid with the same predicate (conv_fprop_impl)
-    if (want_dual(BN, CG, tiles, p.no_b_resident != 0) && (p.force_grid == 0 || STATS)) {
+    if (want_dual(BN, CG, tiles, p.no_b_resident != 0, STATS) && (p.force_grid == 0 || STATS)) {
       p.dual = 1;
       p.b_resident = 0;
       p.nst = nst > 8 ? 8 : nst;
@@ -1317,7 +1318,7 @@ static int conv_fprop_impl(const rnn_conv_desc* d, const void* x, const void* w,
   if (stat_partials != nullptr) {
     RNN_REQUIRE(d->K % BN == 0, RNN_ERR_SHAPE);  // statistics need whole N tiles
     RNN_REQUIRE(p.n_nblk <= rnn_num_sms() / 2, RNN_ERR_SHAPE);
-    plan_stats_grid(&p, want_dual(BN, cg, (long long)p.n_mblk * p.n_nblk));
+    plan_stats_grid(&p, want_dual(BN, cg, (long long)p.n_mblk * p.n_nblk, false, true));
     p.stat_partials = stat_partials;
     *stat_rows = p.stat_rows;
   }

@@ -37,11 +37,13 @@ def test_conv_parity_with_the_filter_resident_form_forced():
 
 @pytest.mark.gpu
 def test_conv_parity_with_two_ctas_per_sm():
-    """RNN_TC_DUAL=1 (off by default: faster alone, slower inside a step) runs the N = 64 convolution tiles as two CTAs
-    per SM, each with a three-stage ring and one epilogue group; it only engages at large tile counts, so the
-    batch-256 C64 3x3 case (fprop with the statistics epilogue, dgrad, wgrad) is the parity check."""
-    env = dict(os.environ, RNN_TC_DUAL="1")
-    r = subprocess.run([sys.executable, "-m", "pytest", str(ROOT / "tests" / "test_tc_real_shapes.py"), "-m", "gpu", "-q",
-                        "-x", "-k", "r50_s1_3x3_c64 or vgg_3x3_c64_224", "--timeout", "600", "-p", "no:cacheprovider"],
-                       cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
-    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    """Two CTAs per SM for the N = 64 convolution tiles (each with a three-stage ring and one epilogue group): the
+    default takes it for every such launch except the statistics epilogue; RNN_TC_DUAL=1 includes that one, =0 is the
+    single-CTA form.  It only engages at large tile counts, so the batch-256 C64 3x3 and VGG 224^2 cases (fprop with
+    the statistics epilogue, dgrad, wgrad) are the parity check, under both non-default settings."""
+    for mode in ("1", "0"):
+        env = dict(os.environ, RNN_TC_DUAL=mode)
+        r = subprocess.run([sys.executable, "-m", "pytest", str(ROOT / "tests" / "test_tc_real_shapes.py"), "-m", "gpu",
+                            "-q", "-x", "-k", "r50_s1_3x3_c64", "--timeout", "600", "-p", "no:cacheprovider"],
+                           cwd=ROOT, env=env, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, f"RNN_TC_DUAL={mode}\n" + r.stdout[-3000:] + r.stderr[-2000:]
